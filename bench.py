@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the kinodynamic RRT* hot path on B200 (contract: see the task statement).
+
+Workload (N = 1): BASELINE.json configs[1] — one RRT* tree on the soccer field with 9 moving opponents, time-space
+collision checks, direct-goal sampling p = 0.1, 20 000 iterations.  A "step" is one complete plan.
+  value  RRT* expansions/s, device time of the grow call only (inputs resident in HBM)
+  e2e    the same metric through the C ABI with HOST buffers: obstacle upload + start + grow + result read-back,
+         CUDA events on the context's stream around the whole sequence
+N > 1: a single tree does not shard ("replicas only"): every rank plans the same scene with its own
+Philox stream (query_id = rank); value = all ranks' expansions / max-over-ranks time.  The batched-query sweep, which
+DOES shard (contiguous blocks + one NCCL all-gather of results), is reported in the same line under "batched".
+
+--impl reference: the CPU oracle (oracle/krrt_oracle.c — the reference's own RRT* sources are an absent submodule,
+so nothing of it can be built: DESIGN.md §3) timed on the host cores on the same config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+N_ITER = 20000
+P_DIRECT = 0.1
+BATCH_Q = 4096          # config 3/4: queries per GPU
+BATCH_ITERS = 200
+METRIC = "rrtstar_expansions_per_sec"
+UNIT = "expansions/s"
+WORKLOAD = "C2: soccer field, 9 moving opponents, time-space collision, direct-goal p=0.1, 20000 iterations, fp64"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[2 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def c2_scene():
+    from robosoccer_motion_planning_b200 import scenes
+    return scenes.dynamic_obstacles(), scenes.START, scenes.GOAL
+
+
+# ---------------------------------------------------------------------------------------------- reference arm
+def run_reference(args, rank, world):
+    """CPU oracle on the host cores: `world` replicas of the C2 plan, one thread each (a single tree is sequential)."""
+    if rank != 0:
+        return
+    import oracle_binding as ob
+    obs, start, goal = c2_scene()
+    n = max(1, world)
+    cores = min(n, os.cpu_count() or 1)
+    cfg = ob.default_config(p_direct=P_DIRECT, capacity=N_ITER + 2)
+    starts = np.tile(start, (n, 1))
+    goals = np.tile(goal, (n, 1))
+    obss = np.tile(obs, (n, 1, 1))
+    for _ in range(args.warmup):
+        ob.plan_batch(cfg, starts, goals, obss, 1, N_ITER, nthreads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = ob.plan_batch(cfg, starts, goals, obss, 1, N_ITER, nthreads=cores)
+    dt = time.perf_counter() - t0
+    value = n * N_ITER * args.steps / dt
+    # batched queries on all host cores, bounded sample
+    from robosoccer_motion_planning_b200 import scenes
+    allc = os.cpu_count() or 1
+    qs = 16 * allc
+    bs, bg, bo = scenes.batch_queries(qs, 9, seed=0)
+    cfgb = ob.default_config(p_direct=P_DIRECT)
+    tb = time.perf_counter()
+    ob.plan_batch(cfgb, bs, bg, bo, 1, BATCH_ITERS, nthreads=allc)
+    tb = time.perf_counter() - tb
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "replicas": n, "note": "CPU oracle port; the reference's RRT* sources "
+                   "(submodule alifahrri/motion_planning@3b3183e) are absent, nothing of it builds"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} full plans x {n} replica(s), {N_ITER} iterations each, kd-tree near search"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "batched": {"queries_per_sec": qs / tb, "expansions_per_sec": qs * BATCH_ITERS / tb, "queries": qs,
+                    "iters": BATCH_ITERS, "cores": allc},
+        "solved": int(out["solved"].sum()),
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------- our arm
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from robosoccer_motion_planning_b200 import capi, scenes, sweep
+    assert torch.cuda.is_available(), "bench.py needs a GPU: libkrrt has no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def flush_l2():
+        flush_buf.zero_()
+        torch.cuda.synchronize()
+
+    obs, start, goal = c2_scene()
+    G = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, query_id=rank, batch=args.batch)
+
+    def plan_device_timed():
+        G.set_obstacles(obs, 1)
+        G.set_start(start)
+        r = G.grow(goal, N_ITER)
+        return G.last_timing()["total_ms"], r
+
+    def plan_e2e():
+        G.timer_begin()
+        G.set_obstacles(obs, 1)
+        G.set_start(start)
+        r = G.grow(goal, N_ITER)
+        res = G.result(*r)
+        return G.timer_end(), res
+
+    for _ in range(max(args.warmup, 3)):
+        plan_device_timed()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    # ---- value: device time of the grow call, K steps
+    barrier()
+    l0 = G.launch_count
+    tot_ms = 0.0
+    for _ in range(args.steps):
+        flush_l2()
+        ms, r_last = plan_device_timed()
+        tot_ms += ms
+    launches = G.launch_count - l0
+    barrier()
+    tot_ms = max_over_ranks(tot_ms)
+    value = world * N_ITER * args.steps / (tot_ms * 1e-3)
+    # ---- e2e: host buffers, copies inside the timed region
+    barrier()
+    e2e_ms = 0.0
+    for _ in range(args.steps):
+        flush_l2()
+        ms, res = plan_e2e()
+        e2e_ms += ms
+    barrier()
+    e2e_ms = max_over_ranks(e2e_ms)
+    e2e_value = world * N_ITER * args.steps / (e2e_ms * 1e-3)
+    clocks = sampler.stop() if rank == 0 else None
+    ctl_bytes = 224
+    path_len = int(res["path_len"])
+    h2d = obs.nbytes + 64
+    d2h = 4 * ctl_bytes + min(path_len, 32) * 40 + 4 + 16
+
+    # ---- roofline of the neighbour scan (profile pass: CUDA events around every scan launch)
+    peak, peak_src = peaks()
+    G.set_profile(1)
+    flush_l2()
+    plan_device_timed()
+    lt = G.last_timing()
+    G.set_profile(0)
+    scan_bytes = lt["scan_node_samples"] * 32.0
+    achieved = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k_near_scan", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": scan_bytes / max(1, lt["scan_launches"]),
+                "avg_launch_us": 1e3 * lt["scan_ms"] / max(1, lt["scan_launches"]),
+                "share_of_step": lt["scan_ms"] / lt["total_ms"] if lt["total_ms"] > 0 else None,
+                "note": "algorithmic bytes = 32 B x tree nodes x samples served by the launch (SURVEY §8d: N x 32 B per "
+                        "expansion); one launch serves a batch of samples from one pass over the states, so frac can "
+                        "exceed 1; trees <= 20k nodes (640 KB) are L2-resident"}
+
+    # ---- batched queries (configs 3/4): one warp per query, sharded over ranks, NCCL all-gather of the results
+    q_total = BATCH_Q * world
+    lo, hi = sweep.shard_bounds(q_total, rank, world)
+    bs, bg, bo = scenes.batch_queries(hi - lo, 9, seed=0, first=lo)
+    Gb = capi.Planner(device=local_rank, p_direct=P_DIRECT)
+    d_s = torch.from_numpy(bs).to(dev)
+    d_g = torch.from_numpy(bg).to(dev)
+    d_o = torch.from_numpy(bo).to(dev)
+    item = capi.RESULT_DTYPE.itemsize
+    d_out = torch.zeros((hi - lo) * item, dtype=torch.uint8, device=dev)
+    d_all = torch.zeros(q_total * item, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def batched_step():
+        Gb.plan_batch_device(d_s.data_ptr(), d_g.data_ptr(), d_o.data_ptr(), hi - lo, 9, 1, BATCH_ITERS, lo,
+                             d_out.data_ptr(), stream)
+        if world > 1:
+            dist.all_gather_into_tensor(d_all, d_out)
+
+    for _ in range(3):
+        batched_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    bsteps = max(3, args.steps)
+    b_ms = 0.0
+    for _ in range(bsteps):
+        flush_l2()
+        e0.record()
+        batched_step()
+        e1.record()
+        e1.synchronize()
+        b_ms += e0.elapsed_time(e1)
+    barrier()
+    b_ms = max_over_ranks(b_ms)
+    # e2e batched: pinned host buffers through krrt_plan_batch
+    p_s = torch.from_numpy(bs).pin_memory().numpy()
+    p_g = torch.from_numpy(bg).pin_memory().numpy()
+    p_o = torch.from_numpy(bo).pin_memory().numpy()
+    Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo)
+    be_ms = 0.0
+    for _ in range(bsteps):
+        flush_l2()
+        Gb.timer_begin()
+        out_h = Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo)
+        be_ms += Gb.timer_end()
+    barrier()
+    be_ms = max_over_ranks(be_ms)
+    batched = {
+        "workload": f"{BATCH_Q} queries/GPU x {BATCH_ITERS} iterations, 9 moving obstacles, p_direct=0.1 (C4; sharded sweep C5 for N>1)",
+        "queries_per_sec": q_total * bsteps / (b_ms * 1e-3),
+        "expansions_per_sec": q_total * BATCH_ITERS * bsteps / (b_ms * 1e-3),
+        "ms_per_step": b_ms / bsteps,
+        "e2e_queries_per_sec": q_total * bsteps / (be_ms * 1e-3),
+        "h2d_bytes_per_step": int(bs.nbytes + bg.nbytes + bo.nbytes), "d2h_bytes_per_step": int((hi - lo) * item),
+        "gather": "nccl all_gather_into_tensor of result records" if world > 1 else "none (1 GPU)",
+        "solved_frac": float(out_h["solved"].mean()),
+    }
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "replicas": world, "speculative_batch": int(G.cfg.batch),
+                   "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only (single tree); "
+                   "batched queries shard by contiguous blocks"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "batched": batched,
+        "tree_nodes": int(res["n_nodes"]), "solved": bool(res["solved"]), "cost": float(res["cost"]),
+    }
+
+    if rank == 0 and world == 1:
+        import oracle_binding as ob
+        O = ob.OraclePlanner(capacity=N_ITER + 2, p_direct=P_DIRECT, query_id=0)
+        reps = 3
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            O.set_obstacles(obs, 1)
+            O.set_start(start)
+            ro = O.grow(goal, N_ITER)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": reps * N_ITER / dt, "unit": UNIT, "cores": 1, "kind": "port",
+                                "sample": f"{reps} full C2 plans ({N_ITER} iterations each), kd-tree near search, 1 thread "
+                                          "(a single RRT* tree is sequential)"}
+        same = all(np.array_equal(a, b) for a, b in zip(G.tree(), O.tree())) and r_last == ro
+        line["parity_vs_oracle"] = "bit-exact" if same else "MISMATCH"
+        # batched CPU baseline on all host cores, bounded sample
+        allc = os.cpu_count() or 1
+        qs = min(hi - lo, 16 * allc)
+        tb = time.perf_counter()
+        refb = ob.plan_batch(ob.default_config(p_direct=P_DIRECT), bs[:qs], bg[:qs], bo[:qs], 1, BATCH_ITERS,
+                             query_base=lo, nthreads=allc)
+        tb = time.perf_counter() - tb
+        line["batched"]["cpu_baseline"] = {"queries_per_sec": qs / tb, "cores": allc, "kind": "port",
+                                           "sample": f"{qs} of the {BATCH_Q} queries"}
+        line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
+                                               else "MISMATCH")
+        # config 3: single large tree, 100k iterations, static obstacles
+        if not args.skip_c3:
+            G3 = capi.Planner(device=local_rank, capacity=100002, batch=args.batch)
+            G3.set_profile(1)
+            G3.set_obstacles(scenes.static_obstacles(), 0)
+            G3.set_start(start)
+            flush_l2()
+            G3.grow(None, 100000)
+            t3 = G3.last_timing()
+            line["c3_100k"] = {"expansions_per_sec": 100000 / (t3["total_ms"] * 1e-3), "nodes": G3.size,
+                               "scan_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
+                               "scan_share": t3["scan_ms"] / t3["total_ms"]}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=0, help="speculative batch size (0 = library default)")
+    ap.add_argument("--skip-c3", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, max(world, args.gpus if world == 1 else world))
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,149 @@
+/* krrt.h — C ABI of libkrrt.so, the sm_100a kinodynamic RRT* hot path.
+ *
+ * This is the drop-in boundary: plain C, opaque handles, caller-owned HOST
+ * buffers, the library owns device memory, every call returns an int status (0 = OK) and
+ * never throws or longjmps.  One krrt_ctx = one CUDA device + one stream; a ctx is NOT
+ * thread-safe, distinct ctxs may be used from distinct threads / GPUs.  There is no CPU
+ * fallback: every entry point runs CUDA kernels or fails with a status.
+ *
+ * What each entry point replaces in the reference (all paths under /root/reference/src/;
+ * the RRT* sources themselves are the absent submodule src/motion_planning, so the citations
+ * are the in-tree call sites of the RRTStar<Tree,Cost,Sampler,NeighborRadius,Environment,
+ * GoalChecker,Connector> component surface):
+ *
+ *   krrt_set_start      rrt.setStart(xs); rrt.setIteration(0)   robosoccer_motion_planning/src/robosoccer_motion_planning_node.cpp:135-136
+ *   krrt_set_obstacles  env.setObstacles(subs.getObstacles())   …node.cpp:139-141
+ *   krrt_grow           for(i<iteration) rrt.grow(xg)           …node.cpp:176-185   (+ sampler.set_next_sample :184 via `samples`)
+ *   goal_index out      rrt.goalIndex()                         robosoccer_motion_planning/include/robosoccer_visual.hpp:19
+ *   krrt_steer_cost     solver.solver.cost(xi,xf) -> (t,c)      …node.cpp:242-244   (Cost slot)
+ *   krrt_solve          solver.solver.solve(xi,xf,dt)           …node.cpp:245       (Connector slot)
+ *   krrt_near           Tree nearest / radius query (KD-tree in the reference)      (Tree slot)
+ *   krrt_edge_collide   Environment collision predicate, static and env.at(t) time-space variants
+ *                                                               robosoccer_visual.hpp:16-17,35 ; …node.cpp:84-85
+ *   krrt_tree_download  tree.tree.cloud.states / tree.parent / tree.trajectories    robosoccer_visual.hpp:18
+ *   krrt_path           tree.states(idx) root->idx chain        …node.cpp:237
+ *   krrt_trajectory     get_trajectory(): per edge solver.solve(a,b,0.1) appended   …node.cpp:232-249
+ *   krrt_plan_batch     solve_rrt() (…node.cpp:167-196) for q independent queries at once
+ */
+#ifndef KRRT_H
+#define KRRT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KRRT_MAX_OBS 64
+#define KRRT_MAX_WAYPOINTS 32
+
+enum {
+  KRRT_OK = 0,
+  KRRT_ERR_INVALID = 1,       /* bad argument / config                                      */
+  KRRT_ERR_CUDA = 2,          /* a CUDA runtime call failed (text in krrt_last_error)       */
+  KRRT_ERR_NO_DEVICE = 3,     /* no usable sm_100 device: there is NO CPU fallback          */
+  KRRT_ERR_NEAR_OVERFLOW = 4, /* a near set exceeded near_cap; raise near_cap and re-plan   */
+  KRRT_ERR_STATE = 5,         /* call order (e.g. grow before set_start)                    */
+  KRRT_ERR_UNSUPPORTED = 6
+};
+
+enum { KRRT_F64 = 0, KRRT_F32 = 1 };
+
+typedef struct krrt_config {
+  int32_t device;     /* CUDA device ordinal                                                 */
+  int32_t precision;  /* KRRT_F64 (bit-exact with the oracle). KRRT_F32 -> KRRT_ERR_UNSUPPORTED for now */
+  int32_t capacity;   /* max tree nodes                                                      */
+  int32_t S;          /* samples per edge for collision checks, both end points included     */
+  double r;           /* input weight of J = int (1 + r|u|^2) dt; solver.set_weight(r) (…node.cpp:91-92) */
+  double R;           /* env.collision_radius (…node.cpp:84)                                 */
+  double lo[4];       /* sampler bounds x,y,vx,vy                                            */
+  double hi[4];
+  double gamma;       /* near radius rho(n) = min(rho_max, gamma (ln n / n)^(1/4))           */
+  double rho_max;
+  double p_direct;    /* sampler.set_direct_sample(true, p) (…node.cpp:225-226)              */
+  double goal_tol;    /* node is a goal node iff |x - goal| <= goal_tol (4-D Euclidean)      */
+  uint64_t seed;      /* Philox4x32-10 key                                                   */
+  uint32_t query_id;  /* Philox counter word 1                                               */
+  int32_t batch;      /* speculative batch: samples evaluated against a frozen tree per round, then
+                         committed in order (results do not depend on it). 0 -> default      */
+  int32_t near_cap;   /* per-sample candidate capacity. 0 -> default                         */
+} krrt_config;
+
+typedef struct krrt_result {
+  int32_t solved;
+  int32_t goal_index;
+  int32_t n_nodes;
+  int32_t path_len;   /* true length of the root->goal chain (may exceed KRRT_MAX_WAYPOINTS) */
+  double cost;
+  double time;
+  double waypoints[KRRT_MAX_WAYPOINTS][5]; /* x,y,vx,vy,t_arrival */
+} krrt_result;
+
+typedef struct krrt_stats {
+  int64_t iters, inserted, fail_reject, fail_dup, fail_nofree;
+  int64_t rewired, propagated, sum_near, steer_calls, collide_calls;
+} krrt_stats;
+
+typedef struct krrt_ctx krrt_ctx;
+
+void krrt_default_config(krrt_config* c);
+int krrt_create(const krrt_config* c, krrt_ctx** out);
+void krrt_destroy(krrt_ctx* ctx);
+const char* krrt_last_error(const krrt_ctx* ctx); /* ctx may be NULL: last create error */
+int krrt_device_count(void);
+
+int krrt_set_obstacles(krrt_ctx* ctx, const double* xyvxvy, int m, int dynamic);
+int krrt_set_start(krrt_ctx* ctx, const double x0[4]);
+/* n_iter exact sequential RRT* expansions.  goal: NULL or 4 doubles.  samples: NULL or n_iter x 4
+ * host doubles; a row whose first entry is NaN means "draw from the internal Philox sampler". */
+int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved,
+              int* goal_index);
+int krrt_tree_size(krrt_ctx* ctx, int* n);
+int krrt_iteration(krrt_ctx* ctx, int64_t* iter);
+int krrt_last_sample(krrt_ctx* ctx, double out[4]);
+int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out);
+/* any of the output pointers may be NULL.  states: n x 4, parent: n, cost/time: n              */
+int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time);
+/* root -> idx chain; states cap x 4, times cap; *len = true chain length                        */
+int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len);
+int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out);
+/* fine re-solve of the root -> idx path at step dt: rows (x,y,vx,vy,t) ; *n_rows = rows needed   */
+int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_rows, int* n_rows);
+
+/* stateless batched operators on host arrays (n pairs / edges) */
+int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, double* t, double* c);
+int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
+               int cap_rows, int* n_rows);
+int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const double* tau, const double* t0,
+                      int n, unsigned char* hit);
+/* radius query on the current tree: ascending indices, *count = true count, nearest = lowest index on ties */
+int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, int cap, int* count,
+              int32_t* nearest, double* nearest_d2);
+
+/* q independent queries, one warp each, trees in shared memory.  starts/goals q x 4, obstacles q x m x 4.
+ * Philox query_id = query_base + i.  Uses ctx's config except capacity (= n_iter + 2).         */
+int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, const double* obstacles, int q,
+                    int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* out);
+/* same with device-resident inputs/outputs (pointers from the caller's CUDA allocator, e.g. for
+ * timing with inputs already in HBM, or to feed an NCCL gather without a host round trip)      */
+int krrt_plan_batch_device(krrt_ctx* ctx, const double* d_starts, const double* d_goals,
+                           const double* d_obstacles, int q, int m, int dynamic, int n_iter,
+                           uint32_t query_base, krrt_result* d_out, void* cuda_stream);
+/* oracle-comparable counters summed over the queries of the last batched plan                    */
+int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out);
+/* kernels launched by this ctx since creation (bench.py's gpu_launches)                          */
+int64_t krrt_launch_count(const krrt_ctx* ctx);
+/* CUDA-event stopwatch on the ctx stream spanning any sequence of calls (end-to-end timing incl. copies) */
+int krrt_timer_begin(krrt_ctx* ctx);
+int krrt_timer_end(krrt_ctx* ctx, double* ms);
+/* profile mode: CUDA events around every neighbour-scan launch of krrt_grow (adds a little launch gap)  */
+int krrt_set_profile(krrt_ctx* ctx, int on);
+/* device time of the last krrt_grow / krrt_plan_batch in ms (CUDA events on the ctx stream), and the share
+ * spent in the neighbour-scan kernel (for the roofline line).                                   */
+int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* scan_launches,
+                     double* scan_node_samples);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

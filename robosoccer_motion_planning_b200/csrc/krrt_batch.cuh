@@ -1,0 +1,195 @@
+// krrt_batch.cuh — k_plan_batch: many independent small planning queries, one warp per query, the whole tree
+// (states, costs, child lists, near list) in shared memory.  Replaces solve_rrt()
+// (robosoccer_motion_planning_node.cpp:167-196: setStart, setObstacles, for(i<iteration) grow(xg)) run once per
+// robot / seed / start-goal pair; the live system plans ~75-200-node trees at a high rate (config.yaml:3).
+// Warps pull queries from a global counter, so the grid is sized to the machine, not to q.
+#pragma once
+#include "krrt_warp.cuh"
+
+namespace krrt {
+
+struct ResultRec {  // layout == krrt_result (include/krrt.h)
+  int solved, goal_index, n_nodes, path_len;
+  double cost, time;
+  double waypoints[32][5];
+};
+
+struct BatchJob {
+  const double* starts;     // q x 4
+  const double* goals;      // q x 4
+  const double* obstacles;  // q x m x 4
+  ResultRec* out;           // q
+  int* next_query;          // work counter
+  long long* stats;         // [10] accumulated over queries
+  const double* rho2;       // [cap + 1]
+  int q, m, dynamic, n_iter, cap;
+  uint32_t query_base;
+  double r, R2, goal_tol2;
+  int S;
+  SamplerParams sp;
+};
+
+__host__ __device__ inline size_t batch_warp_smem_bytes(int cap, int m) {
+  size_t b = 0;
+  b += (size_t)cap * 16 * 2;                        // pos, vel
+  b += (size_t)(m > 0 ? m : 1) * 32;                // obstacles
+  b += (size_t)cap * 8 * 8;                         // ctc, tim, ecost, etime, cf, tf, cb, tb
+  b += (size_t)cap * 4 * 6;                         // parent, head, next, prev, queue, near idx
+  b += ((size_t)cap + 15) / 16 * 16;                // tried
+  return (b + 15) / 16 * 16;
+}
+
+__global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = lane_id();
+  const int warp = threadIdx.x >> 5;
+  const int cap = J.cap;
+  unsigned char* base = smem + (size_t)warp * batch_warp_smem_bytes(cap, J.m);
+  TreeView T;
+  NearView N;
+  T.pos = reinterpret_cast<double2*>(base);
+  T.vel = T.pos + cap;
+  double4* s_obs = reinterpret_cast<double4*>(T.vel + cap);
+  T.ctc = reinterpret_cast<double*>(s_obs + (J.m > 0 ? J.m : 1));
+  T.tim = T.ctc + cap;
+  T.ecost = T.tim + cap;
+  T.etime = T.ecost + cap;
+  N.cf = T.etime + cap;
+  N.tf = N.cf + cap;
+  N.cb = N.tf + cap;
+  N.tb = N.cb + cap;
+  T.parent = reinterpret_cast<int*>(N.tb + cap);
+  T.head = T.parent + cap;
+  T.next = T.head + cap;
+  T.prev = T.next + cap;
+  T.queue = T.prev + cap;
+  N.idx = T.queue + cap;
+  N.tried = reinterpret_cast<unsigned char*>(N.idx + cap);
+  T.cap = cap;
+  EnvView E = {s_obs, J.m, J.dynamic, J.R2, J.S};
+  Stats st = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+
+  for (;;) {
+    int qi = 0;
+    if (lane == 0) qi = atomicAdd(J.next_query, 1);
+    qi = __shfl_sync(FULL, qi, 0);
+    if (qi >= J.q) break;
+    const uint32_t query_id = J.query_base + (uint32_t)qi;
+    const double* gs = J.goals + 4 * (size_t)qi;
+    const double* xs = J.starts + 4 * (size_t)qi;
+    const State4 goal = {gs[0], gs[1], gs[2], gs[3]};
+    for (int j = lane; j < J.m; j += 32) {
+      const double* o = J.obstacles + ((size_t)qi * J.m + j) * 4;
+      s_obs[j] = make_double4(o[0], o[1], o[2], o[3]);
+    }
+    if (lane == 0) {
+      T.pos[0] = make_double2(xs[0], xs[1]);
+      T.vel[0] = make_double2(xs[2], xs[3]);
+      T.parent[0] = -1;
+      T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
+      T.head[0] = -1; T.next[0] = -1; T.prev[0] = -1;
+    }
+    __syncwarp();
+    int n = 1;
+    for (int it = 0; it < J.n_iter; ++it) {
+      const State4 s = draw_sample(J.sp, query_id, (uint64_t)it, true, goal);
+      st.iters++;
+      if (!J.dynamic && warp_point_in_obstacle(s, E)) {
+        st.fail_reject++;
+        continue;
+      }
+      if (n >= cap) break;
+      const double rho2n = J.rho2[n];
+      // near set (ascending by construction) + nearest + duplicate detection
+      int K = 0;
+      bool dup = false;
+      double bd = INFINITY;
+      int bi = -1;
+      for (int b0 = 0; b0 < n; b0 += 32) {
+        const int i = b0 + lane;
+        bool valid = false;
+        if (i < n) {
+          double d = dist2(load_state(T, i), s);
+          if (bi < 0 || d < bd) {
+            bd = d;
+            bi = i;
+          }
+          valid = d <= rho2n;
+          dup |= d == 0.0;
+        }
+        unsigned mk = __ballot_sync(FULL, valid);
+        if (valid) N.idx[K + __popc(mk & ((1u << lane) - 1))] = i;
+        K += __popc(mk);
+      }
+      if (__any_sync(FULL, dup)) {
+        st.fail_dup++;
+        continue;
+      }
+      __syncwarp();
+      if (K == 0) {
+        int aux = 0;
+        warp_argmin(bd, bi, aux);
+        if (lane == 0) N.idx[0] = bi;
+        K = 1;
+        __syncwarp();
+        if (lane == 0) {
+          double t, c;
+          steer(load_state(T, bi), s, J.r, t, c);
+          N.cf[0] = c; N.tf[0] = t; N.cb[0] = 0.0; N.tb[0] = 0.0;
+        }
+      } else {
+        // both steering directions of every near node, 2K independent tasks over the lanes
+        for (int t = lane; t < 2 * K; t += 32) {
+          const bool fwd = t < K;
+          const int k = fwd ? t : t - K;
+          const State4 x = load_state(T, N.idx[k]);
+          double tau, c;
+          if (fwd) {
+            steer(x, s, J.r, tau, c);
+            N.tf[k] = tau; N.cf[k] = c;
+          } else {
+            steer(s, x, J.r, tau, c);
+            N.tb[k] = tau; N.cb[k] = c;
+          }
+        }
+      }
+      __syncwarp();
+      st.sum_near += K;
+      int nw = warp_commit(T, N, K, n, s, E, st);
+      if (nw >= 0) n = nw + 1;
+      __syncwarp();
+    }
+    // result record
+    const int gi = warp_find_goal(T, n, goal, J.goal_tol2);
+    ResultRec* R = J.out + qi;
+    double* wp = &R->waypoints[0][0];
+    for (int k = lane; k < 32 * 5; k += 32) wp[k] = 0.0;
+    __syncwarp();
+    if (lane == 0) {
+      R->solved = gi >= 0;
+      R->goal_index = gi;
+      R->n_nodes = n;
+      int len = 0;
+      for (int i = gi; i >= 0 && len < n; i = T.parent[i]) ++len;
+      R->path_len = len;
+      R->cost = gi >= 0 ? T.ctc[gi] : 0.0;
+      R->time = gi >= 0 ? T.tim[gi] : 0.0;
+      int p = len - 1;
+      for (int i = gi; i >= 0 && p >= 0; i = T.parent[i], --p) {
+        if (p < 32) {
+          double2 a = T.pos[i], v = T.vel[i];
+          R->waypoints[p][0] = a.x; R->waypoints[p][1] = a.y;
+          R->waypoints[p][2] = v.x; R->waypoints[p][3] = v.y;
+          R->waypoints[p][4] = T.tim[i];
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0 && J.stats) {
+    const long long* sv = &st.iters;
+    for (int k = 0; k < 10; ++k) atomicAdd(reinterpret_cast<unsigned long long*>(J.stats + k), (unsigned long long)sv[k]);
+  }
+}
+
+}  // namespace krrt

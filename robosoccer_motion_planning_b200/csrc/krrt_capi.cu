@@ -1,0 +1,482 @@
+// krrt_capi.cu — host runtime behind include/krrt.h: owns device memory, one stream per context, launches the
+// sm_100a kernels.  No CPU fallback: when no Blackwell device is present krrt_create fails with
+// KRRT_ERR_NO_DEVICE and nothing else works.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/krrt.h"
+#include "krrt_batch.cuh"
+#include "krrt_kernels.cuh"
+#include "krrt_ops.cuh"
+
+using namespace krrt;
+
+static_assert(sizeof(ResultRec) == sizeof(krrt_result), "result layout");
+static_assert(sizeof(Stats) == sizeof(krrt_stats), "stats layout");
+static_assert(KRRT_MAX_OBS_DEV == KRRT_MAX_OBS, "obstacle cap");
+
+static thread_local std::string g_create_error;
+
+struct krrt_ctx {
+  krrt_config cfg;
+  cudaStream_t stream = nullptr;
+  cudaDeviceProp prop;
+  std::string err;
+  int64_t launches = 0;
+  bool started = false;
+  int n_upper = 0;  // host-side upper bound of the tree size (sizes the scan grid without a sync)
+
+  TreeView T{};
+  double* d_rho2 = nullptr;
+  double4* d_obs = nullptr;
+  Ctl* d_ctl = nullptr;
+  Batch Bt{};
+  Params P{};
+  double* d_user = nullptr;
+  size_t user_cap = 0;
+  std::vector<void*> allocs;
+
+  // scratch for stateless operators / batched planner
+  void* d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t scratch_cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  double* d_rho2_batch = nullptr;
+  int rho2_batch_cap = -1;
+  int* d_counter = nullptr;
+  long long* d_batch_stats = nullptr;
+
+  // timing
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t tm0 = nullptr, tm1 = nullptr;
+  bool profile = false;
+  std::vector<cudaEvent_t> scan_events;
+  double last_total_ms = 0.0, last_scan_ms = 0.0;
+  int64_t last_scan_launches = 0;
+  double last_scan_node_samples = 0.0;
+};
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                               \
+      return KRRT_ERR_CUDA;                                                                        \
+    }                                                                                              \
+  } while (0)
+
+#define REQUIRE(cond, code, msg) \
+  do {                           \
+    if (!(cond)) {               \
+      ctx->err = (msg);          \
+      return (code);             \
+    }                            \
+  } while (0)
+
+template <typename Tp>
+static cudaError_t dev_alloc(krrt_ctx* ctx, Tp** p, size_t count) {
+  cudaError_t e = cudaMalloc((void**)p, sizeof(Tp) * std::max<size_t>(count, 1));
+  if (e == cudaSuccess) ctx->allocs.push_back((void*)*p);
+  return e;
+}
+
+static int ensure_scratch(krrt_ctx* ctx, int slot, size_t bytes) {
+  if (ctx->scratch_cap[slot] >= bytes) return KRRT_OK;
+  if (ctx->d_scratch[slot]) CK(cudaFree(ctx->d_scratch[slot]));
+  ctx->d_scratch[slot] = nullptr;
+  ctx->scratch_cap[slot] = 0;
+  size_t want = std::max<size_t>(bytes, 4096);
+  CK(cudaMalloc(&ctx->d_scratch[slot], want));
+  ctx->scratch_cap[slot] = want;
+  return KRRT_OK;
+}
+
+// squared near radius rho(n)^2, rho(n) = min(rho_max, gamma (ln n / n)^(1/4)); 0 for n < 2 (NeighborRadius slot)
+static double near_radius2(const krrt_config& c, int n) {
+  if (n < 2) return 0.0;
+  double q = std::log((double)n) / (double)n;
+  double rho = c.gamma * std::sqrt(std::sqrt(q));
+  if (rho > c.rho_max) rho = c.rho_max;
+  return rho * rho;
+}
+
+extern "C" {
+
+void krrt_default_config(krrt_config* c) {
+  std::memset(c, 0, sizeof(*c));
+  c->device = 0;
+  c->precision = KRRT_F64;
+  c->capacity = 1 << 16;
+  c->S = 10;
+  c->r = 0.5;    // config/config.yaml:1
+  c->R = 1.35;   // config/config.yaml:5
+  c->lo[0] = -9.0; c->hi[0] = 9.0;   // field 18 x 12 m (global_config.yaml:17-18)
+  c->lo[1] = -6.0; c->hi[1] = 6.0;
+  c->lo[2] = -2.0; c->hi[2] = 2.0;
+  c->lo[3] = -2.0; c->hi[3] = 2.0;
+  c->gamma = 7.0;
+  c->rho_max = 4.0;
+  c->p_direct = 0.0;
+  c->goal_tol = 0.0;
+  c->seed = 0;
+  c->query_id = 0;
+  c->batch = 0;
+  c->near_cap = 0;
+}
+
+int krrt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+const char* krrt_last_error(const krrt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int64_t krrt_launch_count(const krrt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+void krrt_destroy(krrt_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->cfg.device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (void* p : ctx->allocs) cudaFree(p);
+  for (void* p : ctx->d_scratch)
+    if (p) cudaFree(p);
+  if (ctx->d_user) cudaFree(ctx->d_user);
+  if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
+  for (cudaEvent_t e : ctx->scan_events) cudaEventDestroy(e);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->tm0) cudaEventDestroy(ctx->tm0);
+  if (ctx->tm1) cudaEventDestroy(ctx->tm1);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+static int create_impl(krrt_ctx* ctx) {
+  const krrt_config& c = ctx->cfg;
+  REQUIRE(c.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED, "only KRRT_F64 is implemented");
+  REQUIRE(c.capacity >= 2 && c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad capacity / S / r / R");
+  REQUIRE(c.batch >= 1 && c.batch <= 256, KRRT_ERR_INVALID, "batch must be in [1,256]");
+  REQUIRE(c.near_cap >= 32 && c.near_cap <= 5632, KRRT_ERR_INVALID, "near_cap must be in [32,5632]");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev) {
+    ctx->err = std::string("no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range") +
+               "); libkrrt has no CPU fallback";
+    return KRRT_ERR_NO_DEVICE;
+  }
+  CK(cudaSetDevice(c.device));
+  CK(cudaGetDeviceProperties(&ctx->prop, c.device));
+  if (ctx->prop.major != 10) {
+    ctx->err = std::string("device ") + ctx->prop.name + " is not sm_100; libkrrt is built for sm_100a only";
+    return KRRT_ERR_NO_DEVICE;
+  }
+  CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&ctx->ev0));
+  CK(cudaEventCreate(&ctx->ev1));
+  CK(cudaEventCreate(&ctx->tm0));
+  CK(cudaEventCreate(&ctx->tm1));
+  const size_t cap = (size_t)c.capacity;
+  CK(dev_alloc(ctx, &ctx->T.pos, cap));
+  CK(dev_alloc(ctx, &ctx->T.vel, cap));
+  CK(dev_alloc(ctx, &ctx->T.ctc, cap));
+  CK(dev_alloc(ctx, &ctx->T.tim, cap));
+  CK(dev_alloc(ctx, &ctx->T.ecost, cap));
+  CK(dev_alloc(ctx, &ctx->T.etime, cap));
+  CK(dev_alloc(ctx, &ctx->T.parent, cap));
+  CK(dev_alloc(ctx, &ctx->T.head, cap));
+  CK(dev_alloc(ctx, &ctx->T.next, cap));
+  CK(dev_alloc(ctx, &ctx->T.prev, cap));
+  CK(dev_alloc(ctx, &ctx->T.queue, cap));
+  ctx->T.cap = c.capacity;
+  CK(dev_alloc(ctx, &ctx->d_rho2, cap + 1));
+  CK(dev_alloc(ctx, &ctx->d_obs, (size_t)KRRT_MAX_OBS));
+  CK(dev_alloc(ctx, &ctx->d_ctl, (size_t)1));
+  CK(dev_alloc(ctx, &ctx->d_counter, (size_t)1));
+  CK(dev_alloc(ctx, &ctx->d_batch_stats, (size_t)10));
+  CK(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_obs, 0, sizeof(double4) * KRRT_MAX_OBS, ctx->stream));
+  {
+    std::vector<double> rho2(cap + 1);
+    for (size_t n = 0; n <= cap; ++n) rho2[n] = near_radius2(c, (int)n);
+    CK(cudaMemcpyAsync(ctx->d_rho2, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  Batch& B = ctx->Bt;
+  B.B = c.batch;
+  B.near_cap = c.near_cap;
+  const size_t bc = (size_t)B.B * B.near_cap;
+  CK(dev_alloc(ctx, &B.samples, (size_t)B.B));
+  CK(dev_alloc(ctx, &B.reject, (size_t)B.B));
+  CK(dev_alloc(ctx, &B.map, (size_t)B.B));
+  CK(dev_alloc(ctx, &B.count, (size_t)B.B));
+  CK(dev_alloc(ctx, &B.ref, bc));
+  CK(dev_alloc(ctx, &B.d2, bc));
+  CK(dev_alloc(ctx, &B.tf, bc));
+  CK(dev_alloc(ctx, &B.cf, bc));
+  CK(dev_alloc(ctx, &B.tb, bc));
+  CK(dev_alloc(ctx, &B.cb, bc));
+  Params& P = ctx->P;
+  P.r = c.r;
+  P.R2 = c.R * c.R;
+  P.S = c.S;
+  P.capacity = c.capacity;
+  for (int k = 0; k < 4; ++k) {
+    P.sp.lo[k] = c.lo[k];
+    P.sp.hi[k] = c.hi[k];
+  }
+  P.sp.p_direct = c.p_direct;
+  P.sp.seed = c.seed;
+  P.query_id = c.query_id;
+  P.m = 0;
+  P.dynamic = 0;
+  P.goal_tol2 = c.goal_tol * c.goal_tol;
+  P.rho2 = ctx->d_rho2;
+  P.obs = ctx->d_obs;
+  const int commit_smem = (int)(sizeof(double4) * KRRT_MAX_OBS + (size_t)B.near_cap * (4 * 8 + 4 + 1) + 16);
+  CK(cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, commit_smem));
+  return KRRT_OK;
+}
+
+int krrt_create(const krrt_config* c, krrt_ctx** out) {
+  if (!c || !out) {
+    g_create_error = "null argument";
+    return KRRT_ERR_INVALID;
+  }
+  *out = nullptr;
+  krrt_ctx* ctx = new krrt_ctx();
+  ctx->cfg = *c;
+  if (ctx->cfg.batch == 0) ctx->cfg.batch = 64;
+  if (ctx->cfg.near_cap == 0) ctx->cfg.near_cap = 1024;
+  int rc = create_impl(ctx);
+  if (rc != KRRT_OK) {
+    g_create_error = ctx->err;
+    krrt_destroy(ctx);
+    return rc;
+  }
+  *out = ctx;
+  return KRRT_OK;
+}
+
+int krrt_timer_begin(krrt_ctx* ctx) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaEventRecord(ctx->tm0, ctx->stream));
+  return KRRT_OK;
+}
+
+int krrt_timer_end(krrt_ctx* ctx, double* ms) {
+  if (!ctx || !ms) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaEventRecord(ctx->tm1, ctx->stream));
+  CK(cudaEventSynchronize(ctx->tm1));
+  float t = 0.f;
+  CK(cudaEventElapsedTime(&t, ctx->tm0, ctx->tm1));
+  *ms = t;
+  return KRRT_OK;
+}
+
+int krrt_set_profile(krrt_ctx* ctx, int on) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  ctx->profile = on != 0;
+  return KRRT_OK;
+}
+
+int krrt_set_obstacles(krrt_ctx* ctx, const double* o, int m, int dynamic) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(m >= 0 && m <= KRRT_MAX_OBS && (m == 0 || o), KRRT_ERR_INVALID, "0 <= m <= KRRT_MAX_OBS");
+  CK(cudaSetDevice(ctx->cfg.device));
+  if (m > 0) {
+    CK(cudaMemcpyAsync(ctx->d_obs, o, sizeof(double) * 4 * m, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));  // the caller's buffer may be reused right after return
+  }
+  ctx->P.m = m;
+  ctx->P.dynamic = dynamic ? 1 : 0;
+  return KRRT_OK;
+}
+
+__global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  T.pos[0] = make_double2(x0.x, x0.y);
+  T.vel[0] = make_double2(x0.vx, x0.vy);
+  T.parent[0] = -1;
+  T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
+  T.head[0] = -1; T.next[0] = -1; T.prev[0] = -1;
+  Ctl z;
+  memset(&z, 0, sizeof(z));
+  z.n = 1;
+  z.goal_index = -1;
+  *ctl = z;
+}
+
+int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
+  if (!ctx || !x0) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  State4 s = {x0[0], x0[1], x0[2], x0[3]};
+  k_set_start<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, ctx->T, s);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  ctx->started = true;
+  ctx->n_upper = 1;
+  return KRRT_OK;
+}
+
+__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  ctl->full = 0;
+  ctl->scan_pairs = 0.0;
+  ctl->scan_nodes = 0.0;
+  ctl->has_goal = has_goal;
+  ctl->goal[0] = g.x; ctl->goal[1] = g.y; ctl->goal[2] = g.vx; ctl->goal[3] = g.vy;
+}
+
+static int fetch_ctl(krrt_ctx* ctx, Ctl* h) {
+  CK(cudaMemcpyAsync(h, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  ctx->n_upper = h->n;
+  return KRRT_OK;
+}
+
+int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
+  REQUIRE(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  if (samples && n_iter > 0) {
+    size_t need = sizeof(double) * 4 * (size_t)n_iter;
+    if (ctx->user_cap < need) {
+      if (ctx->d_user) CK(cudaFree(ctx->d_user));
+      ctx->d_user = nullptr;
+      ctx->user_cap = 0;
+      CK(cudaMalloc((void**)&ctx->d_user, need));
+      ctx->user_cap = need;
+    }
+    CK(cudaMemcpyAsync(ctx->d_user, samples, need, cudaMemcpyHostToDevice, st));
+  }
+  State4 g = {0, 0, 0, 0};
+  if (goal) g = State4{goal[0], goal[1], goal[2], goal[3]};
+  CK(cudaEventRecord(ctx->ev0, st));
+  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g);
+  ctx->launches++;
+  const int B = ctx->Bt.B;
+  const int nbatch = (n_iter + B - 1) / B;
+  if (ctx->profile) {
+    while ((int)ctx->scan_events.size() < 2 * nbatch) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      ctx->scan_events.push_back(e);
+    }
+  }
+  const int commit_smem = (int)(sizeof(double4) * KRRT_MAX_OBS + (size_t)ctx->Bt.near_cap * (4 * 8 + 4 + 1) + 16);
+  const int prep_threads = ((B + 31) / 32) * 32;
+  const int max_ctas = ctx->prop.multiProcessorCount * 8;
+  for (int k = 0; k < nbatch; ++k) {
+    const int off = k * B;
+    const int nb = std::min(B, n_iter - off);
+    k_batch_prepare<<<1, prep_threads, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, nb, samples ? ctx->d_user : nullptr, off);
+    const int n_up = std::min<long long>(ctx->cfg.capacity, (long long)ctx->n_upper);
+    int ctas = (n_up + SCAN_NODES_PER_CTA - 1) / SCAN_NODES_PER_CTA;
+    ctas = std::max(1, std::min(ctas, max_ctas));
+    if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * k], st));
+    k_near_scan<<<ctas, SCAN_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt);
+    if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * k + 1], st));
+    dim3 sg((ctx->Bt.near_cap + STEER_THREADS - 1) / STEER_THREADS, nb);
+    k_steer_pairs<<<sg, STEER_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt, ctx->P.r);
+    k_commit<<<1, 32, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt);
+    ctx->launches += 4;
+    ctx->n_upper = (int)std::min<long long>(ctx->cfg.capacity, (long long)ctx->n_upper + nb);
+  }
+  k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
+  ctx->launches++;
+  CK(cudaEventRecord(ctx->ev1, st));
+  CK(cudaGetLastError());
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->last_total_ms = ms;
+  ctx->last_scan_ms = 0.0;
+  ctx->last_scan_launches = 0;
+  ctx->last_scan_node_samples = h.scan_pairs;
+  if (ctx->profile) {
+    double acc = 0.0;
+    for (int k = 0; k < nbatch; ++k) {
+      float t = 0.f;
+      CK(cudaEventElapsedTime(&t, ctx->scan_events[2 * k], ctx->scan_events[2 * k + 1]));
+      acc += t;
+    }
+    ctx->last_scan_ms = acc;
+    ctx->last_scan_launches = nbatch;
+  }
+  if (h.error) {
+    ctx->err = h.error == KRRT_ERR_NEAR_OVERFLOW ? "near set exceeded near_cap; raise krrt_config.near_cap" : "device error";
+    return h.error;
+  }
+  if (solved) *solved = h.goal_index >= 0;
+  if (goal_index) *goal_index = h.goal_index;
+  return KRRT_OK;
+}
+
+int krrt_tree_size(krrt_ctx* ctx, int* n) {
+  if (!ctx || !n) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  *n = h.n;
+  return KRRT_OK;
+}
+
+int krrt_iteration(krrt_ctx* ctx, int64_t* iter) {
+  if (!ctx || !iter) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  *iter = h.iter;
+  return KRRT_OK;
+}
+
+int krrt_last_sample(krrt_ctx* ctx, double out[4]) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  std::memcpy(out, h.last_sample, sizeof(double) * 4);
+  return KRRT_OK;
+}
+
+int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  std::memcpy(out, h.stats, sizeof(krrt_stats));
+  return KRRT_OK;
+}
+
+int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* scan_launches,
+                     double* scan_node_samples) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  if (total_ms) *total_ms = ctx->last_total_ms;
+  if (scan_ms) *scan_ms = ctx->last_scan_ms;
+  if (scan_launches) *scan_launches = ctx->last_scan_launches;
+  if (scan_node_samples) *scan_node_samples = ctx->last_scan_node_samples;
+  return KRRT_OK;
+}
+
+}  // extern "C"
+
+#include "krrt_capi_ops.inl"

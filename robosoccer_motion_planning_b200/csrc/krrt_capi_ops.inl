@@ -1,0 +1,365 @@
+// krrt_capi_ops.inl — tree read-back, stateless operators and the batched planner entry points of include/krrt.h.
+// Included at the end of krrt_capi.cu (same translation unit, same -fmad=false arithmetic contract).
+
+static int current_size(krrt_ctx* ctx, int* n) {
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  *n = h.n;
+  return KRRT_OK;
+}
+
+extern "C" {
+
+int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0;
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  cudaStream_t st = ctx->stream;
+  if (states) {
+    // interleave (pos, vel) -> n x 4 rows with two strided copies
+    CK(cudaMemcpy2DAsync(states, 32, ctx->T.pos, 16, 16, n, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(states + 2, 32, ctx->T.vel, 16, 16, n, cudaMemcpyDeviceToHost, st));
+  }
+  if (parent) CK(cudaMemcpyAsync(parent, ctx->T.parent, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  if (cost) CK(cudaMemcpyAsync(cost, ctx->T.ctc, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+  if (time) CK(cudaMemcpyAsync(time, ctx->T.tim, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len) {
+  if (!ctx || !len) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  REQUIRE(cap >= 0, KRRT_ERR_INVALID, "cap < 0");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0;
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  REQUIRE(idx >= 0 && idx < n, KRRT_ERR_INVALID, "node index out of range");
+  cudaStream_t st = ctx->stream;
+  const size_t c = (size_t)std::max(cap, 1);
+  if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 4 * c)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sizeof(double) * c)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 2, sizeof(int) * 4)) != KRRT_OK) return rc;
+  double* d_states = (double*)ctx->d_scratch[0];
+  double* d_times = (double*)ctx->d_scratch[1];
+  int* d_len = (int*)ctx->d_scratch[2];
+  k_path_extract<<<1, 32, 0, st>>>(ctx->T, n, idx, d_states, d_times, cap, d_len);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  int h_len = 0;
+  CK(cudaMemcpyAsync(&h_len, d_len, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const int got = std::min(h_len, cap);
+  if (states && got > 0) CK(cudaMemcpyAsync(states, d_states, sizeof(double) * 4 * got, cudaMemcpyDeviceToHost, st));
+  if (times && got > 0) CK(cudaMemcpyAsync(times, d_times, sizeof(double) * got, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  *len = h_len;
+  return KRRT_OK;
+}
+
+int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  std::memset(out, 0, sizeof(*out));
+  int n = 0;
+  CK(cudaSetDevice(ctx->cfg.device));
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  out->solved = solved;
+  out->goal_index = goal_index;
+  out->n_nodes = n;
+  if (!solved) return KRRT_OK;
+  double st4[KRRT_MAX_WAYPOINTS][4];
+  double tm[KRRT_MAX_WAYPOINTS];
+  int len = 0;
+  rc = krrt_path(ctx, goal_index, &st4[0][0], tm, KRRT_MAX_WAYPOINTS, &len);
+  if (rc != KRRT_OK) return rc;
+  out->path_len = len;
+  for (int k = 0; k < std::min(len, (int)KRRT_MAX_WAYPOINTS); ++k) {
+    for (int d = 0; d < 4; ++d) out->waypoints[k][d] = st4[k][d];
+    out->waypoints[k][4] = tm[k];
+  }
+  CK(cudaMemcpyAsync(&out->cost, ctx->T.ctc + goal_index, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(&out->time, ctx->T.tim + goal_index, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return KRRT_OK;
+}
+
+// rows of every edge of a device-resident chain of `len` states
+static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const double* d_t0, int len, double dt,
+                               double* rows, int cap_rows, int* n_rows) {
+  cudaStream_t st = ctx->stream;
+  const int ne = len - 1;
+  if (ne <= 0) {
+    *n_rows = 0;
+    return KRRT_OK;
+  }
+  int rc;
+  if ((rc = ensure_scratch(ctx, 3, sizeof(double) * ne)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 4, sizeof(int) * (2 * ne + 2))) != KRRT_OK) return rc;
+  double* d_tau = (double*)ctx->d_scratch[3];
+  int* d_rows = (int*)ctx->d_scratch[4];
+  int* d_offs = d_rows + ne;
+  k_traj_count<<<(ne + 127) / 128, 128, 0, st>>>(d_states, ne, ctx->cfg.r, dt, d_tau, d_rows);
+  k_traj_offsets<<<1, 32, 0, st>>>(d_rows, ne, d_offs);
+  ctx->launches += 2;
+  int total = 0;
+  CK(cudaMemcpyAsync(&total, d_offs + ne, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  *n_rows = total;
+  const int got = std::min(total, cap_rows);
+  if (!rows || got <= 0) return KRRT_OK;
+  if ((rc = ensure_scratch(ctx, 5, sizeof(double) * 5 * (size_t)got)) != KRRT_OK) return rc;
+  double* d_out = (double*)ctx->d_scratch[5];
+  k_traj_fill<<<ne, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, dt, d_out, got);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(rows, d_out, sizeof(double) * 5 * (size_t)got, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_rows, int* n_rows) {
+  if (!ctx || !n_rows) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0;
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  REQUIRE(idx >= 0 && idx < n, KRRT_ERR_INVALID, "node index out of range");
+  cudaStream_t st = ctx->stream;
+  if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 4 * (size_t)n)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sizeof(double) * (size_t)n)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 2, sizeof(int) * 4)) != KRRT_OK) return rc;
+  double* d_states = (double*)ctx->d_scratch[0];
+  double* d_times = (double*)ctx->d_scratch[1];
+  int* d_len = (int*)ctx->d_scratch[2];
+  k_path_extract<<<1, 32, 0, st>>>(ctx->T, n, idx, d_states, d_times, n, d_len);
+  ctx->launches++;
+  int len = 0;
+  CK(cudaMemcpyAsync(&len, d_len, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return trajectory_of_chain(ctx, d_states, d_times, len, dt, rows, cap_rows, n_rows);
+}
+
+int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
+               int cap_rows, int* n_rows) {
+  if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
+  REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int rc;
+  if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 8)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sizeof(double) * 2)) != KRRT_OK) return rc;
+  double h[8] = {xi[0], xi[1], xi[2], xi[3], xf[0], xf[1], xf[2], xf[3]};
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], &t0, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return trajectory_of_chain(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], 2, dt, rows,
+                             cap_rows, n_rows);
+}
+
+int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, double* t, double* c) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(n >= 0 && (n == 0 || (xi && xf && t && c)), KRRT_ERR_INVALID, "null buffer");
+  if (n == 0) return KRRT_OK;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t sb = sizeof(double) * 4 * (size_t)n, ob = sizeof(double) * (size_t)n;
+  if ((rc = ensure_scratch(ctx, 0, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 3, ob)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 5, ob)) != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], xi, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], xf, sb, cudaMemcpyHostToDevice, st));
+  k_steer_batch<<<(n + 127) / 128, 128, 0, st>>>((const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], n,
+                                                 ctx->cfg.r, (double*)ctx->d_scratch[3], (double*)ctx->d_scratch[5]);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(t, ctx->d_scratch[3], ob, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(c, ctx->d_scratch[5], ob, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const double* tau, const double* t0, int n,
+                      unsigned char* hit) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(n >= 0 && (n == 0 || (xi && xf && tau && t0 && hit)), KRRT_ERR_INVALID, "null buffer");
+  if (n == 0) return KRRT_OK;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t sb = sizeof(double) * 4 * (size_t)n, ob = sizeof(double) * (size_t)n;
+  if ((rc = ensure_scratch(ctx, 0, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 3, ob)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 5, ob)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 6, (size_t)n)) != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], xi, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], xf, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[3], tau, ob, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[5], t0, ob, cudaMemcpyHostToDevice, st));
+  const long long threads = (long long)n * 32;
+  k_edge_collide_batch<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(
+      (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], (const double*)ctx->d_scratch[3],
+      (const double*)ctx->d_scratch[5], n, ctx->d_obs, ctx->P.m, ctx->P.dynamic, ctx->P.R2, ctx->P.S,
+      (unsigned char*)ctx->d_scratch[6]);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(hit, ctx->d_scratch[6], (size_t)n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, int cap, int* count, int32_t* nearest,
+              double* nearest_d2) {
+  if (!ctx || !x) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  REQUIRE(cap >= 0 && (cap == 0 || idx), KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0;
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  cudaStream_t st = ctx->stream;
+  if ((rc = ensure_scratch(ctx, 4, sizeof(int) * (size_t)std::max(cap, 1))) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 2, 32)) != KRRT_OK) return rc;
+  int* d_idx = (int*)ctx->d_scratch[4];
+  int* d_cnt = (int*)ctx->d_scratch[2];
+  int* d_nearest = d_cnt + 1;
+  double* d_nd2 = (double*)(d_cnt + 2);
+  State4 s = {x[0], x[1], x[2], x[3]};
+  k_near_query<<<1, 1024, 0, st>>>(ctx->T, n, s, radius2, d_idx, cap, d_cnt, d_nearest, d_nd2);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  struct { int cnt, nearest; double nd2; } h;
+  CK(cudaMemcpyAsync(&h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const int got = std::min(h.cnt, cap);
+  if (got > 0) CK(cudaMemcpyAsync(idx, d_idx, sizeof(int) * got, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (count) *count = h.cnt;
+  if (nearest) *nearest = h.nearest;
+  if (nearest_d2) *nearest_d2 = h.nd2;
+  return KRRT_OK;
+}
+
+// ---- batched independent queries ---------------------------------------------------------------------
+static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double* d_goals, const double* d_obs, int q,
+                             int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* d_out,
+                             cudaStream_t st) {
+  const krrt_config& c = ctx->cfg;
+  const int cap = std::min(c.capacity, n_iter + 2);
+  REQUIRE(cap >= 2, KRRT_ERR_INVALID, "n_iter / capacity too small");
+  if (ctx->rho2_batch_cap != cap) {
+    if (ctx->d_rho2_batch) CK(cudaFree(ctx->d_rho2_batch));
+    ctx->d_rho2_batch = nullptr;
+    ctx->rho2_batch_cap = -1;
+    CK(cudaMalloc((void**)&ctx->d_rho2_batch, sizeof(double) * (cap + 1)));
+    std::vector<double> rho2(cap + 1);
+    for (int n = 0; n <= cap; ++n) rho2[n] = near_radius2(c, n);
+    CK(cudaMemcpy(ctx->d_rho2_batch, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice));
+    ctx->rho2_batch_cap = cap;
+  }
+  const size_t pw = batch_warp_smem_bytes(cap, m);
+  const size_t smem_max = ctx->prop.sharedMemPerBlockOptin;            // 227 KB on sm_100
+  const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
+  REQUIRE(pw <= smem_max, KRRT_ERR_UNSUPPORTED,
+          "n_iter too large for the shared-memory batched planner; use krrt_grow per query");
+  int best_w = 1, best_total = 0, best_ctas = 1;
+  for (int w = 1; w <= 8; ++w) {
+    size_t per_cta = (size_t)w * pw;
+    if (per_cta > smem_max) break;
+    int ctas = (int)(smem_sm / (per_cta + 1024));
+    ctas = std::min(ctas, 32);
+    if (ctas < 1) continue;
+    if (w * ctas >= best_total) {
+      best_total = w * ctas;
+      best_w = w;
+      best_ctas = ctas;
+    }
+  }
+  const size_t smem = (size_t)best_w * pw;
+  CK(cudaFuncSetAttribute(k_plan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  BatchJob J;
+  J.starts = d_starts; J.goals = d_goals; J.obstacles = d_obs;
+  J.out = reinterpret_cast<ResultRec*>(d_out);
+  J.next_query = ctx->d_counter;
+  J.stats = ctx->d_batch_stats;
+  J.rho2 = ctx->d_rho2_batch;
+  J.q = q; J.m = m; J.dynamic = dynamic ? 1 : 0; J.n_iter = n_iter; J.cap = cap;
+  J.query_base = query_base;
+  J.r = c.r; J.R2 = c.R * c.R; J.goal_tol2 = c.goal_tol * c.goal_tol; J.S = c.S;
+  for (int k = 0; k < 4; ++k) { J.sp.lo[k] = c.lo[k]; J.sp.hi[k] = c.hi[k]; }
+  J.sp.p_direct = c.p_direct;
+  J.sp.seed = c.seed;
+  CK(cudaMemsetAsync(ctx->d_counter, 0, sizeof(int), st));
+  CK(cudaMemsetAsync(ctx->d_batch_stats, 0, sizeof(long long) * 10, st));
+  long long warps_needed = q;
+  int grid = ctx->prop.multiProcessorCount * best_ctas;
+  grid = (int)std::max<long long>(1, std::min<long long>(grid, (warps_needed + best_w - 1) / best_w));
+  k_plan_batch<<<grid, best_w * 32, smem, st>>>(J);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return KRRT_OK;
+}
+
+int krrt_plan_batch_device(krrt_ctx* ctx, const double* d_starts, const double* d_goals, const double* d_obstacles,
+                           int q, int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* d_out,
+                           void* cuda_stream) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(q >= 0 && m >= 0 && m <= KRRT_MAX_OBS && n_iter >= 0, KRRT_ERR_INVALID, "bad q / m / n_iter");
+  if (q == 0) return KRRT_OK;
+  REQUIRE(d_starts && d_goals && d_out && (m == 0 || d_obstacles), KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+  return launch_plan_batch(ctx, d_starts, d_goals, d_obstacles, q, m, dynamic, n_iter, query_base, d_out, st);
+}
+
+int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, const double* obstacles, int q, int m,
+                    int dynamic, int n_iter, uint32_t query_base, krrt_result* out) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(q >= 0 && m >= 0 && m <= KRRT_MAX_OBS && n_iter >= 0, KRRT_ERR_INVALID, "bad q / m / n_iter");
+  if (q == 0) return KRRT_OK;
+  REQUIRE(starts && goals && out && (m == 0 || obstacles), KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t sb = sizeof(double) * 4 * (size_t)q, ob = sizeof(double) * 4 * (size_t)q * std::max(m, 1);
+  const size_t rb = sizeof(krrt_result) * (size_t)q;
+  if ((rc = ensure_scratch(ctx, 0, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 6, ob)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 7, rb)) != KRRT_OK) return rc;
+  CK(cudaEventRecord(ctx->ev0, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], starts, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], goals, sb, cudaMemcpyHostToDevice, st));
+  if (m > 0) CK(cudaMemcpyAsync(ctx->d_scratch[6], obstacles, sizeof(double) * 4 * (size_t)q * m, cudaMemcpyHostToDevice, st));
+  rc = launch_plan_batch(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1],
+                         (const double*)ctx->d_scratch[6], q, m, dynamic, n_iter, query_base,
+                         (krrt_result*)ctx->d_scratch[7], st);
+  if (rc != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(out, ctx->d_scratch[7], rb, cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(ctx->ev1, st));
+  CK(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->last_total_ms = ms;
+  return KRRT_OK;
+}
+
+int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaMemcpyAsync(out, ctx->d_batch_stats, sizeof(krrt_stats), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return KRRT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+// krrt_ops.cuh — stateless batched operators behind krrt_steer_cost / krrt_edge_collide / krrt_near /
+// krrt_solve / krrt_trajectory (the Cost, Environment, Tree-query and Connector slots called on their own:
+// robosoccer_motion_planning_node.cpp:242-245, robosoccer_visual.hpp:35).
+#pragma once
+#include "krrt_warp.cuh"
+
+namespace krrt {
+
+__global__ void __launch_bounds__(128) k_steer_batch(const double* __restrict__ xi, const double* __restrict__ xf,
+                                                       int n, double r, double* __restrict__ t,
+                                                       double* __restrict__ c) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double4 a = reinterpret_cast<const double4*>(xi)[i];
+  const double4 b = reinterpret_cast<const double4*>(xf)[i];
+  State4 x0 = {a.x, a.y, a.z, a.w}, x1 = {b.x, b.y, b.z, b.w};
+  double tau, cost;
+  steer(x0, x1, r, tau, cost);
+  t[i] = tau;
+  c[i] = cost;
+}
+
+// one warp per edge: S x m disc tests over the lanes
+__global__ void __launch_bounds__(128) k_edge_collide_batch(const double* __restrict__ xi,
+                                                              const double* __restrict__ xf,
+                                                              const double* __restrict__ tau,
+                                                              const double* __restrict__ t0, int n,
+                                                              const double4* __restrict__ obs, int m, int dynamic,
+                                                              double R2, int S, unsigned char* __restrict__ hit) {
+  __shared__ double4 s_obs[KRRT_MAX_OBS_DEV];
+  for (int j = threadIdx.x; j < m; j += blockDim.x) s_obs[j] = obs[j];
+  __syncthreads();
+  int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (e >= n) return;
+  const double4 a = reinterpret_cast<const double4*>(xi)[e];
+  const double4 b = reinterpret_cast<const double4*>(xf)[e];
+  State4 x0 = {a.x, a.y, a.z, a.w}, x1 = {b.x, b.y, b.z, b.w};
+  EnvView E = {s_obs, m, dynamic, R2, S};
+  bool h = warp_edge_collide(x0, x1, tau[e], t0[e], E);
+  if (lane_id() == 0) hit[e] = h ? 1 : 0;
+}
+
+// radius + nearest query of one state against the tree; ascending indices (single CTA, ordered compaction)
+__global__ void __launch_bounds__(1024) k_near_query(TreeView T, int n, State4 x, double radius2, int* out_idx,
+                                                      int cap, int* out_count, int* out_nearest,
+                                                      double* out_nearest_d2) {
+  __shared__ int s_cnt[32];
+  __shared__ double s_d[32];
+  __shared__ int s_i[32];
+  __shared__ int s_total;
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_total = 0;
+  __syncthreads();
+  double bd = INFINITY;
+  int bi = -1, aux = 0;
+  for (int base = 0; base < n; base += 1024) {
+    int i = base + threadIdx.x;
+    bool valid = false;
+    if (i < n) {
+      double d = dist2(load_state(T, i), x);
+      if (bi < 0 || d < bd) {
+        bd = d;
+        bi = i;
+      }
+      valid = d <= radius2;
+    }
+    unsigned mk = __ballot_sync(FULL, valid);
+    if (lane == 0) s_cnt[warp] = __popc(mk);
+    __syncthreads();
+    int off = s_total;
+    for (int w = 0; w < warp; ++w) off += s_cnt[w];
+    if (valid) {
+      int k = off + __popc(mk & ((1u << lane) - 1));
+      if (k < cap) out_idx[k] = i;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+      for (int w = 0; w < 32; ++w) tot += s_cnt[w];
+      s_total += tot;
+    }
+    __syncthreads();
+  }
+  warp_argmin(bd, bi, aux);
+  if (lane == 0) {
+    s_d[warp] = bd;
+    s_i[warp] = bi;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    bd = s_d[threadIdx.x];
+    bi = s_i[threadIdx.x];
+    warp_argmin(bd, bi, aux);
+    if (threadIdx.x == 0) {
+      *out_count = s_total;
+      *out_nearest = bi;
+      *out_nearest_d2 = bd;
+    }
+  }
+}
+
+// root -> idx chain (tree.states(idx), …node.cpp:237): states (len x 4) and arrival times, root first
+__global__ void k_path_extract(TreeView T, int n, int idx, double* states, double* times, int cap, int* out_len) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (idx < 0 || idx >= n) {
+    *out_len = 0;
+    return;
+  }
+  int len = 0;
+  for (int i = idx; i >= 0 && len < n; i = T.parent[i]) ++len;
+  int p = len - 1;
+  for (int i = idx; i >= 0 && p >= 0; i = T.parent[i], --p) {
+    if (p < cap) {
+      double2 a = T.pos[i], v = T.vel[i];
+      states[4 * p + 0] = a.x; states[4 * p + 1] = a.y; states[4 * p + 2] = v.x; states[4 * p + 3] = v.y;
+      times[p] = T.tim[i];
+    }
+  }
+  *out_len = len;
+}
+
+// rows of solver.solve(xi, xf, dt): t = 0, dt, 2dt, ... < tau, then tau.  last = index of the closing row.
+__device__ __forceinline__ int solve_last_row(double tau, double dt) {
+  int k = (int)floor(tau / dt);
+  if (k < 0) k = 0;
+  while ((double)k * dt < tau) ++k;
+  while (k > 0 && !((double)(k - 1) * dt < tau)) --k;
+  return k;
+}
+
+// per path edge e (states[e] -> states[e+1]): tau* and row count
+__global__ void k_traj_count(const double* __restrict__ states, int n_edges, double r, double dt, double* tau,
+                             int* rows) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  const double4 a = reinterpret_cast<const double4*>(states)[e];
+  const double4 b = reinterpret_cast<const double4*>(states)[e + 1];
+  State4 x0 = {a.x, a.y, a.z, a.w}, x1 = {b.x, b.y, b.z, b.w};
+  double t, c;
+  steer(x0, x1, r, t, c);
+  tau[e] = t;
+  rows[e] = solve_last_row(t, dt) + 1;
+}
+
+// exclusive prefix of rows (few edges: one thread), total in offs[n_edges]
+__global__ void k_traj_offsets(const int* rows, int n_edges, int* offs) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  int acc = 0;
+  for (int e = 0; e < n_edges; ++e) {
+    offs[e] = acc;
+    acc += rows[e];
+  }
+  offs[n_edges] = acc;
+}
+
+// one CTA per edge: rows (x, y, vx, vy, t0 + t)
+__global__ void __launch_bounds__(128) k_traj_fill(const double* __restrict__ states, const double* __restrict__ t0s,
+                                                     const double* __restrict__ tau, const int* __restrict__ offs,
+                                                     double dt, double* out, int cap_rows) {
+  const int e = blockIdx.x;
+  const double4 a = reinterpret_cast<const double4*>(states)[e];
+  const double4 b = reinterpret_cast<const double4*>(states)[e + 1];
+  State4 x0 = {a.x, a.y, a.z, a.w}, x1 = {b.x, b.y, b.z, b.w};
+  const double T = tau[e], t0 = t0s[e];
+  const int o = offs[e], cnt = offs[e + 1] - o;
+  Edge ed = make_edge(x0, x1, T, t0);
+  for (int k = threadIdx.x; k < cnt; k += blockDim.x) {
+    if (o + k >= cap_rows) break;
+    double t = (k == cnt - 1) ? T : (double)k * dt;
+    double h = (T == 0.0) ? 0.0 : t / T;
+    double* row = out + 5 * (size_t)(o + k);
+    row[0] = axis_pos(ed.kx, h);
+    row[1] = axis_pos(ed.ky, h);
+    row[2] = axis_vel(ed.kx, h, x0.vx, T);
+    row[3] = axis_vel(ed.ky, h, x0.vy, T);
+    row[4] = t0 + t;
+  }
+}
+
+}  // namespace krrt

@@ -270,7 +270,8 @@ def plan_batch(cfg, starts, goals, obstacles, dynamic, n_iter, query_base=0, nth
     starts = np.ascontiguousarray(starts, dtype=np.float64).reshape(-1, 4)
     goals = np.ascontiguousarray(goals, dtype=np.float64).reshape(-1, 4)
     q = starts.shape[0]
-    obstacles = np.ascontiguousarray(obstacles, dtype=np.float64).reshape(q, -1, 4)
+    obstacles = np.ascontiguousarray(obstacles, dtype=np.float64)
+    obstacles = obstacles.reshape(q, -1, 4) if obstacles.size else np.zeros((q, 0, 4))
     m = obstacles.shape[1]
     out = np.zeros(q, dtype=RESULT_DTYPE)
     lib().ko_plan_batch(ctypes.byref(cfg), _d(starts), _d(goals), _d(obstacles), q, m, int(dynamic), int(n_iter),

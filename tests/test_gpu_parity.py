@@ -1,0 +1,303 @@
+"""GPU parity tests proper: libkrrt.so (through its C ABI) against the CPU oracle on the same seeded inputs.
+
+Bar: bit-exact — states, parents, costs, arrival times, indices, counters (fp64 mode computes with the same
+IEEE operations in the same order as the oracle, so `==` is the tolerance).  north_star would allow 1e-6
+relative on costs/times and ties within 1e-9; we do not need the allowance.
+"""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+from robosoccer_motion_planning_b200 import capi, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def rand_states(rng, n):
+    return rng.uniform(scenes.FIELD_LO, scenes.FIELD_HI, (n, 4))
+
+
+def make_pair(gpu_required, dynamic, p_direct=0.0, capacity=1 << 15, batch=0, near_cap=0, seed=0, query_id=0, **kw):
+    common = dict(capacity=capacity, p_direct=p_direct, seed=seed, query_id=query_id, **kw)
+    G = capi.Planner(batch=batch, near_cap=near_cap, **common)
+    O = ob.OraclePlanner(**common)
+    obs = scenes.dynamic_obstacles() if dynamic else scenes.static_obstacles()
+    for P in (G, O):
+        P.set_obstacles(obs, dynamic)
+        P.set_start(scenes.START)
+    return G, O
+
+
+def assert_same_tree(G, O):
+    gs, gp, gc, gt = G.tree()
+    os_, op, oc, ot = O.tree()
+    assert G.size == O.size
+    assert np.array_equal(gp, op), f"parents differ at {np.nonzero(gp != op)[0][:10]}"
+    assert np.array_equal(gs, os_)
+    assert np.array_equal(gc, oc), f"cost-to-come differs at {np.nonzero(gc != oc)[0][:10]}"
+    assert np.array_equal(gt, ot)
+    assert G.iteration == O.iteration
+    assert G.stats() == O.stats()
+
+
+def test_steer_cost_bit_exact(gpu_required):
+    rng = np.random.default_rng(0)
+    n = 200_000
+    a, b = rand_states(rng, n), rand_states(rng, n)
+    b[::7, :2] = a[::7, :2] + 1e-3 * rng.uniform(-1, 1, (len(a[::7]), 2))   # near-coincident
+    a[::11, 2:] = 0.0; b[::11, 2:] = 0.0                                     # rest to rest
+    b[::13, :2] = a[::13, :2]                                                # same position
+    a[::17, 2:] *= 4; b[::17, 2:] *= 4                                       # multi-root zone (fast, close)
+    b[::17, :2] = a[::17, :2] + 0.3 * rng.uniform(-1, 1, (len(a[::17]), 2))
+    G = capi.Planner(capacity=16)
+    t, c = G.steer_cost(a, b)
+    to, co = ob.steer(a, b, 0.5)
+    assert np.array_equal(t, to) and np.array_equal(c, co)
+    # empty and single-element inputs
+    t0, c0 = G.steer_cost(np.zeros((0, 4)), np.zeros((0, 4)))
+    assert t0.shape == (0,) and c0.shape == (0,)
+    t1, c1 = G.steer_cost(a[:1], b[:1])
+    assert t1[0] == to[0] and c1[0] == co[0]
+
+
+def test_steer_cost_other_weight(gpu_required):
+    rng = np.random.default_rng(5)
+    a, b = rand_states(rng, 5000), rand_states(rng, 5000)
+    for r in (0.05, 1.0, 7.5):
+        G = capi.Planner(capacity=16, r=r)
+        t, c = G.steer_cost(a, b)
+        to, co = ob.steer(a, b, r)
+        assert np.array_equal(t, to) and np.array_equal(c, co)
+
+
+@pytest.mark.parametrize("dynamic", [0, 1])
+def test_edge_collide_bit_exact(gpu_required, dynamic):
+    rng = np.random.default_rng(1)
+    n = 20_000
+    a, b = rand_states(rng, n), rand_states(rng, n)
+    tau, _ = ob.steer(a, b, 0.5)
+    t0 = rng.uniform(0, 10, n)
+    obs = scenes.dynamic_obstacles(3)
+    G = capi.Planner(capacity=16)
+    G.set_obstacles(obs, dynamic)
+    hit = G.edge_collide(a, b, tau, t0)
+    ref = np.array([ob.edge_collide(a[i], b[i], tau[i], t0[i], obs, dynamic) for i in range(n)], dtype=np.uint8)
+    assert np.array_equal(hit, ref)
+    assert 0 < hit.sum() < n
+    # no obstacles -> never hits
+    G.set_obstacles(np.zeros((0, 4)), dynamic)
+    assert G.edge_collide(a[:100], b[:100], tau[:100], t0[:100]).sum() == 0
+
+
+def test_solve_rows_bit_exact(gpu_required):
+    rng = np.random.default_rng(2)
+    G = capi.Planner(capacity=16)
+    for k in range(40):
+        a, b = rand_states(rng, 1)[0], rand_states(rng, 1)[0]
+        dt = [0.1, 0.05, 0.37, 5.0][k % 4]
+        rows = G.solve(a, b, dt=dt, t0=1.25)
+        ref = ob.solve(a, b, 0.5, dt, 1.25)
+        assert rows.shape == ref.shape
+        assert np.array_equal(rows, ref)
+    # degenerate: identical states -> a single row
+    rows = G.solve(a, a, dt=0.1)
+    ref = ob.solve(a, a, 0.5, 0.1, 0.0)
+    assert rows.shape == ref.shape == (1, 5) and np.array_equal(rows, ref)
+
+
+@pytest.mark.parametrize("batch", [1, 5, 64, 256])
+def test_grow_static_c1(gpu_required, batch):
+    G, O = make_pair(gpu_required, dynamic=0, batch=batch)
+    for P in (G, O):
+        P.grow(scenes.GOAL, 3000)
+    assert_same_tree(G, O)
+    assert O.check_invariants() == 0
+    assert O.stats()["fail_reject"] > 0 and O.stats()["rewired"] > 0
+
+
+@pytest.mark.parametrize("batch", [1, 64])
+def test_grow_dynamic_c2(gpu_required, batch):
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, batch=batch)
+    rg = G.grow(scenes.GOAL, 5000)
+    ro = O.grow(scenes.GOAL, 5000)
+    assert rg == ro and ro[0]
+    assert_same_tree(G, O)
+    assert O.stats()["fail_dup"] > 0
+    a = G.result(*rg)
+    b = O.result(*ro)
+    for f in a.dtype.names:
+        assert np.array_equal(a[f], b[f]), f
+    assert np.array_equal(G.last_sample(), O.last_sample())
+
+
+def test_grow_full_c2_20k(gpu_required):
+    """BASELINE config 2 at full size: 9 moving opponents, p_direct 0.1, 20k iterations."""
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, capacity=20002)
+    rg = G.grow(scenes.GOAL, 20000)
+    ro = O.grow(scenes.GOAL, 20000)
+    assert rg == ro
+    assert_same_tree(G, O)
+    ps, pt = G.path(rg[1])
+    qs, qt = O.path(ro[1])
+    assert np.array_equal(ps, qs) and np.array_equal(pt, qt)
+
+
+def test_grow_incremental_calls_match_single_call(gpu_required):
+    """The reference calls grow(xg) once per iteration (…node.cpp:176-177)."""
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1)
+    for _ in range(150):
+        G.grow(scenes.GOAL, 1)
+    G.grow(scenes.GOAL, 77)
+    O.grow(scenes.GOAL, 227)
+    assert_same_tree(G, O)
+
+
+def test_grow_explicit_samples_and_nan_rows(gpu_required):
+    """sampler.set_next_sample(x) (…node.cpp:183-184): forced samples, NaN rows fall back to Philox."""
+    rng = np.random.default_rng(3)
+    n = 500
+    samples = rand_states(rng, n)
+    samples[::3, 0] = np.nan
+    samples[250] = scenes.GOAL
+    samples[498] = scenes.GOAL          # second visit of the goal state: duplicate -> failed iteration
+    samples[10] = samples[9]            # duplicate inside one batch
+    G, O = make_pair(gpu_required, dynamic=1, batch=64)
+    rg = G.grow(scenes.GOAL, n, samples)
+    ro = O.grow(scenes.GOAL, n, samples)
+    assert rg == ro and ro[0]
+    assert_same_tree(G, O)
+    assert O.stats()["fail_dup"] >= 2
+
+
+def test_grow_no_goal_no_obstacles(gpu_required):
+    G = capi.Planner(capacity=4096)
+    O = ob.OraclePlanner(capacity=4096)
+    for P in (G, O):
+        P.set_obstacles(np.zeros((0, 4)), 0)
+        P.set_start(scenes.START)
+    rg = G.grow(None, 2000)
+    ro = O.grow(None, 2000)
+    assert rg == ro == (False, -1)
+    assert_same_tree(G, O)
+
+
+def test_capacity_full(gpu_required):
+    G, O = make_pair(gpu_required, dynamic=1, capacity=300, batch=64)
+    for P in (G, O):
+        P.grow(scenes.GOAL, 500)
+        P.grow(scenes.GOAL, 3)
+    assert G.size == O.size == 300
+    assert_same_tree(G, O)
+
+
+def test_restart_reuses_context(gpu_required):
+    """set_start + setIteration(0) every planning cycle (…node.cpp:118-137)."""
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1)
+    for P in (G, O):
+        P.grow(scenes.GOAL, 300)
+        P.set_obstacles(scenes.dynamic_obstacles(9), 1)
+        P.set_start([0.0, 1.0, 0.5, -0.5])
+        P.grow([3.0, -2.0, 0.0, 0.0], 400)
+    assert_same_tree(G, O)
+
+
+def test_near_overflow_is_loud(gpu_required):
+    G = capi.Planner(capacity=4096, near_cap=32, gamma=50.0, rho_max=50.0)
+    G.set_obstacles(np.zeros((0, 4)), 0)
+    G.set_start(scenes.START)
+    with pytest.raises(capi.KrrtError) as e:
+        G.grow(None, 500)
+    assert e.value.code == capi.KRRT_ERR_NEAR_OVERFLOW
+
+
+def test_near_query(gpu_required):
+    G, O = make_pair(gpu_required, dynamic=0)
+    for P in (G, O):
+        P.grow(None, 4000)
+    rng = np.random.default_rng(4)
+    for k in range(20):
+        x = rand_states(rng, 1)[0]
+        r2 = [0.0, 0.3, 1.0, 9.0, 400.0][k % 5]
+        gi, gn, gd = G.near(x, r2, cap=8192)
+        oi, on, od = O.near(x, r2, cap=8192)
+        assert np.array_equal(gi, oi) and gn == on and gd == od
+    # a tree node itself: distance 0, radius 0 -> exactly that node
+    s = O.tree()[0][123]
+    gi, gn, gd = G.near(s, 0.0)
+    assert list(gi) == [123] and gn == 123 and gd == 0.0
+
+
+def test_trajectory_of_path(gpu_required):
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1)
+    rg = G.grow(scenes.GOAL, 3000)
+    ro = O.grow(scenes.GOAL, 3000)
+    assert rg == ro and rg[0]
+    st, tm = O.path(ro[1])
+    ref = np.concatenate([ob.solve(st[k], st[k + 1], 0.5, 0.1, tm[k]) for k in range(len(st) - 1)])
+    rows = G.trajectory(rg[1], 0.1)
+    assert rows.shape == ref.shape and np.array_equal(rows, ref)
+    # arrival time of the last row == arrival time of the goal node; last row == goal state (1e-9)
+    assert abs(rows[-1, 4] - tm[-1]) <= 1e-9 * max(1.0, tm[-1])
+    assert np.allclose(rows[-1, :4], st[-1], atol=1e-9)
+
+
+@pytest.mark.parametrize("dynamic,n_iter,q", [(1, 200, 300), (0, 75, 200), (1, 1, 40), (1, 0, 8)])
+def test_plan_batch(gpu_required, dynamic, n_iter, q):
+    starts, goals, obs = scenes.batch_queries(q, 9, seed=11)
+    cfg_kw = dict(p_direct=0.1, seed=5)
+    G = capi.Planner(capacity=1 << 12, **cfg_kw)
+    out = G.plan_batch(starts, goals, obs, dynamic, n_iter, query_base=1000)
+    ref = ob.plan_batch(ob.default_config(capacity=1 << 12, **cfg_kw), starts, goals, obs, dynamic, n_iter,
+                        query_base=1000, nthreads=8)
+    for f in out.dtype.names:
+        assert np.array_equal(out[f], ref[f]), f
+    if n_iter >= 75:
+        assert out["solved"].sum() > 0
+
+
+def test_plan_batch_no_obstacles_and_stats(gpu_required):
+    q, n_iter = 64, 120
+    starts, goals, _ = scenes.batch_queries(q, 1, seed=2)
+    obs = np.zeros((q, 0, 4))
+    G = capi.Planner(p_direct=0.25)
+    out = G.plan_batch(starts, goals, obs, 1, n_iter)
+    cfg = ob.default_config(p_direct=0.25)
+    ref = ob.plan_batch(cfg, starts, goals, obs, 1, n_iter, nthreads=4)
+    for f in out.dtype.names:
+        assert np.array_equal(out[f], ref[f]), f
+    # counters: sum over per-query oracle planners
+    tot = None
+    for i in range(q):
+        P = ob.OraclePlanner(p_direct=0.25, capacity=n_iter + 2, query_id=i)
+        P.set_obstacles(np.zeros((0, 4)), 1)
+        P.set_start(starts[i])
+        P.grow(goals[i], n_iter)
+        s = P.stats()
+        tot = s if tot is None else {k: tot[k] + s[k] for k in s}
+    assert G.batch_stats() == tot
+
+
+def test_large_tree_100k_properties_and_parity(gpu_required):
+    """BASELINE config 3 (single large tree, 100k iterations): size-independent invariants on the GPU tree,
+    then full bit parity (the oracle's kd-tree finishes this in a few seconds)."""
+    n_iter = 100_000
+    G, O = make_pair(gpu_required, dynamic=0, capacity=n_iter + 2)
+    G.grow(None, n_iter)
+    st, par, ctc, tim = G.tree()
+    n = len(par)
+    assert par[0] == -1 and ctc[0] == 0.0 and tim[0] == 0.0
+    assert np.all((par[1:] >= 0) & (par[1:] < n))
+    # cost / time telescoping with edge costs recomputed by the GPU steering operator
+    et, ec = G.steer_cost(st[par[1:]], st[1:])
+    assert np.array_equal(ctc[1:], ctc[par[1:]] + ec)
+    assert np.array_equal(tim[1:], tim[par[1:]] + et)
+    # acyclic: repeated parent jumps reach the root
+    cur = np.arange(n)
+    for _ in range(4096):
+        cur = np.where(cur > 0, par[np.maximum(cur, 0)], cur)
+        cur = np.maximum(cur, 0)
+        if not cur.any():
+            break
+    assert not cur.any()
+    O.grow(None, n_iter)
+    assert_same_tree(G, O)
