@@ -99,9 +99,14 @@ def test_solve_rows_bit_exact(gpu_required):
         ref = ob.solve(a, b, 0.5, dt, 1.25)
         assert rows.shape == ref.shape
         assert np.array_equal(rows, ref)
-    # degenerate: identical states -> a single row
+    # identical states with a velocity: a genuine loop of duration sqrt(12 r |v|^2)
     rows = G.solve(a, a, dt=0.1)
     ref = ob.solve(a, a, 0.5, 0.1, 0.0)
+    assert rows.shape == ref.shape and rows.shape[0] > 1 and np.array_equal(rows, ref)
+    # degenerate: identical states at rest -> tau = 0, a single row
+    z = np.array([a[0], a[1], 0.0, 0.0])
+    rows = G.solve(z, z, dt=0.1)
+    ref = ob.solve(z, z, 0.5, 0.1, 0.0)
     assert rows.shape == ref.shape == (1, 5) and np.array_equal(rows, ref)
 
 
@@ -160,7 +165,7 @@ def test_grow_explicit_samples_and_nan_rows(gpu_required):
     samples[::3, 0] = np.nan
     samples[250] = scenes.GOAL
     samples[498] = scenes.GOAL          # second visit of the goal state: duplicate -> failed iteration
-    samples[10] = samples[9]            # duplicate inside one batch
+    samples[11] = samples[10]           # duplicate inside one batch (rows 10, 11 are not NaN rows)
     G, O = make_pair(gpu_required, dynamic=1, batch=64)
     rg = G.grow(scenes.GOAL, n, samples)
     ro = O.grow(scenes.GOAL, n, samples)
