@@ -89,6 +89,10 @@ typedef struct krrt_ctx krrt_ctx;
 void krrt_default_config(krrt_config* c);
 int krrt_create(const krrt_config* c, krrt_ctx** out);
 void krrt_destroy(krrt_ctx* ctx);
+/* change the planner parameters of a live context (solver.set_weight, env.collision_radius, sampler and radius
+ * settings: …node.cpp:84-92,225-226).  device / precision / capacity / batch / near_cap must equal the
+ * create-time values (else KRRT_ERR_INVALID: create a new context).  The tree is left as it is.            */
+int krrt_set_params(krrt_ctx* ctx, const krrt_config* cfg);
 const char* krrt_last_error(const krrt_ctx* ctx); /* ctx may be NULL: last create error */
 int krrt_device_count(void);
 
@@ -104,6 +108,9 @@ int krrt_last_sample(krrt_ctx* ctx, double out[4]);
 int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out);
 /* any of the output pointers may be NULL.  states: n x 4, parent: n, cost/time: n              */
 int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time);
+/* tree.trajectories (robosoccer_visual.hpp:18): for every node i the stored edge parent[i] -> i as S rows
+ * (x,y,vx,vy,t), h = k/(S-1); node 0 gives S copies of the root.  rows: cap_nodes x S x 5 doubles         */
+int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes);
 /* root -> idx chain; states cap x 4, times cap; *len = true chain length                        */
 int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len);
 int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out);
@@ -114,6 +121,9 @@ int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_row
 int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, double* t, double* c);
 int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                int cap_rows, int* n_rows);
+/* Connector slot on its own: the optimal edge of each of n pairs as S rows (x,y,vx,vy,t0+t); rows: n x S x 5 */
+int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const double* t0, int n, int S,
+                      double* rows);
 int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const double* tau, const double* t0,
                       int n, unsigned char* hit);
 /* radius query on the current tree: ascending indices, *count = true count, nearest = lowest index on ties */

@@ -29,7 +29,7 @@ EXPORTS = (
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
-    "krrt_timer_end",
+    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples",
 )
 
 
@@ -114,6 +114,9 @@ def lib():
     L.krrt_plan_batch_device.argtypes = [P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
                                          ctypes.c_void_p, ctypes.c_void_p]
+    L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
+    L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
+    L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]
     L.krrt_launch_count.argtypes = [P]
     L.krrt_launch_count.restype = ctypes.c_int64
     L.krrt_set_profile.argtypes = [P, ctypes.c_int]
@@ -275,6 +278,33 @@ class Planner:
         n = ctypes.c_int32(0)
         self._ck(lib().krrt_solve(self.h, _d(xi), _d(xf), float(dt), float(t0), _d(rows), cap_rows, ctypes.byref(n)))
         return rows[:min(n.value, cap_rows)].copy()
+
+    # Connector slot: S samples (x,y,vx,vy,t0+t) of each optimal edge
+    def edge_samples(self, xi, xf, t0, S=10):
+        xi = _f64(xi, (-1, 4))
+        xf = _f64(xf, (-1, 4))
+        n = xi.shape[0]
+        t0 = _f64(np.broadcast_to(t0, (n,)))
+        rows = np.empty((n, S, 5))
+        self._ck(lib().krrt_edge_samples(self.h, _d(xi), _d(xf), _d(t0), n, int(S), _d(rows)))
+        return rows
+
+    # tree.trajectories: the stored edge parent[i] -> i of every node
+    def tree_edges(self, S=10):
+        n = self.size
+        rows = np.empty((n, S, 5))
+        self._ck(lib().krrt_tree_edges(self.h, int(S), _d(rows), n))
+        return rows
+
+    # solver.set_weight / env.collision_radius / sampler settings on a live context
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if k in ("lo", "hi"):
+                for i in range(4):
+                    getattr(self.cfg, k)[i] = float(v[i])
+            else:
+                setattr(self.cfg, k, v)
+        self._ck(lib().krrt_set_params(self.h, ctypes.byref(self.cfg)))
 
     def edge_collide(self, xi, xf, tau, t0):
         xi = _f64(xi, (-1, 4))

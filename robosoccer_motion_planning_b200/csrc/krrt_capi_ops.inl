@@ -362,4 +362,88 @@ int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out) {
   return KRRT_OK;
 }
 
+int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
+  if (!ctx || !nc) return KRRT_ERR_INVALID;
+  krrt_config c = *nc;
+  if (c.batch == 0) c.batch = ctx->cfg.batch;
+  if (c.near_cap == 0) c.near_cap = ctx->cfg.near_cap;
+  REQUIRE(c.device == ctx->cfg.device && c.precision == ctx->cfg.precision && c.capacity == ctx->cfg.capacity &&
+              c.batch == ctx->cfg.batch && c.near_cap == ctx->cfg.near_cap,
+          KRRT_ERR_INVALID, "device / precision / capacity / batch / near_cap are create-time fields");
+  REQUIRE(c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad S / r / R");
+  CK(cudaSetDevice(c.device));
+  if (c.gamma != ctx->cfg.gamma || c.rho_max != ctx->cfg.rho_max) {
+    const size_t cap = (size_t)c.capacity;
+    std::vector<double> rho2(cap + 1);
+    for (size_t n = 0; n <= cap; ++n) rho2[n] = near_radius2(c, (int)n);
+    CK(cudaMemcpyAsync(ctx->d_rho2, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->rho2_batch_cap = -1;  // the batched planner's table is rebuilt on its next call
+  }
+  ctx->cfg = c;
+  Params& P = ctx->P;
+  P.r = c.r;
+  P.R2 = c.R * c.R;
+  P.S = c.S;
+  for (int k = 0; k < 4; ++k) {
+    P.sp.lo[k] = c.lo[k];
+    P.sp.hi[k] = c.hi[k];
+  }
+  P.sp.p_direct = c.p_direct;
+  P.sp.seed = c.seed;
+  P.query_id = c.query_id;
+  P.goal_tol2 = c.goal_tol * c.goal_tol;
+  return KRRT_OK;
+}
+
+int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const double* t0, int n, int S, double* rows) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(n >= 0 && S >= 1 && (n == 0 || (xi && xf && t0 && rows)), KRRT_ERR_INVALID, "null buffer / S < 1");
+  if (n == 0) return KRRT_OK;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t sb = sizeof(double) * 4 * (size_t)n, ob = sizeof(double) * (size_t)n;
+  const size_t rb = sizeof(double) * 5 * (size_t)n * S;
+  if ((rc = ensure_scratch(ctx, 0, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 3, ob)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 7, rb)) != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], xi, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], xf, sb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_scratch[3], t0, ob, cudaMemcpyHostToDevice, st));
+  const long long total = (long long)n * S;
+  k_edge_samples<<<(unsigned)((total + 127) / 128), 128, 0, st>>>((const double*)ctx->d_scratch[0],
+                                                                  (const double*)ctx->d_scratch[1],
+                                                                  (const double*)ctx->d_scratch[3], n, S, ctx->cfg.r,
+                                                                  (double*)ctx->d_scratch[7]);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(rows, ctx->d_scratch[7], rb, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes) {
+  if (!ctx || !rows) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  REQUIRE(S >= 1 && cap_nodes >= 0, KRRT_ERR_INVALID, "S < 1 / cap_nodes < 0");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0;
+  int rc = current_size(ctx, &n);
+  if (rc != KRRT_OK) return rc;
+  n = std::min(n, cap_nodes);
+  if (n == 0) return KRRT_OK;
+  cudaStream_t st = ctx->stream;
+  const size_t rb = sizeof(double) * 5 * (size_t)n * S;
+  if ((rc = ensure_scratch(ctx, 7, rb)) != KRRT_OK) return rc;
+  const long long total = (long long)n * S;
+  k_tree_edges<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(ctx->T, n, S, (double*)ctx->d_scratch[7]);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(rows, ctx->d_scratch[7], rb, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
 }  // extern "C"

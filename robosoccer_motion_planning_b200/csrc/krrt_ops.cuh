@@ -177,4 +177,46 @@ __global__ void __launch_bounds__(128) k_traj_fill(const double* __restrict__ st
   }
 }
 
+// Connector slot: S samples (x, y, vx, vy, t0 + tau h) at h = k / (S - 1) of the optimal edge xi -> xf, one thread
+// per sample.  tau == nullptr: solve the steering here.  The same h grid as the collision predicate.
+__device__ __forceinline__ void write_edge_sample(const State4& x0, const State4& x1, double tau, double t0, int k,
+                                                  int S, double* row) {
+  const double h = (S > 1) ? (double)k / (double)(S - 1) : 0.0;
+  Edge e = make_edge(x0, x1, tau, t0);
+  row[0] = axis_pos(e.kx, h);
+  row[1] = axis_pos(e.ky, h);
+  row[2] = axis_vel(e.kx, h, x0.vx, tau);
+  row[3] = axis_vel(e.ky, h, x0.vy, tau);
+  row[4] = t0 + tau * h;
+}
+
+__global__ void __launch_bounds__(128) k_edge_samples(const double* __restrict__ xi, const double* __restrict__ xf,
+                                                        const double* __restrict__ t0, int n, int S, double r,
+                                                        double* __restrict__ rows) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long long)n * S) return;
+  const int e = (int)(g / S), k = (int)(g - (long long)e * S);
+  const double4 a = reinterpret_cast<const double4*>(xi)[e];
+  const double4 b = reinterpret_cast<const double4*>(xf)[e];
+  State4 x0 = {a.x, a.y, a.z, a.w}, x1 = {b.x, b.y, b.z, b.w};
+  double tau, c;
+  steer(x0, x1, r, tau, c);
+  write_edge_sample(x0, x1, tau, t0[e], k, S, rows + 5 * g);
+}
+
+// tree.trajectories: for every node i the stored edge parent[i] -> i (node 0: S copies of the root at t = 0)
+__global__ void __launch_bounds__(128) k_tree_edges(TreeView T, int n, int S, double* __restrict__ rows) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long long)n * S) return;
+  const int i = (int)(g / S), k = (int)(g - (long long)i * S);
+  const int p = T.parent[i];
+  const State4 x1 = load_state(T, i);
+  if (p < 0) {
+    double* row = rows + 5 * g;
+    row[0] = x1.x; row[1] = x1.y; row[2] = x1.vx; row[3] = x1.vy; row[4] = 0.0;
+    return;
+  }
+  write_edge_sample(load_state(T, p), x1, T.etime[i], T.tim[p], k, S, rows + 5 * g);
+}
+
 }  // namespace krrt

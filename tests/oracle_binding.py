@@ -149,10 +149,20 @@ def steer(x0, x1, r=0.5):
 
 
 def edge_state(x0, x1, tau, h):
+    """state on the optimal edge at h = t/tau; scalars -> (4,), arrays (n,4),(n,4),(n,),(n,) -> (n,4)"""
     x0 = np.ascontiguousarray(x0, dtype=np.float64)
     x1 = np.ascontiguousarray(x1, dtype=np.float64)
-    out = np.empty(4)
-    lib().ko_edge_state(_d(x0), _d(x1), float(tau), float(h), _d(out))
+    if x0.ndim == 1:
+        out = np.empty(4)
+        lib().ko_edge_state(_d(x0), _d(x1), float(tau), float(h), _d(out))
+        return out
+    n = x0.shape[0]
+    tau = np.broadcast_to(tau, (n,))
+    h = np.broadcast_to(h, (n,))
+    out = np.empty((n, 4))
+    f = lib().ko_edge_state
+    for i in range(n):
+        f(_d(x0[i]), _d(x1[i]), float(tau[i]), float(h[i]), _d(out[i]))
     return out
 
 

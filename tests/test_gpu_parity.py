@@ -306,3 +306,48 @@ def test_large_tree_100k_properties_and_parity(gpu_required):
     assert not cur.any()
     O.grow(None, n_iter)
     assert_same_tree(G, O)
+
+
+def test_edge_samples_and_tree_edges(gpu_required):
+    """Connector slot: S samples per optimal edge, and tree.trajectories (robosoccer_visual.hpp:18)."""
+    rng = np.random.default_rng(9)
+    n, S = 3000, 10
+    a, b = rand_states(rng, n), rand_states(rng, n)
+    t0 = rng.uniform(0, 5, n)
+    G, O = make_pair(gpu_required, 1, p_direct=0.1, capacity=2048)
+    rows = G.edge_samples(a, b, t0, S)
+    tau, _ = ob.steer(a, b, 0.5)
+    for k in range(S):
+        h = k / (S - 1)
+        ref = ob.edge_state(a, b, tau, np.full(n, h))
+        assert np.array_equal(rows[:, k, :4], ref)
+        assert np.array_equal(rows[:, k, 4], t0 + tau * h)
+    G.grow(scenes.GOAL, 1500)
+    O.grow(scenes.GOAL, 1500)
+    st, par, _, tim = O.tree()
+    E = G.tree_edges(S)
+    assert E.shape == (O.size, S, 5)
+    assert np.array_equal(E[0, :, :4], np.tile(st[0], (S, 1))) and not E[0, :, 4].any()
+    i = np.arange(1, O.size)
+    tau, _ = ob.steer(st[par[i]], st[i], 0.5)
+    for k in range(S):
+        h = k / (S - 1)
+        assert np.array_equal(E[1:, k, :4], ob.edge_state(st[par[i]], st[i], tau, np.full(len(i), h)))
+        assert np.array_equal(E[1:, k, 4], tim[par[i]] + tau * h)
+    assert np.array_equal(E[1:, S - 1, 4], tim[par[i]] + tau)
+
+
+def test_set_params_equals_fresh_context(gpu_required):
+    """solver.set_weight(r) / env.collision_radius / sampler settings changed on a live context (…node.cpp:84-92)."""
+    kw = dict(r=1.25, R=0.9, gamma=5.0, rho_max=3.0, p_direct=0.2, seed=7, query_id=3, goal_tol=0.25)
+    G = capi.Planner(capacity=4096)
+    G.set_params(**kw)
+    O = ob.OraclePlanner(capacity=4096, **kw)
+    obs = scenes.dynamic_obstacles(2)
+    for P in (G, O):
+        P.set_obstacles(obs, 1)
+        P.set_start(scenes.START)
+    assert G.grow(scenes.GOAL, 1500) == O.grow(scenes.GOAL, 1500)
+    assert_same_tree(G, O)
+    with pytest.raises(capi.KrrtError):
+        G.set_params(capacity=8192)

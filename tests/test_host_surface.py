@@ -1,0 +1,27 @@
+"""The C++17 component surface (include/rrtstar.hpp, include/integrator2drrt.hpp): a caller written like the
+reference's node (tests/native/host_surface_check.cpp) must compile with plain g++ -std=c++17, fail loudly without a
+GPU, and on a B200 grow exactly the oracle's tree through one grow(xg) call per iteration."""
+import subprocess
+
+import pytest
+
+import native_build
+
+
+def test_surface_compiles_and_has_no_cpu_fallback():
+    exe = native_build.build_host_surface_check()
+    from robosoccer_motion_planning_b200 import capi
+    if capi.lib().krrt_device_count() > 0:
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe, "static", "20"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3, r.stdout + r.stderr          # krrt::Error(KRRT_ERR_NO_DEVICE)
+    assert "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("env,iters", [("static", 100), ("dynamic", 100), ("dynamic", 400)])
+def test_node_style_caller_matches_oracle(gpu_required, env, iters):
+    exe = native_build.build_host_surface_check()
+    r = subprocess.run([exe, env, str(iters)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "0 check failure(s)" in r.stdout
