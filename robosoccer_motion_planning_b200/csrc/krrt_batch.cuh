@@ -126,31 +126,25 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
         continue;
       }
       __syncwarp();
-      if (K == 0) {
+      if (K == 0) {  // empty near set: the nearest node is the only candidate
         int aux = 0;
         warp_argmin(bd, bi, aux);
         if (lane == 0) N.idx[0] = bi;
         K = 1;
         __syncwarp();
-        if (lane == 0) {
-          double t, c;
-          steer(load_state(T, bi), s, J.r, t, c);
-          N.cf[0] = c; N.tf[0] = t; N.cb[0] = 0.0; N.tb[0] = 0.0;
-        }
-      } else {
-        // both steering directions of every near node, 2K independent tasks over the lanes
-        for (int t = lane; t < 2 * K; t += 32) {
-          const bool fwd = t < K;
-          const int k = fwd ? t : t - K;
-          const State4 x = load_state(T, N.idx[k]);
-          double tau, c;
-          if (fwd) {
-            steer(x, s, J.r, tau, c);
-            N.tf[k] = tau; N.cf[k] = c;
-          } else {
-            steer(s, x, J.r, tau, c);
-            N.tb[k] = tau; N.cb[k] = c;
-          }
+      }
+      // both steering directions of every near node: 2K independent tasks over the lanes, ONE call site so the
+      // lanes of a warp iterate the Newton loop together
+      for (int t = lane; t < 2 * K; t += 32) {
+        const bool fwd = t < K;
+        const int k = fwd ? t : t - K;
+        const State4 x = load_state(T, N.idx[k]);
+        double tau, c;
+        steer(fwd ? x : s, fwd ? s : x, J.r, tau, c);
+        if (fwd) {
+          N.tf[k] = tau; N.cf[k] = c;
+        } else {
+          N.tb[k] = tau; N.cb[k] = c;
         }
       }
       __syncwarp();

