@@ -148,6 +148,13 @@ int krrt_timer_begin(krrt_ctx* ctx);
 int krrt_timer_end(krrt_ctx* ctx, double* ms);
 /* profile mode: CUDA events around every neighbour-scan launch of krrt_grow (adds a little launch gap)  */
 int krrt_set_profile(krrt_ctx* ctx, int on);
+/* krrt_set_profile(ctx, 2): an event after every kernel of every round of krrt_grow (first 4096 rounds).
+ * ms / launches [0..6] = k_batch_prepare, k_near_scan, k_steer_pairs, k_wave_decide, k_wave_validate, k_wave_apply,
+ * k_commit; [7] = gaps between rounds (host read-back of the progress counter + enqueue)                  */
+int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]);
+/* since krrt_set_start: out[0] = rounds whose validated prefix was committed in parallel, out[1] = rounds (or
+ * single samples) committed by the sequential warp, out[2] = expansions committed in parallel              */
+int krrt_wave_stats(krrt_ctx* ctx, int64_t out[3]);
 /* device time of the last krrt_grow / krrt_plan_batch in ms (CUDA events on the ctx stream), and the share
  * spent in the neighbour-scan kernel (for the roofline line).                                   */
 int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* scan_launches,

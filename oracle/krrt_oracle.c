@@ -15,6 +15,11 @@
 #include <string.h>
 
 #define KO_MAX_NEWTON 100
+/* Newton on f' converges only linearly (ratio 1/2) when its two positive roots nearly coincide: 48 steps = 2^-48 */
+#define KO_MAX_STATIONARY 48
+/* relative step below which a Newton iteration has converged: a few ulp.  Without it the iteration dithers by
+ * +-1 ulp around the root for ~20 more steps (the rounding noise of f is of the order of one step). */
+#define KO_XTOL 1e-15
 
 /* ------------------------------------------------------------------ */
 /* Steering: tau^4 - a tau^2 + b tau - c0 = 0, SURVEY.md §8-M          */
@@ -42,11 +47,8 @@ static double q_root(double lo, double hi, double x, double a, double b, double 
     if (f == 0.0) return x;
     if (f < 0.0) lo = x; else hi = x;
     double xn = x - f / q_df(x, a, b);
-    if (!(xn > lo && xn < hi)) {
-      xn = lo + 0.5 * (hi - lo);
-      if (!(xn > lo && xn < hi)) return x;
-    }
-    if (xn == x) return x;
+    if (!(xn >= lo && xn <= hi)) xn = lo + 0.5 * (hi - lo); /* Newton left the bracket: bisect */
+    if (fabs(xn - x) <= KO_XTOL * x) return xn;
     x = xn;
   }
   return x;
@@ -55,11 +57,12 @@ static double q_root(double lo, double hi, double x, double a, double b, double 
 /* smallest positive critical point of f (root of f' on (0, sqrt(a/6))), b > 0 */
 static double q_crit_left(double a, double b) {
   double x = 0.0;
-  for (int it = 0; it < KO_MAX_NEWTON; ++it) {
+  for (int it = 0; it < KO_MAX_STATIONARY; ++it) {
     double g = q_df(x, a, b);
     if (!(g > 0.0)) break;
     double xn = x - g / q_ddf(x, a);
     if (!(xn > x)) break;
+    if (xn - x <= KO_XTOL * xn) { x = xn; break; }
     x = xn;
   }
   return x;
@@ -67,11 +70,12 @@ static double q_crit_left(double a, double b) {
 /* largest critical point of f (root of f' right of sqrt(a/6)), 0 <= b */
 static double q_crit_right(double a, double b) {
   double x = sqrt(0.5 * a);
-  for (int it = 0; it < KO_MAX_NEWTON; ++it) {
+  for (int it = 0; it < KO_MAX_STATIONARY; ++it) {
     double g = q_df(x, a, b);
     if (!(g > 0.0)) break;
     double xn = x - g / q_ddf(x, a);
     if (!(xn < x)) break;
+    if (x - xn <= KO_XTOL * x) { x = xn; break; }
     x = xn;
   }
   return x;

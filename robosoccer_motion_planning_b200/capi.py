@@ -29,7 +29,7 @@ EXPORTS = (
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
-    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples",
+    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats",
 )
 
 
@@ -117,6 +117,8 @@ def lib():
     L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
     L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
     L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]
+    L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
+    L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_launch_count.argtypes = [P]
     L.krrt_launch_count.restype = ctypes.c_int64
     L.krrt_set_profile.argtypes = [P, ctypes.c_int]
@@ -356,6 +358,20 @@ class Planner:
         ms = ctypes.c_double(0)
         self._ck(lib().krrt_timer_end(self.h, ctypes.byref(ms)))
         return ms.value
+
+    KERNELS = ("k_batch_prepare", "k_near_scan", "k_steer_pairs", "k_wave_decide", "k_wave_validate", "k_wave_apply",
+               "k_commit", "gap_between_rounds")
+
+    def kernel_times(self):
+        ms = np.zeros(8)
+        n = np.zeros(8, dtype=np.int64)
+        self._ck(lib().krrt_kernel_times(self.h, _d(ms), n.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))))
+        return {k: {"ms": float(ms[i]), "launches": int(n[i])} for i, k in enumerate(self.KERNELS)}
+
+    def wave_stats(self):
+        o = np.zeros(3, dtype=np.int64)
+        self._ck(lib().krrt_wave_stats(self.h, o.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))))
+        return {"rounds_parallel": int(o[0]), "rounds_sequential": int(o[1]), "expansions_parallel": int(o[2])}
 
     def set_profile(self, on):
         self._ck(lib().krrt_set_profile(self.h, int(on)))

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -13,6 +14,7 @@
 #include "../../include/krrt.h"
 #include "krrt_batch.cuh"
 #include "krrt_kernels.cuh"
+#include "krrt_wave.cuh"
 #include "krrt_ops.cuh"
 
 using namespace krrt;
@@ -37,7 +39,20 @@ struct krrt_ctx {
   double4* d_obs = nullptr;
   Ctl* d_ctl = nullptr;
   Batch Bt{};
+  Wave W{};
   Params P{};
+  int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the sequential commit (debugging / A-B timing)
+  int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
+  int wave_warps = 4;         // deciding warps per CTA (bounded by the near list's shared memory)
+  long long rounds_enqueued = 0;
+  // profile level 2: an event after every kernel of every round (bounded), summed per kernel in krrt_kernel_times
+  std::vector<cudaEvent_t> kev;
+  std::vector<int> kev_kind;
+  double kernel_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long kernel_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int level2 = 0;
+  Ctl* h_ctl = nullptr;       // pinned: progress read-back between groups of rounds
+  cudaEvent_t ev_group[2] = {nullptr, nullptr};
   double* d_user = nullptr;
   size_t user_cap = 0;
   std::vector<void*> allocs;
@@ -148,6 +163,10 @@ void krrt_destroy(krrt_ctx* ctx) {
   if (ctx->d_user) cudaFree(ctx->d_user);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
   for (cudaEvent_t e : ctx->scan_events) cudaEventDestroy(e);
+  for (cudaEvent_t e : ctx->kev) cudaEventDestroy(e);
+  if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+  for (cudaEvent_t e : ctx->ev_group)
+    if (e) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->tm0) cudaEventDestroy(ctx->tm0);
   if (ctx->tm1) cudaEventDestroy(ctx->tm1);
@@ -212,6 +231,7 @@ static int create_impl(krrt_ctx* ctx) {
   const size_t bc = (size_t)B.B * B.near_cap;
   CK(dev_alloc(ctx, &B.samples, (size_t)B.B));
   CK(dev_alloc(ctx, &B.reject, (size_t)B.B));
+  CK(dev_alloc(ctx, &B.dup, (size_t)B.B));
   CK(dev_alloc(ctx, &B.map, (size_t)B.B));
   CK(dev_alloc(ctx, &B.count, (size_t)B.B));
   CK(dev_alloc(ctx, &B.ref, bc));
@@ -220,6 +240,31 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &B.cf, bc));
   CK(dev_alloc(ctx, &B.tb, bc));
   CK(dev_alloc(ctx, &B.cb, bc));
+  Wave& W = ctx->W;
+  CK(dev_alloc(ctx, &W.rec, (size_t)B.B));
+  CK(dev_alloc(ctx, &W.near_idx, bc));
+  CK(dev_alloc(ctx, &W.rew_node, bc));
+  CK(dev_alloc(ctx, &W.rew_slot, bc));
+  CK(dev_alloc(ctx, &W.wl, (size_t)B.B * WAVE_QCAP));
+  CK(dev_alloc(ctx, &W.wmin, cap));
+  CK(dev_alloc(ctx, &W.amin, cap));
+  CK(dev_alloc(ctx, &W.dsc, cap));
+  CK(dev_alloc(ctx, &W.lock, cap));
+  CK(cudaMemsetAsync(W.wmin, 0, sizeof(unsigned) * cap, ctx->stream));
+  CK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, ctx->stream));
+  CK(cudaMemsetAsync(W.dsc, 0, sizeof(unsigned) * cap, ctx->stream));
+  CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
+  CK(cudaMallocHost((void**)&ctx->h_ctl, 2 * sizeof(Ctl)));
+  CK(cudaEventCreateWithFlags(&ctx->ev_group[0], cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&ctx->ev_group[1], cudaEventDisableTiming));
+  if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
+  {
+    const size_t per_warp = wave_warp_smem_bytes(B.near_cap);
+    ctx->wave_warps = (int)std::max<size_t>(1, std::min<size_t>(4, (size_t)200 * 1024 / per_warp));
+    CK(cudaFuncSetAttribute(k_wave_decide, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)(per_warp * ctx->wave_warps)));
+  }
   Params& P = ctx->P;
   P.r = c.r;
   P.R2 = c.R * c.R;
@@ -283,6 +328,7 @@ int krrt_timer_end(krrt_ctx* ctx, double* ms) {
 int krrt_set_profile(krrt_ctx* ctx, int on) {
   if (!ctx) return KRRT_ERR_INVALID;
   ctx->profile = on != 0;
+  ctx->level2 = on == 2;
   return KRRT_OK;
 }
 
@@ -310,6 +356,7 @@ __global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
   memset(&z, 0, sizeof(z));
   z.n = 1;
   z.goal_index = -1;
+  z.round = ctl->round;  // the epoch of the conflict marks survives a restart (marks are never cleared)
   *ctl = z;
 }
 
@@ -325,8 +372,15 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   return KRRT_OK;
 }
 
-__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g) {
+__global__ void k_reset_round(Ctl* ctl) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) ctl->round = 0;
+}
+
+__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g, int n_iter) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  ctl->iter_begin = ctl->iter;
+  ctl->iter_target = ctl->iter + n_iter;
+  if (ctl->ema16 <= 0) ctl->ema16 = 16 * 16;
   ctl->full = 0;
   ctl->scan_pairs = 0.0;
   ctl->scan_nodes = 0.0;
@@ -361,35 +415,92 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   State4 g = {0, 0, 0, 0};
   if (goal) g = State4{goal[0], goal[1], goal[2], goal[3]};
   CK(cudaEventRecord(ctx->ev0, st));
-  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g);
+  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g, n_iter);
   ctx->launches++;
   const int B = ctx->Bt.B;
-  const int nbatch = (n_iter + B - 1) / B;
-  if (ctx->profile) {
-    while ((int)ctx->scan_events.size() < 2 * nbatch) {
-      cudaEvent_t e;
-      CK(cudaEventCreate(&e));
-      ctx->scan_events.push_back(e);
-    }
-  }
   const int commit_smem = (int)(sizeof(double4) * KRRT_MAX_OBS + (size_t)ctx->Bt.near_cap * (4 * 8 + 4 + 1) + 16);
+  const int decide_smem = (int)(wave_warp_smem_bytes(ctx->Bt.near_cap) * ctx->wave_warps);
   const int prep_threads = ((B + 31) / 32) * 32;
   const int max_ctas = ctx->prop.multiProcessorCount * 8;
-  for (int k = 0; k < nbatch; ++k) {
-    const int off = k * B;
-    const int nb = std::min(B, n_iter - off);
-    k_batch_prepare<<<1, prep_threads, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, nb, samples ? ctx->d_user : nullptr, off);
-    const int n_up = std::min<long long>(ctx->cfg.capacity, (long long)ctx->n_upper);
-    int ctas = (n_up + SCAN_NODES_PER_CTA - 1) / SCAN_NODES_PER_CTA;
-    ctas = std::max(1, std::min(ctas, max_ctas));
-    if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * k], st));
-    k_near_scan<<<ctas, SCAN_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt);
-    if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * k + 1], st));
-    dim3 sg((ctx->Bt.near_cap + STEER_THREADS - 1) / STEER_THREADS, nb);
-    k_steer_pairs<<<sg, STEER_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt, ctx->P.r);
-    k_commit<<<1, 32, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt);
-    ctx->launches += 4;
-    ctx->n_upper = (int)std::min<long long>(ctx->cfg.capacity, (long long)ctx->n_upper + nb);
+  const double* d_user = samples ? ctx->d_user : nullptr;
+  // Rounds are data dependent (a wave round commits a validated prefix of its batch), so the host enqueues groups
+  // of rounds sized from the progress seen so far and reads the control block back between groups; rounds
+  // enqueued past the target find nothing left to do.
+  size_t kev_used = 0;
+  ctx->kev_kind.clear();
+  auto mark = [&](int kind) -> int {  // kind -1 = start of a round; else the kernel that just went in
+    if (!ctx->level2 || kev_used >= 8 * 4096) return KRRT_OK;
+    if (kev_used >= ctx->kev.size()) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      ctx->kev.push_back(e);
+    }
+    CK(cudaEventRecord(ctx->kev[kev_used++], st));
+    ctx->kev_kind.push_back(kind);
+    return KRRT_OK;
+  };
+  long long consumed = 0;
+  int n_known = ctx->n_upper;
+  double per_round = (ctx->wave_enabled && n_known >= ctx->wave_min_n) ? 16.0 : (double)B;
+  int scan_rounds = 0;
+  Ctl* hp = ctx->h_ctl;
+  while (consumed < n_iter) {
+    const long long left = n_iter - consumed;
+    const int rounds = (int)std::max<long long>(1, std::min<long long>(64, (long long)std::ceil((double)left / per_round)));
+    for (int k = 0; k < rounds; ++k) {
+      if (ctx->rounds_enqueued >= (1ll << 23) - 2) {  // mark epochs are 23 bits: start over with clean marks
+        const size_t cap = (size_t)ctx->cfg.capacity;
+        CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
+        CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
+        CK(cudaMemsetAsync(ctx->W.dsc, 0, sizeof(unsigned) * cap, st));
+        k_reset_round<<<1, 32, 0, st>>>(ctx->d_ctl);
+        ctx->rounds_enqueued = 0;
+      }
+      if (mark(-1) != KRRT_OK) return KRRT_ERR_CUDA;
+      k_batch_prepare<<<1, prep_threads, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->wave_enabled, ctx->wave_min_n, d_user);
+      ctx->rounds_enqueued++;
+      if (mark(0) != KRRT_OK) return KRRT_ERR_CUDA;
+      const int n_up = (int)std::min<long long>(ctx->cfg.capacity, (long long)n_known + (long long)(k + 1) * B);
+      int ctas = (n_up + SCAN_NODES_PER_CTA - 1) / SCAN_NODES_PER_CTA;
+      ctas = std::max(1, std::min(ctas, max_ctas));
+      if (ctx->profile) {
+        while ((int)ctx->scan_events.size() < 2 * (scan_rounds + 1)) {
+          cudaEvent_t e;
+          CK(cudaEventCreate(&e));
+          ctx->scan_events.push_back(e);
+        }
+        CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds], st));
+      }
+      k_near_scan<<<ctas, SCAN_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt);
+      if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds + 1], st));
+      ++scan_rounds;
+      if (mark(1) != KRRT_OK) return KRRT_ERR_CUDA;
+      dim3 sg((ctx->Bt.near_cap + STEER_THREADS - 1) / STEER_THREADS, B);
+      k_steer_pairs<<<sg, STEER_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt, ctx->P.r);
+      ctx->launches += 3;
+      if (mark(2) != KRRT_OK) return KRRT_ERR_CUDA;
+      if (ctx->wave_enabled) {
+        k_wave_decide<<<(B + ctx->wave_warps - 1) / ctx->wave_warps, 128, decide_smem, st>>>(
+            ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, ctx->wave_warps);
+        if (mark(3) != KRRT_OK) return KRRT_ERR_CUDA;
+        k_wave_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->Bt, ctx->W);
+        if (mark(4) != KRRT_OK) return KRRT_ERR_CUDA;
+        k_wave_apply<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->T, ctx->Bt, ctx->W);
+        if (mark(5) != KRRT_OK) return KRRT_ERR_CUDA;
+        ctx->launches += 3;
+      }
+      k_commit<<<1, 32, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
+      if (mark(6) != KRRT_OK) return KRRT_ERR_CUDA;
+      ctx->launches++;
+    }
+    CK(cudaMemcpyAsync(hp, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    const long long now = hp->iter - hp->iter_begin;
+    per_round = std::max(1.0, (double)(now - consumed) / rounds);
+    consumed = now;
+    n_known = hp->n;
+    if (hp->full || hp->error) break;
   }
   k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
   ctx->launches++;
@@ -406,13 +517,30 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   ctx->last_scan_node_samples = h.scan_pairs;
   if (ctx->profile) {
     double acc = 0.0;
-    for (int k = 0; k < nbatch; ++k) {
+    for (int k = 0; k < scan_rounds; ++k) {
       float t = 0.f;
       CK(cudaEventElapsedTime(&t, ctx->scan_events[2 * k], ctx->scan_events[2 * k + 1]));
       acc += t;
     }
     ctx->last_scan_ms = acc;
-    ctx->last_scan_launches = nbatch;
+    ctx->last_scan_launches = scan_rounds;
+  }
+  if (ctx->level2) {
+    for (int k = 0; k < 8; ++k) { ctx->kernel_ms[k] = 0.0; ctx->kernel_n[k] = 0; }
+    for (size_t k = 1; k < kev_used; ++k) {
+      const int kind = ctx->kev_kind[k];
+      if (kind < 0) {  // gap between rounds (host sync + enqueue, or nothing when rounds are back to back)
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, ctx->kev[k - 1], ctx->kev[k]));
+        ctx->kernel_ms[7] += t;
+        ctx->kernel_n[7]++;
+        continue;
+      }
+      float t = 0.f;
+      CK(cudaEventElapsedTime(&t, ctx->kev[k - 1], ctx->kev[k]));
+      ctx->kernel_ms[kind] += t;
+      ctx->kernel_n[kind]++;
+    }
   }
   if (h.error) {
     ctx->err = h.error == KRRT_ERR_NEAR_OVERFLOW ? "near set exceeded near_cap; raise krrt_config.near_cap" : "device error";
@@ -464,6 +592,28 @@ int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out) {
   int rc = fetch_ctl(ctx, &h);
   if (rc != KRRT_OK) return rc;
   std::memcpy(out, h.stats, sizeof(krrt_stats));
+  return KRRT_OK;
+}
+
+int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]) {
+  if (!ctx || !ms || !launches) return KRRT_ERR_INVALID;
+  for (int k = 0; k < 8; ++k) {
+    ms[k] = ctx->kernel_ms[k];
+    launches[k] = ctx->kernel_n[k];
+  }
+  return KRRT_OK;
+}
+
+int krrt_wave_stats(krrt_ctx* ctx, int64_t out[3]) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  out[0] = h.rounds_wave;
+  out[1] = h.rounds_seq;
+  out[2] = h.wave_committed;
   return KRRT_OK;
 }
 

@@ -34,6 +34,14 @@ struct Ctl {  // device-resident control block of one single-tree context
   double goal[4];
   double last_sample[4];
   long long stats[10];
+  // round control (all decided on the device: the host only enqueues rounds until iter == iter_target)
+  long long iter_begin;   // iteration counter when the current krrt_grow call began (index base of user samples)
+  long long iter_target;  // iteration counter at which the current krrt_grow call is complete
+  unsigned round;         // round id: epoch of the conflict marks (krrt_wave.cuh)
+  int wave;               // this round commits a validated prefix in parallel (tree large enough)
+  int wave_F;             // length of that prefix
+  int ema16;              // 16 x running mean of the prefix length: sizes the next round's batch
+  long long rounds_wave, rounds_seq, wave_committed;  // diagnostics since set_start
 };
 
 struct Params {
@@ -54,6 +62,7 @@ struct Batch {
   State4* samples;        // [B]
   unsigned char* reject;  // [B] sample inside a static obstacle
   int* map;               // [B] node index the sample became, or -1
+  unsigned char* dup;     // [B] a frozen node coincides with the sample (distance exactly 0)
   int* count;             // [B] candidates found (may exceed near_cap: overflow)
   int* ref;               // [B][near_cap]
   double* d2;             // [B][near_cap]
@@ -66,17 +75,26 @@ struct Batch {
 };
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void k_batch_prepare(Ctl* ctl, Params P, Batch Bt, int nb_req, const double* user_samples,
-                                int user_offset) {
+__global__ void k_batch_prepare(Ctl* ctl, Params P, Batch Bt, int wave_enabled, int wave_min_n,
+                                const double* user_samples) {
   __shared__ State4 ss[256];
   __shared__ double s_rho2max;
   const int b = threadIdx.x;
   const int n0 = ctl->n;
-  const int nb = ctl->full ? 0 : nb_req;
   const long long iter0 = ctl->iter;
+  const long long left = ctl->iter_target - iter0;
+  const int wave = wave_enabled && n0 >= wave_min_n;
+  int nb_req = Bt.B;
+  if (wave) nb_req = min(Bt.B, max(16, (2 * ctl->ema16) / 16 + 8));  // ~2x the prefix the last rounds committed
+  const int nb = (ctl->full || ctl->error || left <= 0) ? 0 : (int)min((long long)nb_req, left);
+  const int user_offset = (int)(iter0 - ctl->iter_begin);
+  __syncthreads();  // every thread has read the control block before thread 0 rewrites it
   if (b == 0) {
     ctl->n0 = n0;
     ctl->nb = nb;
+    ctl->wave = wave;
+    ctl->wave_F = nb;
+    ctl->round += 1;
     double mx = 0.0;
     int hi = min(n0 + nb, P.capacity);
     for (int k = n0; k <= hi; ++k) mx = fmax(mx, P.rho2[k]);
@@ -111,6 +129,7 @@ __global__ void k_batch_prepare(Ctl* ctl, Params P, Batch Bt, int nb_req, const 
     Bt.samples[b] = s;
     Bt.reject[b] = hit ? 1 : 0;
     Bt.map[b] = -1;
+    Bt.dup[b] = 0;
     ss[b] = s;
   }
   __syncthreads();
@@ -164,6 +183,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_near_scan(const Ctl* ctl, cons
       const State4 s = ss[b];
       double da = dist2(a, s), dc = dist2(c, s);
       if (v0 && da <= rmax) {
+        if (da == 0.0) Bt.dup[b] = 1;
         int slot = atomicAdd(&Bt.count[b], 1);
         if (slot < Bt.near_cap) {
           Bt.ref[(size_t)b * Bt.near_cap + slot] = i0;
@@ -171,6 +191,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_near_scan(const Ctl* ctl, cons
         }
       }
       if (v1 && dc <= rmax) {
+        if (dc == 0.0) Bt.dup[b] = 1;
         int slot = atomicAdd(&Bt.count[b], 1);
         if (slot < Bt.near_cap) {
           Bt.ref[(size_t)b * Bt.near_cap + slot] = i1;
@@ -211,8 +232,44 @@ __global__ void __launch_bounds__(STEER_THREADS) k_steer_pairs(const Ctl* ctl, c
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Per-sample decision of a wave round (krrt_wave.cuh) and the conflict marks it is validated with.
+enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5 };
+constexpr int WAVE_QCAP = 2048;  // write-list capacity per sample (descendants of its rewired nodes)
+
+struct WaveRec {
+  int outcome;
+  int n_b;    // tree size this sample expects to see (== index of the node it inserts)
+  int par;    // chosen parent (node index)
+  int park;   // its slot in the sample's candidate list
+  int K;      // near-set size
+  int nrew;   // rewired nodes
+  int nwl;    // strict descendants of the rewired nodes (== cost/time updates to propagate)
+  int pad;
+  double ctc_new, tim_new;
+  long long collide_calls;
+};
+
+struct Wave {
+  WaveRec* rec;     // [B]
+  int* near_idx;    // [B][near_cap] near set (node indices)
+  int* rew_node;    // [B][near_cap] rewired nodes ...
+  int* rew_slot;    // [B][near_cap] ... and their slots in the candidate list
+  int* wl;          // [B][WAVE_QCAP] strict descendants of the rewired nodes / BFS scratch of the apply pass
+  unsigned* wmin;   // [capacity] mark: lowest sample of this round that WRITES the node's cost/time
+  unsigned* amin;   // [capacity] mark: lowest sample of this round that reads or writes it
+  unsigned* dsc;    // [capacity] mark: lowest sample for which the node is a strict descendant of a rewired node
+  int* lock;        // [capacity] child-list lock of a parent
+};
+
+// marks carry the round id, so they never need clearing: (round << 9) | (511 - sample), combined with atomicMax
+__device__ __forceinline__ unsigned mark_key(unsigned round, int b) { return (round << 9) | (unsigned)(511 - b); }
+__device__ __forceinline__ int mark_sample(unsigned m, unsigned round) {
+  return (m >> 9) == round ? 511 - (int)(m & 511u) : 0x7fffffff;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // In-order commit of one batch by a single warp.  Dynamic shared memory: near list (near_cap entries) + obstacles.
-__global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, Batch Bt) {
+__global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = lane_id();
   const int cap = Bt.near_cap;
@@ -224,8 +281,44 @@ __global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, B
   N.tb = N.cb + cap;
   N.idx = reinterpret_cast<int*>(N.tb + cap);
   N.tried = reinterpret_cast<unsigned char*>(N.idx + cap);
-  const int nb = ctl->nb;
+  int nb = ctl->nb;
   if (nb == 0 || ctl->error) return;
+  if (ctl->wave) {
+    const int F = ctl->wave_F;
+    if (F > 0) {  // the first F samples were committed in parallel (k_wave_apply): fold their counters in
+      long long v[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+      for (int b = lane; b < F; b += 32) {
+        const WaveRec r = W.rec[b];
+        v[0] += 1;
+        if (r.outcome == OUT_INSERT) {
+          v[1] += 1; v[5] += r.nrew; v[6] += r.nwl; v[7] += r.K; v[8] += 2 * r.K - 1; v[9] += r.collide_calls;
+        } else if (r.outcome == OUT_REJECT) {
+          v[2] += 1;
+        } else if (r.outcome == OUT_DUP) {
+          v[3] += 1;
+        } else {  // OUT_NOFREE
+          v[4] += 1; v[7] += r.K; v[8] += r.K; v[9] += r.collide_calls;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 10; ++k)
+        for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], off);
+      if (lane == 0) {
+        ctl->n += (int)v[1];
+        ctl->iter += F;
+        for (int k = 0; k < 10; ++k) ctl->stats[k] += v[k];
+        const State4 ls = Bt.samples[F - 1];
+        ctl->last_sample[0] = ls.x; ctl->last_sample[1] = ls.y; ctl->last_sample[2] = ls.vx; ctl->last_sample[3] = ls.vy;
+        ctl->ema16 = (3 * ctl->ema16 + 16 * F) / 4;
+        ctl->rounds_wave += 1;
+        ctl->wave_committed += F;
+      }
+      return;
+    }
+    nb = 1;  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
+    if (lane == 0) ctl->ema16 = (3 * ctl->ema16 + 16) / 4;
+  }
+  if (lane == 0) ctl->rounds_seq += 1;
   for (int j = lane; j < P.m; j += 32) s_obs[j] = P.obs[j];
   __syncwarp();
   EnvView E = {s_obs, P.m, P.dynamic, P.R2, P.S};

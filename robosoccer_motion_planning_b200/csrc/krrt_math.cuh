@@ -17,6 +17,13 @@
 
 #define KRRT_HD __host__ __device__ __forceinline__
 #define KRRT_NEWTON_MAX 100
+#define KRRT_STATIONARY_MAX 48  // == KO_MAX_STATIONARY: linear convergence (ratio 1/2) at a near-double root of f'
+// relative Newton step that counts as converged (a few ulp; the CPU checker uses the same constant): without it the
+// iteration dithers +-1 ulp around the root for ~20 more steps and every lane of the warp waits for the slowest
+#define KRRT_XTOL 1e-15
+#ifndef KRRT_ITER_HOOK
+#define KRRT_ITER_HOOK(which)  // test instrumentation point (tests/native/newton_iters.cu counts iterations here)
+#endif
 
 namespace krrt {
 
@@ -37,15 +44,13 @@ KRRT_HD double arrival_cost(double t, double a, double b, double c0) {
 // Newton safeguarded by a sign bracket [lo,hi] with f(lo) <= 0 <= f(hi)
 KRRT_HD double bracketed_root(double lo, double hi, double x, double a, double b, double c0) {
   for (int it = 0; it < KRRT_NEWTON_MAX; ++it) {
+    KRRT_ITER_HOOK(0)
     double f = quartic(x, a, b, c0);
     if (f == 0.0) return x;
     if (f < 0.0) lo = x; else hi = x;
     double xn = x - f / quartic_d1(x, a, b);
-    if (!(xn > lo && xn < hi)) {
-      xn = lo + 0.5 * (hi - lo);
-      if (!(xn > lo && xn < hi)) return x;
-    }
-    if (xn == x) return x;
+    if (!(xn >= lo && xn <= hi)) xn = lo + 0.5 * (hi - lo);  // Newton left the bracket: bisect
+    if (fabs(xn - x) <= KRRT_XTOL * x) return xn;
     x = xn;
   }
   return x;
@@ -54,22 +59,32 @@ KRRT_HD double bracketed_root(double lo, double hi, double x, double a, double b
 // stationary points of f: monotone Newton on f' from the left (start 0) and from the right (start sqrt(a/2))
 KRRT_HD double stationary_left(double a, double b) {
   double x = 0.0;
-  for (int it = 0; it < KRRT_NEWTON_MAX; ++it) {
+  for (int it = 0; it < KRRT_STATIONARY_MAX; ++it) {
+    KRRT_ITER_HOOK(1)
     double g = quartic_d1(x, a, b);
     if (!(g > 0.0)) break;
     double xn = x - g / quartic_d2(x, a);
     if (!(xn > x)) break;
+    if (xn - x <= KRRT_XTOL * xn) {
+      x = xn;
+      break;
+    }
     x = xn;
   }
   return x;
 }
 KRRT_HD double stationary_right(double a, double b) {
   double x = sqrt(0.5 * a);
-  for (int it = 0; it < KRRT_NEWTON_MAX; ++it) {
+  for (int it = 0; it < KRRT_STATIONARY_MAX; ++it) {
+    KRRT_ITER_HOOK(2)
     double g = quartic_d1(x, a, b);
     if (!(g > 0.0)) break;
     double xn = x - g / quartic_d2(x, a);
     if (!(xn < x)) break;
+    if (x - xn <= KRRT_XTOL * x) {
+      x = xn;
+      break;
+    }
     x = xn;
   }
   return x;
@@ -81,7 +96,7 @@ KRRT_HD double stationary_right(double a, double b) {
 // Written for SIMT convergence: every lane of a warp walks the SAME instruction sequence — one bracket
 // set-up, ONE bracketed-Newton loop for the primary root, and a rare (0.07 % of field-scale pairs) second pass
 // for the three-root zone — instead of one inlined Newton loop per case.  The operations each lane performs,
-// and their order, are exactly those of the oracle's case tree (oracle/krrt_oracle.c ko_steer), so results are
+// and their order, are exactly those of the oracle's case tree (the CPU checker restates the same case tree), so results are
 // bit-identical; only the instruction layout differs.
 KRRT_HD void steer(const State4& x0, const State4& x1, double r, double& tau_out, double& cost_out) {
   double dpx = x1.x - x0.x, dpy = x1.y - x0.y;
