@@ -153,8 +153,10 @@ int krrt_set_profile(krrt_ctx* ctx, int on);
  * k_commit; [7] = gaps between rounds (host read-back of the progress counter + enqueue)                  */
 int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]);
 /* since krrt_set_start: out[0] = rounds whose validated prefix was committed in parallel, out[1] = rounds (or
- * single samples) committed by the sequential warp, out[2] = expansions committed in parallel              */
-int krrt_wave_stats(krrt_ctx* ctx, int64_t out[3]);
+ * single samples) committed by the sequential warp, out[2] = expansions committed in parallel; out[3..7] = what
+ * ended the parallel prefixes: end of batch, in-batch neighbour, sample needing the sequential path, sample with
+ * no collision-free parent, read/write conflict                                                             */
+int krrt_wave_stats(krrt_ctx* ctx, int64_t out[8]);
 /* device time of the last krrt_grow / krrt_plan_batch in ms (CUDA events on the ctx stream), and the share
  * spent in the neighbour-scan kernel (for the roofline line).                                   */
 int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* scan_launches,

@@ -369,9 +369,11 @@ class Planner:
         return {k: {"ms": float(ms[i]), "launches": int(n[i])} for i, k in enumerate(self.KERNELS)}
 
     def wave_stats(self):
-        o = np.zeros(3, dtype=np.int64)
+        o = np.zeros(8, dtype=np.int64)
         self._ck(lib().krrt_wave_stats(self.h, o.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))))
-        return {"rounds_parallel": int(o[0]), "rounds_sequential": int(o[1]), "expansions_parallel": int(o[2])}
+        return {"rounds_parallel": int(o[0]), "rounds_sequential": int(o[1]), "expansions_parallel": int(o[2]),
+                "prefix_ended_by": {"batch_end": int(o[3]), "in_batch_neighbour": int(o[4]), "sequential_sample": int(o[5]),
+                                    "no_free_parent": int(o[6]), "rw_conflict": int(o[7])}}
 
     def set_profile(self, on):
         self._ck(lib().krrt_set_profile(self.h, int(on)))

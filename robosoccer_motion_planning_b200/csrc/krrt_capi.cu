@@ -483,7 +483,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
         k_wave_decide<<<(B + ctx->wave_warps - 1) / ctx->wave_warps, 128, decide_smem, st>>>(
             ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, ctx->wave_warps);
         if (mark(3) != KRRT_OK) return KRRT_ERR_CUDA;
-        k_wave_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->Bt, ctx->W);
+        k_wave_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->W);
         if (mark(4) != KRRT_OK) return KRRT_ERR_CUDA;
         k_wave_apply<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->T, ctx->Bt, ctx->W);
         if (mark(5) != KRRT_OK) return KRRT_ERR_CUDA;
@@ -604,7 +604,7 @@ int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]) {
   return KRRT_OK;
 }
 
-int krrt_wave_stats(krrt_ctx* ctx, int64_t out[3]) {
+int krrt_wave_stats(krrt_ctx* ctx, int64_t out[8]) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -614,6 +614,7 @@ int krrt_wave_stats(krrt_ctx* ctx, int64_t out[3]) {
   out[0] = h.rounds_wave;
   out[1] = h.rounds_seq;
   out[2] = h.wave_committed;
+  for (int k = 0; k < 5; ++k) out[3 + k] = h.why[k];
   return KRRT_OK;
 }
 

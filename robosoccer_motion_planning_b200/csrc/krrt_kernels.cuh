@@ -42,6 +42,7 @@ struct Ctl {  // device-resident control block of one single-tree context
   int wave_F;             // length of that prefix
   int ema16;              // 16 x running mean of the prefix length: sizes the next round's batch
   long long rounds_wave, rounds_seq, wave_committed;  // diagnostics since set_start
+  long long why[5];  // what ended the prefix: batch end, in-batch neighbour, needs sequential path, no free parent, read/write conflict
 };
 
 struct Params {
@@ -247,6 +248,8 @@ struct WaveRec {
   int pad;
   double ctc_new, tim_new;
   long long collide_calls;
+  double d2_in_max;   // largest squared distance inside the near set ...
+  double d2_out_min;  // ... and smallest one outside it: the decision holds for any radius in between
 };
 
 struct Wave {
@@ -312,6 +315,12 @@ __global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, B
         ctl->ema16 = (3 * ctl->ema16 + 16 * F) / 4;
         ctl->rounds_wave += 1;
         ctl->wave_committed += F;
+        int why = 0;
+        if (F < nb) {
+          const int o = W.rec[F].outcome;
+          why = o == OUT_CONFLICT ? 1 : o == OUT_COMPLEX ? 2 : (o == OUT_NOFREE ? 3 : 4);
+        }
+        ctl->why[why] += 1;
       }
       return;
     }

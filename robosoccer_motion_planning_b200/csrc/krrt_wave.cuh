@@ -5,7 +5,7 @@
 // batch is decided in parallel against the tree as it stands (k_wave_decide), each decision marks what it read and
 // what it would write, and k_wave_validate finds the longest prefix [0, F) of the batch in which no sample touches
 // anything an earlier sample writes (and no earlier sample touches anything it writes), no earlier sample's new
-// node falls inside its near radius, and every earlier sample got the node index it was assumed to get.  For that
+// node falls inside its near radius, and its near set is the same at the radius of the tree size it really sees.  For that
 // prefix the sequential outcome IS the speculated one, so k_wave_apply commits it in parallel; the batch restarts
 // at sample F in the next round (as sample 0, which by construction has nothing before it).  A sample that cannot
 // be decided this way at all (empty near set -> global nearest, a rewired subtree larger than WAVE_QCAP, a near
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(128) k_wave_decide(const Ctl* ctl, Params P, T
 
   WaveRec r;
   r.outcome = OUT_COMPLEX; r.n_b = 0; r.par = -1; r.park = -1; r.K = 0; r.nrew = 0; r.nwl = 0; r.pad = 0;
-  r.ctc_new = 0.0; r.tim_new = 0.0; r.collide_calls = 0;
+  r.ctc_new = 0.0; r.tim_new = 0.0; r.collide_calls = 0; r.d2_in_max = 0.0; r.d2_out_min = INFINITY;
   const State4 s = Bt.samples[b];
   if (!P.dynamic && Bt.reject[b]) {
     r.outcome = OUT_REJECT;
@@ -71,6 +71,7 @@ __global__ void __launch_bounds__(128) k_wave_decide(const Ctl* ctl, Params P, T
   const double rho2n = P.rho2[n_b];
   int K = 0;
   bool dup = false, inbatch = false;
+  double din = 0.0, dout = INFINITY;
   for (int base = 0; base < cnt; base += 32) {
     const int e = base + lane;
     bool valid = false;
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(128) k_wave_decide(const Ctl* ctl, Params P, T
       } else {
         valid = d <= rho2n;
         dup |= d == 0.0;
+        if (valid) din = fmax(din, d); else dout = fmin(dout, d);
       }
     }
     const unsigned mk = __ballot_sync(FULL, valid);
@@ -104,6 +106,12 @@ __global__ void __launch_bounds__(128) k_wave_decide(const Ctl* ctl, Params P, T
     if (lane == 0) W.rec[b] = r;
     return;
   }
+  for (int off = 16; off > 0; off >>= 1) {
+    din = fmax(din, __shfl_xor_sync(FULL, din, off));
+    dout = fmin(dout, __shfl_xor_sync(FULL, dout, off));
+  }
+  r.d2_in_max = din;
+  r.d2_out_min = dout;
   if (K == 0 || K > 1024) {  // nearest-node fallback scans the whole tree (and 1024 = 32 lanes x 32 tried bits): sequential path
     if (lane == 0) W.rec[b] = r;
     return;
@@ -252,7 +260,7 @@ __global__ void __launch_bounds__(128) k_wave_decide(const Ctl* ctl, Params P, T
 
 // ---------------------------------------------------------------------------------------------------
 // One warp per sample: is the decision still the sequential one given everything earlier samples do?
-__global__ void __launch_bounds__(128) k_wave_validate(Ctl* ctl, Batch Bt, Wave W) {
+__global__ void __launch_bounds__(128) k_wave_validate(Ctl* ctl, Params P, Batch Bt, Wave W) {
   if (!ctl->wave) return;
   const int nb = ctl->nb;
   const int lane = lane_id();
@@ -267,6 +275,17 @@ __global__ void __launch_bounds__(128) k_wave_validate(Ctl* ctl, Batch Bt, Wave 
   const unsigned round = ctl->round;
   const int cap = Bt.near_cap;
   bool conf = false;
+  // the node index / tree size this sample really gets: earlier samples that found no free parent did not insert.
+  // The decision was taken at the radius of r.n_b; it stands if no candidate lies between the two radii.
+  int ins = 0;
+  for (int e = lane; e < b; e += 32) ins += W.rec[e].outcome == OUT_INSERT ? 1 : 0;
+  for (int off = 16; off > 0; off >>= 1) ins += __shfl_xor_sync(FULL, ins, off);
+  const int n_true = ctl->n0 + ins;
+  if (n_true != r.n_b) {
+    const double rt = P.rho2[n_true];
+    conf = !(r.d2_in_max <= rt && r.d2_out_min > rt);
+    if (lane == 0) W.rec[b].n_b = n_true;
+  }
   const int* g_near = W.near_idx + (size_t)b * cap;
   for (int k = lane; k < r.K; k += 32) conf |= mark_sample(__ldcg(&W.wmin[g_near[k]]), round) < b;
   if (r.outcome == OUT_INSERT) {
@@ -278,7 +297,6 @@ __global__ void __launch_bounds__(128) k_wave_validate(Ctl* ctl, Batch Bt, Wave 
   conf = __any_sync(FULL, conf);
   if (lane == 0) {
     if (conf) atomicMin(&ctl->wave_F, b);
-    else if (r.outcome == OUT_NOFREE) atomicMin(&ctl->wave_F, b + 1);  // later samples assumed it would insert
   }
 }
 
