@@ -149,8 +149,8 @@ int krrt_timer_end(krrt_ctx* ctx, double* ms);
 /* profile mode: CUDA events around every neighbour-scan launch of krrt_grow (adds a little launch gap)  */
 int krrt_set_profile(krrt_ctx* ctx, int on);
 /* krrt_set_profile(ctx, 2): an event after every kernel of every round of krrt_grow (first 4096 rounds).
- * ms / launches [0..6] = k_batch_prepare, k_near_scan, k_steer_pairs, k_wave_decide, k_wave_validate, k_wave_apply,
- * k_commit; [7] = gaps between rounds (host read-back of the progress counter + enqueue)                  */
+ * ms / launches: [1] = k_round_scan, [3] = k_round_decide, [4] = k_round_validate, [5] = k_round_apply (others 0);
+ * [7] = gaps between rounds (host read-back of the progress counter + enqueue)                           */
 int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]);
 /* since krrt_set_start: out[0] = rounds whose validated prefix was committed in parallel, out[1] = rounds (or
  * single samples) committed by the sequential warp, out[2] = expansions committed in parallel; out[3..7] = what

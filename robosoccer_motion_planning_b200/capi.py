@@ -359,8 +359,8 @@ class Planner:
         self._ck(lib().krrt_timer_end(self.h, ctypes.byref(ms)))
         return ms.value
 
-    KERNELS = ("k_batch_prepare", "k_near_scan", "k_steer_pairs", "k_wave_decide", "k_wave_validate", "k_wave_apply",
-               "k_commit", "gap_between_rounds")
+    KERNELS = ("-", "k_round_scan", "-", "k_round_decide", "k_round_validate", "k_round_apply", "-",
+               "gap_between_rounds")
 
     def kernel_times(self):
         ms = np.zeros(8)

@@ -43,7 +43,6 @@ struct krrt_ctx {
   Params P{};
   int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the sequential commit (debugging / A-B timing)
   int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
-  int wave_warps = 4;         // deciding warps per CTA (bounded by the near list's shared memory)
   long long rounds_enqueued = 0;
   // profile level 2: an event after every kernel of every round (bounded), summed per kernel in krrt_kernel_times
   std::vector<cudaEvent_t> kev;
@@ -259,12 +258,8 @@ static int create_impl(krrt_ctx* ctx) {
   CK(cudaEventCreateWithFlags(&ctx->ev_group[1], cudaEventDisableTiming));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
-  {
-    const size_t per_warp = wave_warp_smem_bytes(B.near_cap);
-    ctx->wave_warps = (int)std::max<size_t>(1, std::min<size_t>(4, (size_t)200 * 1024 / per_warp));
-    CK(cudaFuncSetAttribute(k_wave_decide, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)(per_warp * ctx->wave_warps)));
-  }
+  CK(cudaFuncSetAttribute(k_round_decide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decide_smem_bytes(B.near_cap)));
+  CK(cudaFuncSetAttribute(k_round_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)commit_smem_bytes(B.near_cap)));
   Params& P = ctx->P;
   P.r = c.r;
   P.R2 = c.R * c.R;
@@ -282,8 +277,6 @@ static int create_impl(krrt_ctx* ctx) {
   P.goal_tol2 = c.goal_tol * c.goal_tol;
   P.rho2 = ctx->d_rho2;
   P.obs = ctx->d_obs;
-  const int commit_smem = (int)(sizeof(double4) * KRRT_MAX_OBS + (size_t)B.near_cap * (4 * 8 + 4 + 1) + 16);
-  CK(cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, commit_smem));
   return KRRT_OK;
 }
 
@@ -376,7 +369,11 @@ __global__ void k_reset_round(Ctl* ctl) {
   if (threadIdx.x == 0 && blockIdx.x == 0) ctl->round = 0;
 }
 
-__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g, int n_iter) {
+__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g, int n_iter, Batch Bt) {
+  for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {  // candidate lists start empty
+    Bt.count[b] = 0;
+    Bt.dup[b] = 0;
+  }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   ctl->iter_begin = ctl->iter;
   ctl->iter_target = ctl->iter + n_iter;
@@ -415,14 +412,16 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   State4 g = {0, 0, 0, 0};
   if (goal) g = State4{goal[0], goal[1], goal[2], goal[3]};
   CK(cudaEventRecord(ctx->ev0, st));
-  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g, n_iter);
+  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g, n_iter, ctx->Bt);
   ctx->launches++;
   const int B = ctx->Bt.B;
-  const int commit_smem = (int)(sizeof(double4) * KRRT_MAX_OBS + (size_t)ctx->Bt.near_cap * (4 * 8 + 4 + 1) + 16);
-  const int decide_smem = (int)(wave_warp_smem_bytes(ctx->Bt.near_cap) * ctx->wave_warps);
-  const int prep_threads = ((B + 31) / 32) * 32;
+  const int commit_smem = (int)commit_smem_bytes(ctx->Bt.near_cap);
+  const int decide_smem = (int)decide_smem_bytes(ctx->Bt.near_cap);
   const int max_ctas = ctx->prop.multiProcessorCount * 8;
-  const double* d_user = samples ? ctx->d_user : nullptr;
+  RoundCfg rcfg;
+  rcfg.wave_enabled = ctx->wave_enabled;
+  rcfg.wave_min_n = ctx->wave_min_n;
+  rcfg.user_samples = samples ? ctx->d_user : nullptr;
   // Rounds are data dependent (a wave round commits a validated prefix of its batch), so the host enqueues groups
   // of rounds sized from the progress seen so far and reads the control block back between groups; rounds
   // enqueued past the target find nothing left to do.
@@ -457,12 +456,11 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
         ctx->rounds_enqueued = 0;
       }
       if (mark(-1) != KRRT_OK) return KRRT_ERR_CUDA;
-      k_batch_prepare<<<1, prep_threads, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->wave_enabled, ctx->wave_min_n, d_user);
       ctx->rounds_enqueued++;
-      if (mark(0) != KRRT_OK) return KRRT_ERR_CUDA;
+      // scan grid: node tiles x sample chunks, enough CTAs to fill the machine even for a small tree
       const int n_up = (int)std::min<long long>(ctx->cfg.capacity, (long long)n_known + (long long)(k + 1) * B);
-      int ctas = (n_up + SCAN_NODES_PER_CTA - 1) / SCAN_NODES_PER_CTA;
-      ctas = std::max(1, std::min(ctas, max_ctas));
+      const int tiles = std::max(1, std::min((n_up + ROUND_THREADS - 1) / ROUND_THREADS, max_ctas));
+      const int chunks = std::max(1, std::min(8, (2 * ctx->prop.multiProcessorCount + tiles - 1) / tiles));
       if (ctx->profile) {
         while ((int)ctx->scan_events.size() < 2 * (scan_rounds + 1)) {
           cudaEvent_t e;
@@ -471,27 +469,20 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
         }
         CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds], st));
       }
-      k_near_scan<<<ctas, SCAN_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt);
+      k_round_scan<<<dim3(tiles, chunks), ROUND_THREADS, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, rcfg, ctx->T.pos, ctx->T.vel);
       if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds + 1], st));
       ++scan_rounds;
       if (mark(1) != KRRT_OK) return KRRT_ERR_CUDA;
-      dim3 sg((ctx->Bt.near_cap + STEER_THREADS - 1) / STEER_THREADS, B);
-      k_steer_pairs<<<sg, STEER_THREADS, 0, st>>>(ctx->d_ctl, ctx->T.pos, ctx->T.vel, ctx->Bt, ctx->P.r);
-      ctx->launches += 3;
-      if (mark(2) != KRRT_OK) return KRRT_ERR_CUDA;
+      k_round_decide<<<B, ROUND_THREADS, decide_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
+      if (mark(3) != KRRT_OK) return KRRT_ERR_CUDA;
       if (ctx->wave_enabled) {
-        k_wave_decide<<<(B + ctx->wave_warps - 1) / ctx->wave_warps, 128, decide_smem, st>>>(
-            ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, ctx->wave_warps);
-        if (mark(3) != KRRT_OK) return KRRT_ERR_CUDA;
-        k_wave_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->W);
+        k_round_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->W);
         if (mark(4) != KRRT_OK) return KRRT_ERR_CUDA;
-        k_wave_apply<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->T, ctx->Bt, ctx->W);
-        if (mark(5) != KRRT_OK) return KRRT_ERR_CUDA;
-        ctx->launches += 3;
+        ctx->launches++;
       }
-      k_commit<<<1, 32, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
-      if (mark(6) != KRRT_OK) return KRRT_ERR_CUDA;
-      ctx->launches++;
+      k_round_apply<<<B + 1, APPLY_THREADS, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
+      if (mark(5) != KRRT_OK) return KRRT_ERR_CUDA;
+      ctx->launches += 3;
     }
     CK(cudaMemcpyAsync(hp, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));

@@ -1,16 +1,12 @@
 // krrt_kernels.cuh — sm_100a kernels of the kinodynamic RRT* hot path.
 //
-// Single big tree (configs C1-C3): samples are counter-based (Philox), so the tree-independent work of a
-// whole batch of B future expansions is evaluated in parallel against the tree as it stands ("frozen"),
-// and a single warp then commits the B expansions strictly in order:
-//   k_batch_prepare  draw the B samples, static rejection flags, in-batch (sample-vs-earlier-sample) pairs
-//   k_near_scan      every frozen node vs every batch sample: 4-D distance, radius test, candidate append
-//   k_steer_pairs    tau*/c* of both directions for every candidate pair
-//   k_commit         in order: exact radius filter, parent choice, collision, insert, rewire, propagate
-// Every arithmetic operation a sequential planner would do is done with the same operands; only the point
-// in time differs, so trees are bit-identical with the CPU oracle whatever B is.
+// Single big tree (configs C1-C3): samples are counter-based (Philox), so the tree-independent work of a whole
+// batch of future expansions is evaluated in parallel against the tree as it stands ("frozen"); a validated prefix of
+// the batch is then committed in parallel (krrt_wave.cuh) or, while the tree is small, the batch is committed strictly
+// in order by one warp (round_finish below).  Every arithmetic operation a sequential planner would do is done with
+// the same operands; only the point in time differs, so trees are bit-identical with a sequential run.
 //
-// Batched small trees (configs C4/C5): k_plan_batch, one warp per query, tree in shared memory.
+// Batched small trees (configs C4/C5): k_plan_batch (krrt_batch.cuh), one warp per query, tree in shared memory.
 #pragma once
 #include "krrt_warp.cuh"
 
@@ -76,163 +72,6 @@ struct Batch {
 };
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void k_batch_prepare(Ctl* ctl, Params P, Batch Bt, int wave_enabled, int wave_min_n,
-                                const double* user_samples) {
-  __shared__ State4 ss[256];
-  __shared__ double s_rho2max;
-  const int b = threadIdx.x;
-  const int n0 = ctl->n;
-  const long long iter0 = ctl->iter;
-  const long long left = ctl->iter_target - iter0;
-  const int wave = wave_enabled && n0 >= wave_min_n;
-  int nb_req = Bt.B;
-  if (wave) nb_req = min(Bt.B, max(16, (2 * ctl->ema16) / 16 + 8));  // ~2x the prefix the last rounds committed
-  const int nb = (ctl->full || ctl->error || left <= 0) ? 0 : (int)min((long long)nb_req, left);
-  const int user_offset = (int)(iter0 - ctl->iter_begin);
-  __syncthreads();  // every thread has read the control block before thread 0 rewrites it
-  if (b == 0) {
-    ctl->n0 = n0;
-    ctl->nb = nb;
-    ctl->wave = wave;
-    ctl->wave_F = nb;
-    ctl->round += 1;
-    double mx = 0.0;
-    int hi = min(n0 + nb, P.capacity);
-    for (int k = n0; k <= hi; ++k) mx = fmax(mx, P.rho2[k]);
-    s_rho2max = mx;
-    ctl->rho2max = mx;
-    if (nb > 0) {
-      ctl->scan_pairs += (double)n0 * (double)nb;
-      ctl->scan_nodes += (double)n0;
-    }
-  }
-  State4 s = {0, 0, 0, 0};
-  if (b < nb) {
-    bool drawn = true;
-    if (user_samples) {
-      const double* u = user_samples + 4 * (size_t)(user_offset + b);
-      if (!(u[0] != u[0])) {
-        s.x = u[0]; s.y = u[1]; s.vx = u[2]; s.vy = u[3];
-        drawn = false;
-      }
-    }
-    if (drawn) {
-      State4 g = {ctl->goal[0], ctl->goal[1], ctl->goal[2], ctl->goal[3]};
-      s = draw_sample(P.sp, P.query_id, (uint64_t)(iter0 + b), ctl->has_goal != 0, g);
-    }
-    bool hit = false;
-    if (!P.dynamic) {
-      for (int j = 0; j < P.m; ++j) {
-        double dx = s.x - P.obs[j].x, dy = s.y - P.obs[j].y;
-        hit |= fma(dy, dy, dx * dx) < P.R2;
-      }
-    }
-    Bt.samples[b] = s;
-    Bt.reject[b] = hit ? 1 : 0;
-    Bt.map[b] = -1;
-    Bt.dup[b] = 0;
-    ss[b] = s;
-  }
-  __syncthreads();
-  if (b < nb) {
-    const double rmax = s_rho2max;
-    int cnt = 0;
-    for (int e = 0; e < b; ++e) {
-      double d = dist2(ss[e], s);
-      if (d <= rmax) {
-        if (cnt < Bt.near_cap) {
-          Bt.ref[(size_t)b * Bt.near_cap + cnt] = IN_BATCH | e;
-          Bt.d2[(size_t)b * Bt.near_cap + cnt] = d;
-        }
-        ++cnt;
-      }
-    }
-    Bt.count[b] = cnt;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// Neighbour scan: HBM/L2-bound read of the SoA states (32 B per node), B distance evaluations per node.
-// Each thread keeps two nodes in registers and walks the batch samples broadcast from shared memory.
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_NODES_PER_CTA = 2 * SCAN_THREADS;
-
-__global__ void __launch_bounds__(SCAN_THREADS) k_near_scan(const Ctl* ctl, const double2* __restrict__ pos,
-                                                              const double2* __restrict__ vel, Batch Bt) {
-  __shared__ State4 ss[256];
-  const int n0 = ctl->n0;
-  const int nb = ctl->nb;
-  if (nb == 0 || (long long)blockIdx.x * SCAN_NODES_PER_CTA >= n0) return;
-  const double rmax = ctl->rho2max;
-  for (int b = threadIdx.x; b < nb; b += SCAN_THREADS) ss[b] = Bt.samples[b];
-  __syncthreads();
-  for (long long base = (long long)blockIdx.x * SCAN_NODES_PER_CTA; base < n0;
-       base += (long long)gridDim.x * SCAN_NODES_PER_CTA) {
-    const int i0 = (int)base + threadIdx.x, i1 = i0 + SCAN_THREADS;
-    const bool v0 = i0 < n0, v1 = i1 < n0;
-    State4 a = {0, 0, 0, 0}, c = {0, 0, 0, 0};
-    if (v0) {
-      double2 p = pos[i0], v = vel[i0];
-      a.x = p.x; a.y = p.y; a.vx = v.x; a.vy = v.y;
-    }
-    if (v1) {
-      double2 p = pos[i1], v = vel[i1];
-      c.x = p.x; c.y = p.y; c.vx = v.x; c.vy = v.y;
-    }
-#pragma unroll 4
-    for (int b = 0; b < nb; ++b) {
-      const State4 s = ss[b];
-      double da = dist2(a, s), dc = dist2(c, s);
-      if (v0 && da <= rmax) {
-        if (da == 0.0) Bt.dup[b] = 1;
-        int slot = atomicAdd(&Bt.count[b], 1);
-        if (slot < Bt.near_cap) {
-          Bt.ref[(size_t)b * Bt.near_cap + slot] = i0;
-          Bt.d2[(size_t)b * Bt.near_cap + slot] = da;
-        }
-      }
-      if (v1 && dc <= rmax) {
-        if (dc == 0.0) Bt.dup[b] = 1;
-        int slot = atomicAdd(&Bt.count[b], 1);
-        if (slot < Bt.near_cap) {
-          Bt.ref[(size_t)b * Bt.near_cap + slot] = i1;
-          Bt.d2[(size_t)b * Bt.near_cap + slot] = dc;
-        }
-      }
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------
-constexpr int STEER_THREADS = 128;
-__global__ void __launch_bounds__(STEER_THREADS) k_steer_pairs(const Ctl* ctl, const double2* __restrict__ pos,
-                                                                 const double2* __restrict__ vel, Batch Bt,
-                                                                 double r) {
-  const int b = blockIdx.y;
-  if (b >= ctl->nb) return;
-  const int cnt = min(Bt.count[b], Bt.near_cap);
-  const int e = blockIdx.x * STEER_THREADS + threadIdx.x;
-  if (e >= cnt) return;
-  const size_t o = (size_t)b * Bt.near_cap + e;
-  const int ref = Bt.ref[o];
-  State4 x;
-  if (ref & IN_BATCH) {
-    x = Bt.samples[ref & ~IN_BATCH];
-  } else {
-    double2 p = pos[ref], v = vel[ref];
-    x.x = p.x; x.y = p.y; x.vx = v.x; x.vy = v.y;
-  }
-  const State4 s = Bt.samples[b];
-  double t, c;
-  steer(x, s, r, t, c);
-  Bt.tf[o] = t;
-  Bt.cf[o] = c;
-  steer(s, x, r, t, c);
-  Bt.tb[o] = t;
-  Bt.cb[o] = c;
-}
-
-// ---------------------------------------------------------------------------------------------------
 // Per-sample decision of a wave round (krrt_wave.cuh) and the conflict marks it is validated with.
 enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5 };
 constexpr int WAVE_QCAP = 2048;  // write-list capacity per sample (descendants of its rewired nodes)
@@ -271,9 +110,15 @@ __device__ __forceinline__ int mark_sample(unsigned m, unsigned round) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// In-order commit of one batch by a single warp.  Dynamic shared memory: near list (near_cap entries) + obstacles.
-__global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W) {
-  extern __shared__ __align__(16) unsigned char smem[];
+// End of a round, ONE warp: fold in the counters of the prefix the wave committed in parallel, or commit in order
+// (the whole batch while the tree is small; only the first sample when that sample needs the sequential path).
+// smem: obstacles + near list (commit_smem_bytes).
+__host__ __device__ inline size_t commit_smem_bytes(int near_cap) {
+  return sizeof(double4) * KRRT_MAX_OBS_DEV + (size_t)near_cap * (4 * 8 + 4 + 1) + 16;
+}
+
+__device__ __noinline__ void round_finish_body(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
+                                               const Wave& W, unsigned char* smem) {
   const int lane = lane_id();
   const int cap = Bt.near_cap;
   double4* s_obs = reinterpret_cast<double4*>(smem);
@@ -422,6 +267,16 @@ __global__ void __launch_bounds__(32) k_commit(Ctl* ctl, Params P, TreeView T, B
     ctl->last_sample[0] = s.x; ctl->last_sample[1] = s.y; ctl->last_sample[2] = s.vx; ctl->last_sample[3] = s.vy;
     const long long* sv = &st.iters;
     for (int k = 0; k < 10; ++k) ctl->stats[k] += sv[k];
+  }
+}
+
+__device__ __forceinline__ void round_finish(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
+                                             const Wave& W, unsigned char* smem) {
+  round_finish_body(ctl, P, T, Bt, W, smem);
+  __syncwarp();
+  for (int b = lane_id(); b < Bt.B; b += 32) {  // candidate lists of the next round start empty
+    Bt.count[b] = 0;
+    Bt.dup[b] = 0;
   }
 }
 
