@@ -225,24 +225,29 @@ def run_ours(args, rank, world, local_rank):
     h2d = obs.nbytes + 64
     d2h = 4 * ctl_bytes + min(path_len, 32) * 40 + 4 + 16
 
-    # ---- roofline of the neighbour scan (profile pass: CUDA events around every scan launch)
+    # ---- per-kernel shares and the roofline of the neighbour scan (profile pass: CUDA events after every kernel)
     peak, peak_src = peaks()
-    G.set_profile(1)
+    G.set_profile(2)
     flush_l2()
     plan_device_timed()
     lt = G.last_timing()
+    kt = G.kernel_times()
+    wave = G.wave_stats()
     G.set_profile(0)
+    ksum = sum(v["ms"] for v in kt.values()) or 1.0
+    shares = {k: round(v["ms"] / ksum, 4) for k, v in kt.items() if v["launches"]}
     scan_bytes = lt["scan_node_samples"] * 32.0
     achieved = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k_near_scan", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_round_scan", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": scan_bytes / max(1, lt["scan_launches"]),
                 "avg_launch_us": 1e3 * lt["scan_ms"] / max(1, lt["scan_launches"]),
-                "share_of_step": lt["scan_ms"] / lt["total_ms"] if lt["total_ms"] > 0 else None,
-                "note": "algorithmic bytes = 32 B x tree nodes x samples served by the launch (SURVEY §8d: N x 32 B per "
-                        "expansion); one launch serves a batch of samples from one pass over the states, so frac can "
-                        "exceed 1; trees <= 20k nodes (640 KB) are L2-resident"}
-
+                "share_of_step": shares.get("k_round_scan"),
+                "kernel_shares": shares,
+                "note": "algorithmic bytes = 32 B x tree nodes x samples served by the launch (SURVEY 8d: N x 32 B per "
+                        "expansion); a <= 20k-node tree is 640 KB, L2-resident, and a launch lasts ~10 us: this config is "
+                        "bound by the dependent fp64 / L2-latency chains of k_round_decide and k_round_apply, not by HBM "
+                        "(see c3_100k for the scan on a larger tree)"}
     # ---- batched queries (configs 3/4): one warp per query, sharded over ranks, NCCL all-gather of the results
     q_total = BATCH_Q * world
     lo, hi = sweep.shard_bounds(q_total, rank, world)
@@ -320,6 +325,7 @@ def run_ours(args, rank, world, local_rank):
         "roofline": roofline,
         "batched": batched,
         "tree_nodes": int(res["n_nodes"]), "solved": bool(res["solved"]), "cost": float(res["cost"]),
+        "rounds": wave,
     }
 
     if rank == 0 and world == 1:
@@ -348,18 +354,28 @@ def run_ours(args, rank, world, local_rank):
                                            "sample": f"{qs} of the {BATCH_Q} queries"}
         line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
                                                else "MISMATCH")
-        # config 3: single large tree, 100k iterations, static obstacles
+        # config 3: single large tree, 100k iterations, static obstacles (+ the 1M-iteration tree with --c3-1m)
         if not args.skip_c3:
-            G3 = capi.Planner(device=local_rank, capacity=100002, batch=args.batch)
-            G3.set_profile(1)
-            G3.set_obstacles(scenes.static_obstacles(), 0)
-            G3.set_start(start)
-            flush_l2()
-            G3.grow(None, 100000)
-            t3 = G3.last_timing()
-            line["c3_100k"] = {"expansions_per_sec": 100000 / (t3["total_ms"] * 1e-3), "nodes": G3.size,
+            for label, iters in (("c3_100k", 100000),) + ((("c3_1m", 1000000),) if args.c3_1m else ()):
+                G3 = capi.Planner(device=local_rank, capacity=iters + 2, batch=args.batch or 128)
+                G3.set_obstacles(scenes.static_obstacles(), 0)
+                G3.set_start(start)
+                flush_l2()
+                G3.grow(None, iters)
+                t_plain = G3.last_timing()["total_ms"]
+                G3.set_profile(2)
+                G3.set_start(start)
+                flush_l2()
+                G3.grow(None, iters)
+                t3 = G3.last_timing()
+                k3 = G3.kernel_times()
+                ks = sum(v["ms"] for v in k3.values()) or 1.0
+                line[label] = {"expansions_per_sec": iters / (t_plain * 1e-3), "ms": t_plain, "nodes": G3.size,
                                "scan_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
-                               "scan_share": t3["scan_ms"] / t3["total_ms"]}
+                               "scan_frac_of_hbm_peak": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9 / peak,
+                               "kernel_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["launches"]},
+                               "rounds": G3.wave_stats()}
+                G3.close()
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -374,6 +390,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=0, help="speculative batch size (0 = library default)")
     ap.add_argument("--skip-c3", action="store_true")
+    ap.add_argument("--c3-1m", action="store_true", help="also grow the 1M-iteration single tree (a few seconds)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
