@@ -33,12 +33,10 @@ def main():
         G.set_obstacles(scenes.static_obstacles(), 0)
         goal = None
     G.set_start(scenes.START)
-    if os.environ.get("KRRT_PROFILE2"):
-        G.set_profile(2)
     r = G.grow(goal, n_iter)
     print(mode, "n", G.size, "result", r, "ms", G.last_timing()["total_ms"], "launches", G.launch_count)
     print("wave", G.wave_stats())
-    if os.environ.get("KRRT_PROFILE2"):
+    if True:
         for k, v in G.kernel_times().items():
             print(f"  {k:20s} {v['ms']:9.3f} ms  {v['launches']:6d} launches  {1e3 * v['ms'] / max(1, v['launches']):8.2f} us avg")
 

@@ -359,8 +359,8 @@ class Planner:
         self._ck(lib().krrt_timer_end(self.h, ctypes.byref(ms)))
         return ms.value
 
-    KERNELS = ("-", "k_round_scan", "-", "k_round_decide", "k_round_validate", "k_round_apply", "-",
-               "gap_between_rounds")
+    # phases of the persistent k_grow kernel (device clocks of its last CTA, scaled to the call's device time)
+    KERNELS = ("scan", "steer", "decide", "validate", "apply", "sequential_windows", "-", "-")
 
     def kernel_times(self):
         ms = np.zeros(8)

@@ -14,7 +14,7 @@
 #include "../../include/krrt.h"
 #include "krrt_batch.cuh"
 #include "krrt_kernels.cuh"
-#include "krrt_wave.cuh"
+#include "krrt_grow.cuh"
 #include "krrt_ops.cuh"
 
 using namespace krrt;
@@ -41,17 +41,12 @@ struct krrt_ctx {
   Batch Bt{};
   Wave W{};
   Params P{};
-  int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the sequential commit (debugging / A-B timing)
+  int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the in-order commit (debugging / A-B timing)
   int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
-  long long rounds_enqueued = 0;
-  // profile level 2: an event after every kernel of every round (bounded), summed per kernel in krrt_kernel_times
-  std::vector<cudaEvent_t> kev;
-  std::vector<int> kev_kind;
-  double kernel_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  long long kernel_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  int level2 = 0;
-  Ctl* h_ctl = nullptr;       // pinned: progress read-back between groups of rounds
-  cudaEvent_t ev_group[2] = {nullptr, nullptr};
+  int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
+  unsigned long long* d_bar = nullptr;  // its grid barrier counter
+  double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
   size_t user_cap = 0;
   std::vector<void*> allocs;
@@ -68,7 +63,6 @@ struct krrt_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   cudaEvent_t tm0 = nullptr, tm1 = nullptr;
   bool profile = false;
-  std::vector<cudaEvent_t> scan_events;
   double last_total_ms = 0.0, last_scan_ms = 0.0;
   int64_t last_scan_launches = 0;
   double last_scan_node_samples = 0.0;
@@ -161,11 +155,6 @@ void krrt_destroy(krrt_ctx* ctx) {
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
-  for (cudaEvent_t e : ctx->scan_events) cudaEventDestroy(e);
-  for (cudaEvent_t e : ctx->kev) cudaEventDestroy(e);
-  if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
-  for (cudaEvent_t e : ctx->ev_group)
-    if (e) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->tm0) cudaEventDestroy(ctx->tm0);
   if (ctx->tm1) cudaEventDestroy(ctx->tm1);
@@ -178,8 +167,8 @@ static int create_impl(krrt_ctx* ctx) {
   const krrt_config& c = ctx->cfg;
   REQUIRE(c.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED, "only KRRT_F64 is implemented");
   REQUIRE(c.capacity >= 2 && c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad capacity / S / r / R");
-  REQUIRE(c.batch >= 1 && c.batch <= 256, KRRT_ERR_INVALID, "batch must be in [1,256]");
-  REQUIRE(c.near_cap >= 32 && c.near_cap <= 5632, KRRT_ERR_INVALID, "near_cap must be in [32,5632]");
+  REQUIRE(c.batch >= 1 && c.batch <= GROW_WMAX, KRRT_ERR_INVALID, "batch must be in [1,512]");
+  REQUIRE(c.near_cap >= 32 && c.near_cap <= 4096, KRRT_ERR_INVALID, "near_cap must be in [32,4096]");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev) {
@@ -253,13 +242,20 @@ static int create_impl(krrt_ctx* ctx) {
   CK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.dsc, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
-  CK(cudaMallocHost((void**)&ctx->h_ctl, 2 * sizeof(Ctl)));
-  CK(cudaEventCreateWithFlags(&ctx->ev_group[0], cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&ctx->ev_group[1], cudaEventDisableTiming));
+  CK(dev_alloc(ctx, &ctx->d_bar, (size_t)16));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
-  CK(cudaFuncSetAttribute(k_round_decide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decide_smem_bytes(B.near_cap)));
-  CK(cudaFuncSetAttribute(k_round_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)commit_smem_bytes(B.near_cap)));
+  {
+    const int dyn = (int)commit_smem_bytes(B.near_cap);
+    CK(cudaFuncSetAttribute(k_grow, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow, GROW_THREADS, dyn));
+    int coop = 0;
+    CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c.device));
+    REQUIRE(per_sm >= 1 && coop, KRRT_ERR_UNSUPPORTED, "k_grow does not fit one CTA per SM / no cooperative launch");
+    ctx->grow_grid = ctx->prop.multiProcessorCount;
+    if (const char* e = std::getenv("KRRT_GRID")) ctx->grow_grid = std::max(2, std::min(ctx->grow_grid, std::atoi(e)));
+  }
   Params& P = ctx->P;
   P.r = c.r;
   P.R2 = c.R * c.R;
@@ -288,7 +284,8 @@ int krrt_create(const krrt_config* c, krrt_ctx** out) {
   *out = nullptr;
   krrt_ctx* ctx = new krrt_ctx();
   ctx->cfg = *c;
-  if (ctx->cfg.batch == 0) ctx->cfg.batch = 64;
+  if (ctx->cfg.batch == 0) ctx->cfg.batch = 256;
+  if (const char* e = std::getenv("KRRT_WINDOW")) ctx->cfg.batch = std::max(1, std::min(GROW_WMAX, std::atoi(e)));
   if (ctx->cfg.near_cap == 0) ctx->cfg.near_cap = 1024;
   int rc = create_impl(ctx);
   if (rc != KRRT_OK) {
@@ -321,7 +318,6 @@ int krrt_timer_end(krrt_ctx* ctx, double* ms) {
 int krrt_set_profile(krrt_ctx* ctx, int on) {
   if (!ctx) return KRRT_ERR_INVALID;
   ctx->profile = on != 0;
-  ctx->level2 = on == 2;
   return KRRT_OK;
 }
 
@@ -365,22 +361,27 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   return KRRT_OK;
 }
 
-__global__ void k_reset_round(Ctl* ctl) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) ctl->round = 0;
-}
-
-__global__ void k_begin_grow(Ctl* ctl, int has_goal, State4 g, int n_iter, Batch Bt) {
-  for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {  // candidate lists start empty
+// before every k_grow launch: barrier counter, empty candidate lists, armed prefix slots; `first`: a new krrt_grow call
+__global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, unsigned long long* bar,
+                             int reset_round) {
+  for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {
     Bt.count[b] = 0;
     Bt.dup[b] = 0;
   }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  *bar = 0ull;
+  ctl->wave_Fs[0] = 0x7fffffff;
+  ctl->wave_Fs[1] = 0x7fffffff;
+  if (reset_round) ctl->round = 0;
+  if (!first) return;
   ctl->iter_begin = ctl->iter;
   ctl->iter_target = ctl->iter + n_iter;
   if (ctl->ema16 <= 0) ctl->ema16 = 16 * 16;
   ctl->full = 0;
   ctl->scan_pairs = 0.0;
   ctl->scan_nodes = 0.0;
+  ctl->windows = 0;
+  for (int k = 0; k < 8; ++k) ctl->phase_clk[k] = 0;
   ctl->has_goal = has_goal;
   ctl->goal[0] = g.x; ctl->goal[1] = g.y; ctl->goal[2] = g.vx; ctl->goal[3] = g.vy;
 }
@@ -412,126 +413,55 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   State4 g = {0, 0, 0, 0};
   if (goal) g = State4{goal[0], goal[1], goal[2], goal[3]};
   CK(cudaEventRecord(ctx->ev0, st));
-  k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, goal ? 1 : 0, g, n_iter, ctx->Bt);
-  ctx->launches++;
-  const int B = ctx->Bt.B;
-  const int commit_smem = (int)commit_smem_bytes(ctx->Bt.near_cap);
-  const int decide_smem = (int)decide_smem_bytes(ctx->Bt.near_cap);
-  const int max_ctas = ctx->prop.multiProcessorCount * 8;
-  RoundCfg rcfg;
-  rcfg.wave_enabled = ctx->wave_enabled;
-  rcfg.wave_min_n = ctx->wave_min_n;
-  rcfg.user_samples = samples ? ctx->d_user : nullptr;
-  // Rounds are data dependent (a wave round commits a validated prefix of its batch), so the host enqueues groups
-  // of rounds sized from the progress seen so far and reads the control block back between groups; rounds
-  // enqueued past the target find nothing left to do.
-  size_t kev_used = 0;
-  ctx->kev_kind.clear();
-  auto mark = [&](int kind) -> int {  // kind -1 = start of a round; else the kernel that just went in
-    if (!ctx->level2 || kev_used >= 8 * 4096) return KRRT_OK;
-    if (kev_used >= ctx->kev.size()) {
-      cudaEvent_t e;
-      CK(cudaEventCreate(&e));
-      ctx->kev.push_back(e);
+  GrowCfg gcfg;
+  gcfg.wave_enabled = ctx->wave_enabled;
+  gcfg.wave_min_n = ctx->wave_min_n;
+  gcfg.user_samples = samples ? ctx->d_user : nullptr;
+  gcfg.bar = ctx->d_bar;
+  const int dyn = (int)commit_smem_bytes(ctx->Bt.near_cap);
+  Ctl h;
+  // ONE persistent kernel does the whole call; it only comes back early when the 23-bit epoch of the conflict marks
+  // is used up (8 M sub-rounds): clear the marks and go on
+  for (int launch = 0;; ++launch) {
+    const bool wrap = launch > 0;
+    if (wrap) {
+      const size_t cap = (size_t)ctx->cfg.capacity;
+      CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
+      CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
+      CK(cudaMemsetAsync(ctx->W.dsc, 0, sizeof(unsigned) * cap, st));
     }
-    CK(cudaEventRecord(ctx->kev[kev_used++], st));
-    ctx->kev_kind.push_back(kind);
-    return KRRT_OK;
-  };
-  long long consumed = 0;
-  int n_known = ctx->n_upper;
-  double per_round = (ctx->wave_enabled && n_known >= ctx->wave_min_n) ? 16.0 : (double)B;
-  int scan_rounds = 0;
-  Ctl* hp = ctx->h_ctl;
-  while (consumed < n_iter) {
-    const long long left = n_iter - consumed;
-    const int rounds = (int)std::max<long long>(1, std::min<long long>(64, (long long)std::ceil((double)left / per_round)));
-    for (int k = 0; k < rounds; ++k) {
-      if (ctx->rounds_enqueued >= (1ll << 23) - 2) {  // mark epochs are 23 bits: start over with clean marks
-        const size_t cap = (size_t)ctx->cfg.capacity;
-        CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
-        CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
-        CK(cudaMemsetAsync(ctx->W.dsc, 0, sizeof(unsigned) * cap, st));
-        k_reset_round<<<1, 32, 0, st>>>(ctx->d_ctl);
-        ctx->rounds_enqueued = 0;
-      }
-      if (mark(-1) != KRRT_OK) return KRRT_ERR_CUDA;
-      ctx->rounds_enqueued++;
-      // scan grid: node tiles x sample chunks, enough CTAs to fill the machine even for a small tree
-      const int n_up = (int)std::min<long long>(ctx->cfg.capacity, (long long)n_known + (long long)(k + 1) * B);
-      const int tiles = std::max(1, std::min((n_up + ROUND_THREADS - 1) / ROUND_THREADS, max_ctas));
-      const int chunks = std::max(1, std::min(8, (2 * ctx->prop.multiProcessorCount + tiles - 1) / tiles));
-      if (ctx->profile) {
-        while ((int)ctx->scan_events.size() < 2 * (scan_rounds + 1)) {
-          cudaEvent_t e;
-          CK(cudaEventCreate(&e));
-          ctx->scan_events.push_back(e);
-        }
-        CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds], st));
-      }
-      k_round_scan<<<dim3(tiles, chunks), ROUND_THREADS, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, rcfg, ctx->T.pos, ctx->T.vel);
-      if (ctx->profile) CK(cudaEventRecord(ctx->scan_events[2 * scan_rounds + 1], st));
-      ++scan_rounds;
-      if (mark(1) != KRRT_OK) return KRRT_ERR_CUDA;
-      k_round_decide<<<B, ROUND_THREADS, decide_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
-      if (mark(3) != KRRT_OK) return KRRT_ERR_CUDA;
-      if (ctx->wave_enabled) {
-        k_round_validate<<<(B * 32 + 127) / 128, 128, 0, st>>>(ctx->d_ctl, ctx->P, ctx->Bt, ctx->W);
-        if (mark(4) != KRRT_OK) return KRRT_ERR_CUDA;
-        ctx->launches++;
-      }
-      k_round_apply<<<B + 1, APPLY_THREADS, commit_smem, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W);
-      if (mark(5) != KRRT_OK) return KRRT_ERR_CUDA;
-      ctx->launches += 3;
-    }
-    CK(cudaMemcpyAsync(hp, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    CK(cudaGetLastError());
-    const long long now = hp->iter - hp->iter_begin;
-    per_round = std::max(1.0, (double)(now - consumed) / rounds);
-    consumed = now;
-    n_known = hp->n;
-    if (hp->full || hp->error) break;
+    k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);
+    void* args[] = {(void*)&ctx->d_ctl, (void*)&ctx->P, (void*)&ctx->T, (void*)&ctx->Bt, (void*)&ctx->W, (void*)&gcfg};
+    CK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(ctx->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
+    ctx->launches += 2;
+    int rc = fetch_ctl(ctx, &h);
+    if (rc != KRRT_OK) return rc;
+    if (h.full || h.error || h.iter >= h.iter_target) break;
+    REQUIRE(h.round >= (1u << 23) - 2, KRRT_ERR_CUDA, "k_grow returned before its target");
   }
   k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
   ctx->launches++;
   CK(cudaEventRecord(ctx->ev1, st));
   CK(cudaGetLastError());
-  Ctl h;
-  int rc = fetch_ctl(ctx, &h);
-  if (rc != KRRT_OK) return rc;
+  {
+    int rc = fetch_ctl(ctx, &h);
+    if (rc != KRRT_OK) return rc;
+  }
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->last_total_ms = ms;
-  ctx->last_scan_ms = 0.0;
-  ctx->last_scan_launches = 0;
   ctx->last_scan_node_samples = h.scan_pairs;
-  if (ctx->profile) {
-    double acc = 0.0;
-    for (int k = 0; k < scan_rounds; ++k) {
-      float t = 0.f;
-      CK(cudaEventElapsedTime(&t, ctx->scan_events[2 * k], ctx->scan_events[2 * k + 1]));
-      acc += t;
+  {
+    // phase clocks of the kernel's last CTA -> shares of the call's device time
+    double tot = 0.0;
+    for (int k = 0; k < 8; ++k) tot += (double)h.phase_clk[k];
+    const long long subs = h.rounds_wave + h.rounds_seq;
+    for (int k = 0; k < 8; ++k) {
+      ctx->phase_ms[k] = tot > 0.0 ? ms * (double)h.phase_clk[k] / tot : 0.0;
+      ctx->phase_n[k] = k < 2 ? h.windows : (k < 5 ? subs : 0);
     }
-    ctx->last_scan_ms = acc;
-    ctx->last_scan_launches = scan_rounds;
-  }
-  if (ctx->level2) {
-    for (int k = 0; k < 8; ++k) { ctx->kernel_ms[k] = 0.0; ctx->kernel_n[k] = 0; }
-    for (size_t k = 1; k < kev_used; ++k) {
-      const int kind = ctx->kev_kind[k];
-      if (kind < 0) {  // gap between rounds (host sync + enqueue, or nothing when rounds are back to back)
-        float t = 0.f;
-        CK(cudaEventElapsedTime(&t, ctx->kev[k - 1], ctx->kev[k]));
-        ctx->kernel_ms[7] += t;
-        ctx->kernel_n[7]++;
-        continue;
-      }
-      float t = 0.f;
-      CK(cudaEventElapsedTime(&t, ctx->kev[k - 1], ctx->kev[k]));
-      ctx->kernel_ms[kind] += t;
-      ctx->kernel_n[kind]++;
-    }
+    ctx->last_scan_ms = ctx->phase_ms[0];
+    ctx->last_scan_launches = h.windows;
   }
   if (h.error) {
     ctx->err = h.error == KRRT_ERR_NEAR_OVERFLOW ? "near set exceeded near_cap; raise krrt_config.near_cap" : "device error";
@@ -589,8 +519,8 @@ int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out) {
 int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]) {
   if (!ctx || !ms || !launches) return KRRT_ERR_INVALID;
   for (int k = 0; k < 8; ++k) {
-    ms[k] = ctx->kernel_ms[k];
-    launches[k] = ctx->kernel_n[k];
+    ms[k] = ctx->phase_ms[k];
+    launches[k] = ctx->phase_n[k];
   }
   return KRRT_OK;
 }

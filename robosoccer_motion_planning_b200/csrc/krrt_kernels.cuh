@@ -1,10 +1,11 @@
 // krrt_kernels.cuh — sm_100a kernels of the kinodynamic RRT* hot path.
 //
 // Single big tree (configs C1-C3): samples are counter-based (Philox), so the tree-independent work of a whole
-// batch of future expansions is evaluated in parallel against the tree as it stands ("frozen"); a validated prefix of
-// the batch is then committed in parallel (krrt_wave.cuh) or, while the tree is small, the batch is committed strictly
-// in order by one warp (round_finish below).  Every arithmetic operation a sequential planner would do is done with
-// the same operands; only the point in time differs, so trees are bit-identical with a sequential run.
+// window of future expansions is evaluated in parallel against the tree as it stands ("frozen"); validated prefixes of
+// the window are then committed in parallel or, while the tree is small, the window is committed strictly in order by
+// one warp (krrt_grow.cuh: one persistent kernel per krrt_grow call).  Every arithmetic operation a sequential planner
+// would do is done with the same operands; only the point in time differs, so trees are bit-identical with a
+// sequential run.
 //
 // Batched small trees (configs C4/C5): k_plan_batch (krrt_batch.cuh), one warp per query, tree in shared memory.
 #pragma once
@@ -30,15 +31,19 @@ struct Ctl {  // device-resident control block of one single-tree context
   double goal[4];
   double last_sample[4];
   long long stats[10];
-  // round control (all decided on the device: the host only enqueues rounds until iter == iter_target)
+  // round control (all decided on the device: k_grow runs until iter == iter_target)
   long long iter_begin;   // iteration counter when the current krrt_grow call began (index base of user samples)
   long long iter_target;  // iteration counter at which the current krrt_grow call is complete
-  unsigned round;         // round id: epoch of the conflict marks (krrt_wave.cuh)
+  unsigned round;         // sub-round id: epoch of the conflict marks (krrt_grow.cuh)
   int wave;               // this round commits a validated prefix in parallel (tree large enough)
   int wave_F;             // length of that prefix
   int ema16;              // 16 x running mean of the prefix length: sizes the next round's batch
   long long rounds_wave, rounds_seq, wave_committed;  // diagnostics since set_start
   long long why[5];  // what ended the prefix: batch end, in-batch neighbour, needs sequential path, no free parent, read/write conflict
+  int wave_Fs[2];         // prefix length of the current sub-round (slot = round & 1; the other slot is being re-armed)
+  long long windows;      // windows scanned since the current krrt_grow call began
+  long long phase_clk[8]; // SM clocks the last CTA spent per phase since the call began: 0 scan, 1 steer, 2 decide,
+                          // 3 validate, 4 apply + finish, 5 sequential windows
 };
 
 struct Params {
@@ -72,7 +77,7 @@ struct Batch {
 };
 
 // ---------------------------------------------------------------------------------------------------
-// Per-sample decision of a wave round (krrt_wave.cuh) and the conflict marks it is validated with.
+// Per-sample decision of a sub-round (krrt_grow.cuh) and the conflict marks it is validated with.
 enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5 };
 constexpr int WAVE_QCAP = 2048;  // write-list capacity per sample (descendants of its rewired nodes)
 
@@ -109,175 +114,9 @@ __device__ __forceinline__ int mark_sample(unsigned m, unsigned round) {
   return (m >> 9) == round ? 511 - (int)(m & 511u) : 0x7fffffff;
 }
 
-// ---------------------------------------------------------------------------------------------------
-// End of a round, ONE warp: fold in the counters of the prefix the wave committed in parallel, or commit in order
-// (the whole batch while the tree is small; only the first sample when that sample needs the sequential path).
-// smem: obstacles + near list (commit_smem_bytes).
+// shared-memory scratch of the in-order commit warp (krrt_grow.cuh: seq_commit): obstacles + near list
 __host__ __device__ inline size_t commit_smem_bytes(int near_cap) {
   return sizeof(double4) * KRRT_MAX_OBS_DEV + (size_t)near_cap * (4 * 8 + 4 + 1) + 16;
-}
-
-__device__ __noinline__ void round_finish_body(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
-                                               const Wave& W, unsigned char* smem) {
-  const int lane = lane_id();
-  const int cap = Bt.near_cap;
-  double4* s_obs = reinterpret_cast<double4*>(smem);
-  NearView N;
-  N.cf = reinterpret_cast<double*>(s_obs + KRRT_MAX_OBS_DEV);
-  N.tf = N.cf + cap;
-  N.cb = N.tf + cap;
-  N.tb = N.cb + cap;
-  N.idx = reinterpret_cast<int*>(N.tb + cap);
-  N.tried = reinterpret_cast<unsigned char*>(N.idx + cap);
-  int nb = ctl->nb;
-  if (nb == 0 || ctl->error) return;
-  if (ctl->wave) {
-    const int F = ctl->wave_F;
-    if (F > 0) {  // the first F samples were committed in parallel (k_wave_apply): fold their counters in
-      long long v[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-      for (int b = lane; b < F; b += 32) {
-        const WaveRec r = W.rec[b];
-        v[0] += 1;
-        if (r.outcome == OUT_INSERT) {
-          v[1] += 1; v[5] += r.nrew; v[6] += r.nwl; v[7] += r.K; v[8] += 2 * r.K - 1; v[9] += r.collide_calls;
-        } else if (r.outcome == OUT_REJECT) {
-          v[2] += 1;
-        } else if (r.outcome == OUT_DUP) {
-          v[3] += 1;
-        } else {  // OUT_NOFREE
-          v[4] += 1; v[7] += r.K; v[8] += r.K; v[9] += r.collide_calls;
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < 10; ++k)
-        for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], off);
-      if (lane == 0) {
-        ctl->n += (int)v[1];
-        ctl->iter += F;
-        for (int k = 0; k < 10; ++k) ctl->stats[k] += v[k];
-        const State4 ls = Bt.samples[F - 1];
-        ctl->last_sample[0] = ls.x; ctl->last_sample[1] = ls.y; ctl->last_sample[2] = ls.vx; ctl->last_sample[3] = ls.vy;
-        ctl->ema16 = (3 * ctl->ema16 + 16 * F) / 4;
-        ctl->rounds_wave += 1;
-        ctl->wave_committed += F;
-        int why = 0;
-        if (F < nb) {
-          const int o = W.rec[F].outcome;
-          why = o == OUT_CONFLICT ? 1 : o == OUT_COMPLEX ? 2 : (o == OUT_NOFREE ? 3 : 4);
-        }
-        ctl->why[why] += 1;
-      }
-      return;
-    }
-    nb = 1;  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
-    if (lane == 0) ctl->ema16 = (3 * ctl->ema16 + 16) / 4;
-  }
-  if (lane == 0) ctl->rounds_seq += 1;
-  for (int j = lane; j < P.m; j += 32) s_obs[j] = P.obs[j];
-  __syncwarp();
-  EnvView E = {s_obs, P.m, P.dynamic, P.R2, P.S};
-
-  Stats st = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-  int n = ctl->n;
-  long long iter = ctl->iter;
-  int full = 0, error = 0;
-  State4 s = {0, 0, 0, 0};
-  for (int b = 0; b < nb; ++b) {
-    s = Bt.samples[b];
-    ++iter;
-    st.iters++;
-    if (!P.dynamic && Bt.reject[b]) {
-      st.fail_reject++;
-      continue;
-    }
-    if (n >= P.capacity) {
-      full = 1;
-      break;
-    }
-    const int cnt = Bt.count[b];
-    if (cnt > cap) {
-      error = 4;  // KRRT_ERR_NEAR_OVERFLOW
-      --iter;
-      st.iters--;
-      break;
-    }
-    const double rho2n = P.rho2[n];
-    int K = 0;
-    bool dup = false;
-    for (int base = 0; base < cnt; base += 32) {
-      const int e = base + lane;
-      bool valid = false;
-      int node = -1;
-      size_t o = (size_t)b * cap + e;
-      if (e < cnt) {
-        int ref = Bt.ref[o];
-        double d = Bt.d2[o];
-        node = (ref & IN_BATCH) ? Bt.map[ref & ~IN_BATCH] : ref;
-        valid = node >= 0 && d <= rho2n;
-        dup |= valid && d == 0.0;
-      }
-      unsigned mk = __ballot_sync(FULL, valid);
-      if (valid) {
-        int k = K + __popc(mk & ((1u << lane) - 1));
-        N.idx[k] = node;
-        N.cf[k] = Bt.cf[o];
-        N.tf[k] = Bt.tf[o];
-        N.cb[k] = Bt.cb[o];
-        N.tb[k] = Bt.tb[o];
-      }
-      K += __popc(mk);
-    }
-    if (__any_sync(FULL, dup)) {
-      st.fail_dup++;
-      continue;
-    }
-    if (K == 0) {  // empty near set: exact nearest over the whole tree (rare once the tree is dense)
-      int ni;
-      double nd2;
-      warp_nearest(T, n, s, ni, nd2);
-      if (nd2 == 0.0) {
-        st.fail_dup++;
-        continue;
-      }
-      if (lane == 0) {
-        double t, c;
-        steer(load_state(T, ni), s, P.r, t, c);
-        N.idx[0] = ni;
-        N.cf[0] = c;
-        N.tf[0] = t;
-        N.cb[0] = 0.0;
-        N.tb[0] = 0.0;
-      }
-      K = 1;
-    }
-    __syncwarp();
-    st.sum_near += K;
-    int nw = warp_commit(T, N, K, n, s, E, st);
-    if (nw >= 0) {
-      if (lane == 0) Bt.map[b] = nw;
-      n = nw + 1;
-    }
-    __syncwarp();
-  }
-  if (lane == 0) {
-    ctl->n = n;
-    ctl->iter = iter;
-    ctl->full = full;
-    if (error) ctl->error = error;
-    ctl->last_sample[0] = s.x; ctl->last_sample[1] = s.y; ctl->last_sample[2] = s.vx; ctl->last_sample[3] = s.vy;
-    const long long* sv = &st.iters;
-    for (int k = 0; k < 10; ++k) ctl->stats[k] += sv[k];
-  }
-}
-
-__device__ __forceinline__ void round_finish(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
-                                             const Wave& W, unsigned char* smem) {
-  round_finish_body(ctl, P, T, Bt, W, smem);
-  __syncwarp();
-  for (int b = lane_id(); b < Bt.B; b += 32) {  // candidate lists of the next round start empty
-    Bt.count[b] = 0;
-    Bt.dup[b] = 0;
-  }
 }
 
 // goal lookup after a grow call: cheapest node within goal_tol of the goal (rrt.goalIndex(), robosoccer_visual.hpp:19)
