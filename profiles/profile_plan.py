@@ -36,6 +36,9 @@ def main():
     r = G.grow(goal, n_iter)
     print(mode, "n", G.size, "result", r, "ms", G.last_timing()["total_ms"], "launches", G.launch_count)
     print("wave", G.wave_stats())
+    subs = max(1, sum(G.wave_stats()[k] for k in ("rounds_parallel", "rounds_sequential")))
+    print("dbg cycles per sub-round", [int(v) // subs for v in G.debug_clocks()])
+    print("stats", G.stats())
     if True:
         for k, v in G.kernel_times().items():
             print(f"  {k:20s} {v['ms']:9.3f} ms  {v['launches']:6d} launches  {1e3 * v['ms'] / max(1, v['launches']):8.2f} us avg")

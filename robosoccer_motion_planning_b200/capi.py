@@ -29,7 +29,7 @@ EXPORTS = (
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
-    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats",
+    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
 )
 
 
@@ -117,6 +117,7 @@ def lib():
     L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
     L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
     L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]
+    L.krrt_debug_clocks.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_launch_count.argtypes = [P]
@@ -374,6 +375,11 @@ class Planner:
         return {"rounds_parallel": int(o[0]), "rounds_sequential": int(o[1]), "expansions_parallel": int(o[2]),
                 "prefix_ended_by": {"batch_end": int(o[3]), "in_batch_neighbour": int(o[4]), "sequential_sample": int(o[5]),
                                     "no_free_parent": int(o[6]), "rw_conflict": int(o[7])}}
+
+    def debug_clocks(self):
+        o = np.zeros(16, dtype=np.int64)
+        self._ck(lib().krrt_debug_clocks(self.h, o.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))))
+        return o
 
     def set_profile(self, on):
         self._ck(lib().krrt_set_profile(self.h, int(on)))

@@ -34,7 +34,7 @@ __host__ __device__ inline size_t batch_warp_smem_bytes(int cap, int m) {
   b += (size_t)cap * 16 * 2;                        // pos, vel
   b += (size_t)(m > 0 ? m : 1) * 32;                // obstacles
   b += (size_t)cap * 8 * 8;                         // ctc, tim, ecost, etime, cf, tf, cb, tb
-  b += (size_t)cap * 4 * 6;                         // parent, head, next, prev, queue, near idx
+  b += (size_t)cap * 4 * 6;                         // link (first child, next sibling), parent, prev, queue, near idx
   b += ((size_t)cap + 15) / 16 * 16;                // tried
   return (b + 15) / 16 * 16;
 }
@@ -58,10 +58,9 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
   N.tf = N.cf + cap;
   N.cb = N.tf + cap;
   N.tb = N.cb + cap;
-  T.parent = reinterpret_cast<int*>(N.tb + cap);
-  T.head = T.parent + cap;
-  T.next = T.head + cap;
-  T.prev = T.next + cap;
+  T.link = reinterpret_cast<int2*>(N.tb + cap);
+  T.parent = reinterpret_cast<int*>(T.link + cap);
+  T.prev = T.parent + cap;
   T.queue = T.prev + cap;
   N.idx = T.queue + cap;
   N.tried = reinterpret_cast<unsigned char*>(N.idx + cap);
@@ -87,7 +86,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       T.vel[0] = make_double2(xs[2], xs[3]);
       T.parent[0] = -1;
       T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
-      T.head[0] = -1; T.next[0] = -1; T.prev[0] = -1;
+      T.link[0] = make_int2(-1, -1); T.prev[0] = -1;
     }
     __syncwarp();
     int n = 1;

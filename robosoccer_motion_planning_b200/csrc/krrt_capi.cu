@@ -44,7 +44,7 @@ struct krrt_ctx {
   int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the in-order commit (debugging / A-B timing)
   int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
   int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
-  unsigned long long* d_bar = nullptr;  // its grid barrier counter
+  GridBar* d_bar = nullptr;    // its two grid barriers
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
@@ -195,8 +195,7 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &ctx->T.ecost, cap));
   CK(dev_alloc(ctx, &ctx->T.etime, cap));
   CK(dev_alloc(ctx, &ctx->T.parent, cap));
-  CK(dev_alloc(ctx, &ctx->T.head, cap));
-  CK(dev_alloc(ctx, &ctx->T.next, cap));
+  CK(dev_alloc(ctx, &ctx->T.link, cap));
   CK(dev_alloc(ctx, &ctx->T.prev, cap));
   CK(dev_alloc(ctx, &ctx->T.queue, cap));
   ctx->T.cap = c.capacity;
@@ -230,23 +229,21 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &B.cb, bc));
   Wave& W = ctx->W;
   CK(dev_alloc(ctx, &W.rec, (size_t)B.B));
-  CK(dev_alloc(ctx, &W.near_idx, bc));
-  CK(dev_alloc(ctx, &W.rew_node, bc));
-  CK(dev_alloc(ctx, &W.rew_slot, bc));
-  CK(dev_alloc(ctx, &W.wl, (size_t)B.B * WAVE_QCAP));
   CK(dev_alloc(ctx, &W.wmin, cap));
   CK(dev_alloc(ctx, &W.amin, cap));
-  CK(dev_alloc(ctx, &W.dsc, cap));
   CK(dev_alloc(ctx, &W.lock, cap));
+#ifdef KRRT_DEBUG_CLK
+  CK(dev_alloc(ctx, &W.dbg_log, (size_t)8 * ((1 << 20) + 1)));
+  CK(cudaMemsetAsync(W.dbg_log, 0, sizeof(int) * 8, ctx->stream));
+#endif
   CK(cudaMemsetAsync(W.wmin, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, ctx->stream));
-  CK(cudaMemsetAsync(W.dsc, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
-  CK(dev_alloc(ctx, &ctx->d_bar, (size_t)16));
+  CK(dev_alloc(ctx, &ctx->d_bar, (size_t)2));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
   {
-    const int dyn = (int)commit_smem_bytes(B.near_cap);
+    const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));
     CK(cudaFuncSetAttribute(k_grow, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
     int per_sm = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow, GROW_THREADS, dyn));
@@ -340,7 +337,7 @@ __global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
   T.vel[0] = make_double2(x0.vx, x0.vy);
   T.parent[0] = -1;
   T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
-  T.head[0] = -1; T.next[0] = -1; T.prev[0] = -1;
+  T.link[0] = make_int2(-1, -1); T.prev[0] = -1;
   Ctl z;
   memset(&z, 0, sizeof(z));
   z.n = 1;
@@ -362,14 +359,15 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
 }
 
 // before every k_grow launch: barrier counter, empty candidate lists, armed prefix slots; `first`: a new krrt_grow call
-__global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, unsigned long long* bar,
+__global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, GridBar* bar,
                              int reset_round) {
   for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {
     Bt.count[b] = 0;
     Bt.dup[b] = 0;
   }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  *bar = 0ull;
+  bar[0].arrive = 0ull;
+  bar[1].arrive = 0ull;
   ctl->wave_Fs[0] = 0x7fffffff;
   ctl->wave_Fs[1] = 0x7fffffff;
   if (reset_round) ctl->round = 0;
@@ -382,6 +380,8 @@ __global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_
   ctl->scan_nodes = 0.0;
   ctl->windows = 0;
   for (int k = 0; k < 8; ++k) ctl->phase_clk[k] = 0;
+  for (int k = 0; k < 16; ++k) ctl->dbg_clk[k] = 0;
+  for (int k = 0; k < 3 * 160; ++k) (&ctl->dbg_cta[0][0])[k] = 0;
   ctl->has_goal = has_goal;
   ctl->goal[0] = g.x; ctl->goal[1] = g.y; ctl->goal[2] = g.vx; ctl->goal[3] = g.vy;
 }
@@ -418,7 +418,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   gcfg.wave_min_n = ctx->wave_min_n;
   gcfg.user_samples = samples ? ctx->d_user : nullptr;
   gcfg.bar = ctx->d_bar;
-  const int dyn = (int)commit_smem_bytes(ctx->Bt.near_cap);
+  const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(ctx->Bt.near_cap));
   Ctl h;
   // ONE persistent kernel does the whole call; it only comes back early when the 23-bit epoch of the conflict marks
   // is used up (8 M sub-rounds): clear the marks and go on
@@ -428,7 +428,6 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       const size_t cap = (size_t)ctx->cfg.capacity;
       CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
-      CK(cudaMemsetAsync(ctx->W.dsc, 0, sizeof(unsigned) * cap, st));
     }
     k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);
     void* args[] = {(void*)&ctx->d_ctl, (void*)&ctx->P, (void*)&ctx->T, (void*)&ctx->Bt, (void*)&ctx->W, (void*)&gcfg};
@@ -521,6 +520,34 @@ int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]) {
   for (int k = 0; k < 8; ++k) {
     ms[k] = ctx->phase_ms[k];
     launches[k] = ctx->phase_n[k];
+  }
+  return KRRT_OK;
+}
+
+int krrt_debug_clocks(krrt_ctx* ctx, int64_t out[16]) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  for (int k = 0; k < 16; ++k) out[k] = h.dbg_clk[k];
+  if (const char* path = std::getenv("KRRT_DEBUG_LOG")) {
+    if (ctx->W.dbg_log) {
+      int n = 0;
+      cudaMemcpy(&n, ctx->W.dbg_log, sizeof(int), cudaMemcpyDeviceToHost);
+      n = std::min(n, 1 << 20);
+      std::vector<int> buf((size_t)8 * n);
+      cudaMemcpy(buf.data(), ctx->W.dbg_log + 8, sizeof(int) * 8 * (size_t)n, cudaMemcpyDeviceToHost);
+      if (FILE* f = std::fopen(path, "wb")) {
+        std::fwrite(buf.data(), sizeof(int), buf.size(), f);
+        std::fclose(f);
+      }
+    }
+  }
+  if (std::getenv("KRRT_DEBUG_DUMP")) {
+    for (int c = 0; c < 160; ++c)
+      if (h.dbg_cta[0][c] || h.dbg_cta[2][c])
+        std::printf("cta %3d decide %10lld validate %10lld apply %10lld\n", c, h.dbg_cta[0][c], h.dbg_cta[1][c], h.dbg_cta[2][c]);
   }
   return KRRT_OK;
 }

@@ -23,7 +23,7 @@
 // near radius, and b's near set is unchanged at the radius of the tree size it really sees (earlier samples that
 // found no collision-free parent did not insert).  For such a prefix the sequential outcome IS the speculated one.
 // A sample that cannot be decided this way (empty near set -> global nearest, a rewired subtree larger than
-// WAVE_QCAP, a near node inside one of its own rewired subtrees) is committed alone by one warp; while the tree is
+// GROW_QCAP, a near node inside one of its own rewired subtrees) is committed alone by one warp; while the tree is
 // small (conflicts everywhere) whole windows are.  Trees are bit-identical to the in-order commit whatever the
 // prefix lengths are.
 #pragma once
@@ -35,13 +35,7 @@ constexpr int GROW_THREADS = 256;
 constexpr int GROW_WMAX = 512;    // window cap
 constexpr int GROW_LEVELS = 62;   // BFS depth below the rewired nodes that the parallel path handles
 constexpr int GROW_SEQ_WINDOW = 64;
-
-struct GrowCfg {
-  int wave_enabled;
-  int wave_min_n;
-  const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
-  unsigned long long* bar;     // grid barrier counter (zero at launch)
-};
+constexpr int GROW_SMAX = 64;     // edge sample counts up to this use a shared table of h = p / (S - 1)
 
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
   unsigned long long v;
@@ -49,16 +43,32 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
   return v;
 }
 
-// all CTAs are co-resident (cooperative launch, one per SM): arrive with a release, spin with an acquire
-__device__ __forceinline__ void grid_barrier(unsigned long long* bar, unsigned long long& target) {
+// Grid barrier over n co-resident CTAs (cooperative launch, one CTA per SM): one counter, red.release to arrive
+// (MEMBAR.ALL.GPU + REDG), ld.acquire to poll (LDG.STRONG.GPU + CCTL.IVALL, so later plain loads miss L1).  Measured on
+// B200 (tests/native/barrier_bench.cu): 2200 cycles with 64 CTAs, against 3000 for fence + atomicAdd + spin + fence
+// and 2400 for cooperative_groups grid.sync().
+// `relaxed`: CTAs that only wait for a far-away event (the end of the window's sub-rounds) back off between polls.
+struct GridBar {
+  unsigned long long arrive, pad0[15];
+};
+struct BarState {
+  unsigned long long arrived;
+};
+struct GrowCfg {
+  int wave_enabled;
+  int wave_min_n;
+  const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
+  GridBar* bar;                // [0] all CTAs, [1] the CTAs that take part in a window's sub-rounds (zero at launch)
+};
+
+__device__ __forceinline__ void grid_barrier(GridBar* bar, BarState& st, int n, bool relaxed) {
   __syncthreads();
-  target += gridDim.x;
+  st.arrived += (unsigned long long)n;
   if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(bar, 1ull);
-    while (ld_acquire_u64(bar) < target) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&bar->arrive) : "memory");
+    while (ld_acquire_u64(&bar->arrive) < st.arrived) {
+      if (relaxed) __nanosleep(400);
     }
-    __threadfence();
   }
   __syncthreads();
 }
@@ -91,19 +101,22 @@ __device__ __forceinline__ void list_unlock(int* lock, int p) {
   atomicExch(&lock[p], 0);
 }
 __device__ __forceinline__ void link_child_cg(const TreeView& T, int par, int c) {
-  const int h = __ldcg(&T.head[par]);
-  __stcg(&T.next[c], h);
+  const int h = __ldcg(&T.link[par].x);
+  __stcg(&T.link[c].y, h);
   __stcg(&T.prev[c], -1);
   if (h >= 0) __stcg(&T.prev[h], c);
-  __stcg(&T.head[par], c);
+  __stcg(&T.link[par].x, c);
 }
 __device__ __forceinline__ void unlink_child_cg(const TreeView& T, int par, int c) {
-  const int nx = __ldcg(&T.next[c]), pv = __ldcg(&T.prev[c]);
-  if (pv >= 0) __stcg(&T.next[pv], nx); else __stcg(&T.head[par], nx);
+  const int nx = __ldcg(&T.link[c].y), pv = __ldcg(&T.prev[c]);
+  if (pv >= 0) __stcg(&T.link[pv].y, nx); else __stcg(&T.link[par].x, nx);
   if (nx >= 0) __stcg(&T.prev[nx], pv);
 }
 
-struct GrowShared {
+constexpr int GROW_QCAP = 1024;   // strict descendants of one sample's rewired nodes that the parallel path handles
+constexpr int GROW_HASH = 512;    // near-set membership table (>= 2 x GROW_THREADS)
+
+struct GrowShared {  // lives in dynamic shared memory, in front of the in-order commit's scratch
   union {
     State4 ss[GROW_WMAX];  // scan: the window's samples
     struct {
@@ -114,17 +127,44 @@ struct GrowShared {
       int flag[GROW_THREADS];    // 1 in near set, 2 forward edge collides, 8 rewire edge collides
       int cand[GROW_THREADS];    // slots of the rewire candidates
       int rewn[GROW_THREADS];    // rewired nodes, in the order they become children of the new node
-      int wl[WAVE_QCAP];         // strict descendants of the rewired nodes, level by level
+      double rctc[GROW_THREADS]; // their new cost-to-come / arrival time (apply)
+      double rtim[GROW_THREADS];
+      int hash[GROW_HASH];       // open addressing over the near set's node indices
+      int wl[GROW_QCAP];         // strict descendants of the rewired nodes, level by level ...
+      int wl_head[GROW_QCAP];    // ... their first child (read together with the sibling link) ...
+      int wl_par[GROW_QCAP];     // ... and their parent: index in wl, or -(q + 1) for rewired node q
+      double wl_ctc[GROW_QCAP];  // new cost-to-come / arrival time (apply)
+      double wl_tim[GROW_QCAP];
       int lvl[GROW_LEVELS + 2];  // level boundaries in wl
     } d;
   } u;
   double4 obs[KRRT_MAX_OBS_DEV];
   double red_c[GROW_THREADS / 32];
   int red_i[GROW_THREADS / 32], red_k[GROW_THREADS / 32];
-  double par_key, par_tim;
-  int par_k, par_node;
-  int ncand, nrew, tail;
+  double hS[GROW_SMAX];      // h = p / (S - 1) of the edge sample points
+  double rho[GROW_THREADS];  // squared near radius at tree sizes nsub .. nsub + nb
+  double par_cf;             // c*(parent -> sample)
+  int ncand, nrew, tail, tries, K, flags, intra;
+  long long fin[20];  // last CTA: counters of the call, flushed to the control block when the kernel ends
 };
+__host__ __device__ inline size_t grow_shared_bytes() { return (sizeof(GrowShared) + 15) / 16 * 16; }
+
+__device__ __forceinline__ unsigned near_hash(int node) { return ((unsigned)node * 2654435761u) >> 23; }  // 9 bits
+
+// children of `first`'s list go to the write list: one 8-byte load per sibling gives its own first child too
+__device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm, int first, int parent_ref) {
+  int c = first;
+  for (int guard = 0; c >= 0 && guard < T.cap; ++guard) {
+    const int2 lk = __ldcg(&T.link[c]);
+    const int pos = atomicAdd(&sm.tail, 1);
+    if (pos < GROW_QCAP) {
+      sm.u.d.wl[pos] = c;
+      sm.u.d.wl_head[pos] = lk.x;
+      sm.u.d.wl_par[pos] = parent_ref;
+    }
+    c = lk.y;
+  }
+}
 
 // ---------------------------------------------------------------------------------------------------
 // In-order commit of window samples [b0, b1) by ONE warp (the whole window while the tree is small; a single sample
@@ -249,15 +289,18 @@ __device__ __forceinline__ void clear_window(const Batch& Bt) {
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,
                                                             GrowCfg cfg) {
-  extern __shared__ __align__(16) unsigned char dyn_smem[];  // sequential commit scratch (last CTA only)
-  __shared__ GrowShared sm;
+  extern __shared__ __align__(16) unsigned char dyn_raw[];
+  GrowShared& sm = *reinterpret_cast<GrowShared*>(dyn_raw);
+  unsigned char* dyn_smem = dyn_raw + grow_shared_bytes();  // in-order commit scratch (last CTA only)
   const int t = threadIdx.x;
   const int G = gridDim.x;
   const int cta = blockIdx.x;
   const bool last = cta == G - 1;  // never owns a sample: finishes the sub-rounds, commits sequentially
   const int cap = Bt.near_cap;
   const int S = P.S;
-  unsigned long long bar_target = 0;
+  BarState bs_all = {0ull}, bs_sub = {0ull};
+  if (t < 20) sm.fin[t] = 0;
+  if (t < GROW_SMAX) sm.hS[t] = (S > 1) ? (double)t / (double)(S - 1) : 0.0;
   long long clk_mark = clock64();
   auto phase_done = [&](int which) {  // phase clocks of the last CTA (it waits at every barrier like the others)
     if (last && t == 0) {
@@ -267,6 +310,16 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     }
   };
 
+#ifdef KRRT_DEBUG_CLK
+  long long dbg_t0 = 0;
+  long long dbg_acc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  long long cta_dec = 0, cta_val = 0, cta_app = 0, cta_t = 0;
+#define DBG_START() do { if (t == 0) dbg_t0 = clock64(); } while (0)
+#define DBG_STAMP(k) do { if (cta == 0 && t == 0) { const long long now_ = clock64(); dbg_acc[k] += now_ - dbg_t0; dbg_t0 = now_; } } while (0)
+#else
+#define DBG_START()
+#define DBG_STAMP(k)
+#endif
   for (;;) {
     // ================================================================ window
     const int n0 = __ldcg(&ctl->n);
@@ -354,7 +407,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
       }
     }
-    grid_barrier(cfg.bar, bar_target);
+    grid_barrier(cfg.bar, bs_all, G, false);
     phase_done(0);
     // ---- steer: tau*, c* of candidate -> sample and sample -> candidate, one thread per (candidate, direction)
     for (int b = cta; b < Wn; b += G) {
@@ -377,7 +430,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
       }
     }
-    grid_barrier(cfg.bar, bar_target);
+    grid_barrier(cfg.bar, bs_all, G, false);
     phase_done(1);
 
     if (!wave) {  // small tree: the whole window in order, one warp
@@ -387,20 +440,28 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         clear_window(Bt);
         if (t == 0) ctl->rounds_seq += 1;
       }
-      grid_barrier(cfg.bar, bar_target);
+      grid_barrier(cfg.bar, bs_all, G, !last);
       phase_done(5);
       continue;
     }
 
     // ================================================================ sub-rounds
     for (int j = t; j < P.m; j += GROW_THREADS) sm.obs[j] = P.obs[j];
+    // the CTAs that take part in this window's sub-rounds: enough for twice the prefixes seen lately + the last CTA;
+    // the others go straight to the window's end and doze there
+    const int Pn = min(G - 1, max(48, (3 * __ldcg(&ctl->ema16)) / 16 + 16));
+    const bool takes_part = cta < Pn || last;
+    // the set changes from window to window: pick the barrier's counters up where they stand (nothing is in flight)
+    bs_sub.arrived = __ldcg(&cfg.bar[1].arrive);
     int F0 = 0;
-    while (F0 < Wn) {
+    while (takes_part && F0 < Wn) {
       const int nsub = __ldcg(&ctl->n);
+      const long long iter_sub = __ldcg(&ctl->iter);
+      const int ema_sub = __ldcg(&ctl->ema16);
       const unsigned round = __ldcg(&ctl->round);
       if (__ldcg(&ctl->full) || __ldcg(&ctl->error) || round >= (1u << 23) - 2) break;
       const int slot = (int)(round & 1u);
-      const int nb = min(min(G - 1, Wn - F0), max(16, (2 * __ldcg(&ctl->ema16)) / 16 + 8));
+      const int nb = min(min(Pn, Wn - F0), max(16, (2 * ema_sub) / 16 + 8));
       const bool active = cta < nb;
       const int b = F0 + cta;
       const size_t base = (size_t)b * cap;
@@ -415,63 +476,100 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       State4 s = {0, 0, 0, 0};
 
       // -------------------------------------------------------------- decide
+      DBG_START();
+#ifdef KRRT_DEBUG_CLK
+      const long long dec_begin = clock64();
+      cta_t = dec_begin;
+#endif
       if (active) do {
+        // first round trip: everything that is addressed by the sample alone.  Slots past the candidate count hold stale
+        // but allocated data; they are ignored below.
+        const bool in_list = t < cap;
+        const int ref = in_list ? __ldcg(&Bt.ref[base + t]) : 0;
+        my_d = in_list ? __ldcg(&Bt.d2[base + t]) : 0.0;
+        my_cf = in_list ? __ldcg(&Bt.cf[base + t]) : 0.0;
+        my_cb = in_list ? __ldcg(&Bt.cb[base + t]) : 0.0;
+        const double my_tf = in_list ? __ldcg(&Bt.tf[base + t]) : 0.0;
+        const double my_tb = in_list ? __ldcg(&Bt.tb[base + t]) : 0.0;
+        const int cnt_raw = __ldcg(&Bt.count[b]);
+        const bool rejected = !P.dynamic && __ldcg(&Bt.reject[b]);
+        const bool earlier_ins = t < cta && sample_insertable(Bt, P, F0 + t);
+        if (t <= nb) sm.rho[t] = P.rho2[min(nsub + t, P.capacity)];
         s = Bt.samples[b];
         if (t == 0) {
           sm.ncand = 0;
           sm.nrew = 0;
           sm.tail = 0;
-          sm.par_k = -1;
+          sm.tries = 0;
+          sm.K = 0;
+          sm.flags = 0;
+          sm.intra = 0;
         }
-        if (!P.dynamic && __ldcg(&Bt.reject[b])) break;  // OUT_REJECT
+        if (rejected) break;  // OUT_REJECT
         outcome = OUT_COMPLEX;
-        const int cnt_raw = __ldcg(&Bt.count[b]);
-        // tree size this sample sees if every earlier sample of the sub-round that can insert does insert
-        const int ins = __syncthreads_count(t < cta && sample_insertable(Bt, P, F0 + t));
-        n_b = nsub + ins;
-        if (n_b >= P.capacity || cnt_raw > min(cap, GROW_THREADS)) break;  // tree full / overflow / huge near set
-        rho2n = P.rho2[n_b];
-        bool dup = false, pend = false;
-        if (t < cnt_raw) {
-          const int ref = __ldcg(&Bt.ref[base + t]);
-          my_d = __ldcg(&Bt.d2[base + t]);
+        // second round trip: the candidate's node (a sample committed in an earlier sub-round goes through the map)
+        bool pend = false;
+        const bool listed = t < cnt_raw && in_list;
+        if (listed) {
           if (ref & IN_BATCH) {
             const int e = ref & ~IN_BATCH;
-            if (e < F0) my_node = __ldcg(&Bt.map[e]);        // committed in an earlier sub-round (-1: it did not insert)
-            else pend = sample_insertable(Bt, P, e);          // may land inside the radius: wait for the next sub-round
+            if (e < F0) my_node = __ldcg(&Bt.map[e]);  // -1: it did not insert
+            else pend = sample_insertable(Bt, P, e);    // may land inside the radius: wait for the next sub-round
           } else {
             my_node = ref;
           }
-          if (my_node >= 0) {
-            my_near = my_d <= rho2n;
-            dup = my_near && my_d == 0.0;
+        }
+        State4 x = {0, 0, 0, 0};
+        double my_tim = 0.0;
+        int my_head = -1;
+        if (my_node >= 0) {
+          x = load_state_cg(T, my_node);
+          my_ctc = __ldcg(&T.ctc[my_node]);
+          my_tim = __ldcg(&T.tim[my_node]);
+          my_head = __ldcg(&T.link[my_node].x);  // only needed if the node gets rewired; it rides along for free
+        }
+        sm.u.d.hash[t] = -1;
+        sm.u.d.hash[t + GROW_THREADS] = -1;
+        // tree size this sample sees if every earlier sample of the sub-round that can insert does insert
+        const int ins = __syncthreads_count(earlier_ins);
+        n_b = nsub + ins;
+        if (n_b >= P.capacity || cnt_raw > min(cap, GROW_THREADS)) break;  // tree full / overflow / huge near set
+        rho2n = sm.rho[ins];
+        DBG_STAMP(0);
+        my_near = my_node >= 0 && my_d <= rho2n;
+        {
+          const unsigned nearb = __ballot_sync(FULL, my_near);
+          const unsigned dupb = __ballot_sync(FULL, my_near && my_d == 0.0);
+          const unsigned pendb = __ballot_sync(FULL, pend);
+          if ((t & 31) == 0) {
+            if (nearb) atomicAdd(&sm.K, __popc(nearb));
+            if (dupb | pendb) atomicOr(&sm.flags, (dupb ? 1 : 0) | (pendb ? 2 : 0));
           }
         }
-        const int any_dup = __syncthreads_or(dup);
-        const int any_pend = __syncthreads_or(pend);
-        K = __syncthreads_count(my_near);
-        if (any_dup) {
+        if (my_near) {
+          sm.u.d.st[t] = x;
+          sm.u.d.tim[t] = my_tim;
+          sm.u.d.tf[t] = my_tf;
+          sm.u.d.tb[t] = my_tb;
+          atomicMax(&W.amin[my_node], key);  // read mark
+        }
+        sm.u.d.flag[t] = my_near ? 1 : 0;
+        __syncthreads();
+        K = sm.K;
+        if (sm.flags & 1) {
           outcome = OUT_DUP;
           break;
         }
-        if (any_pend) {
+        if (sm.flags & 2) {
           outcome = OUT_CONFLICT;
           break;
         }
         if (K == 0) break;  // nearest-node fallback scans the whole tree: sequential path
-        // near set: gathers + read marks
-        if (my_near) {
-          sm.u.d.st[t] = load_state_cg(T, my_node);
-          my_ctc = __ldcg(&T.ctc[my_node]);
-          sm.u.d.tim[t] = __ldcg(&T.tim[my_node]);
-          my_cf = __ldcg(&Bt.cf[base + t]);
-          my_cb = __ldcg(&Bt.cb[base + t]);
-          sm.u.d.tf[t] = __ldcg(&Bt.tf[base + t]);
-          sm.u.d.tb[t] = __ldcg(&Bt.tb[base + t]);
-          atomicMax(&W.amin[my_node], key);
+        if (my_near) {  // membership table of the near set (the table was cleared before the barrier above)
+          unsigned hsl = near_hash(my_node);
+          while (atomicCAS(&sm.u.d.hash[hsl], -1, my_node) != -1) hsl = (hsl + 1) & (GROW_HASH - 1);
         }
-        sm.u.d.flag[t] = my_near ? 1 : 0;
-        __syncthreads();
+        DBG_STAMP(2);
         // forward edges of ALL near nodes at once: one thread per (edge, sample point)
         if (P.m > 0) {
           const int tot = min(cnt_raw, GROW_THREADS) * S;
@@ -479,51 +577,55 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             const int k = w / S, p = w - k * S;
             if (!(sm.u.d.flag[k] & 1)) continue;
             const Edge ed = make_edge(sm.u.d.st[k], s, sm.u.d.tf[k], sm.u.d.tim[k]);
-            bool h = false;
-            for (int j = 0; j < P.m; ++j) h |= edge_point_hits(ed, p, S, sm.obs[j], P.dynamic, P.R2);
-            if (h) atomicOr(&sm.u.d.flag[k], 2);
+            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+            if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) atomicOr(&sm.u.d.flag[k], 2);
           }
           __syncthreads();
         }
-        // parent = arg-min (cost, node index) over collision-free near nodes
+        DBG_STAMP(3);
+        // parent = arg-min (cost, node index) over collision-free near nodes.  Costs are >= 0, so their bit patterns
+        // order like unsigned integers: three REDUX per warp, then every thread folds the per-warp winners
         {
+          const bool ok = my_near && !(sm.u.d.flag[t] & 2);
+          const unsigned long long kb = ok ? (unsigned long long)__double_as_longlong(my_ctc + my_cf) : ~0ull;
+          const unsigned hi = (unsigned)(kb >> 32), lo = (unsigned)kb;
+          const unsigned mh = __reduce_min_sync(FULL, hi);
+          const unsigned ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
+          const bool top = ok && hi == mh && lo == ml;
+          const unsigned mn = __reduce_min_sync(FULL, top ? (unsigned)my_node : 0xffffffffu);
+          if (top && (unsigned)my_node == mn) {
+            sm.red_c[t >> 5] = my_ctc + my_cf;
+            sm.red_i[t >> 5] = my_node;
+            sm.red_k[t >> 5] = t;
+          } else if ((t & 31) == 0 && mn == 0xffffffffu) {
+            sm.red_i[t >> 5] = -1;
+          }
+          __syncthreads();
           double bc = INFINITY;
           int bi = -1, bk = -1;
-          if (my_near && !(sm.u.d.flag[t] & 2)) {
-            bc = my_ctc + my_cf;
-            bi = my_node;
-            bk = t;
-          }
-          warp_argmin(bc, bi, bk);
-          if ((t & 31) == 0) {
-            sm.red_c[t >> 5] = bc;
-            sm.red_i[t >> 5] = bi;
-            sm.red_k[t >> 5] = bk;
-          }
-          __syncthreads();
-          if (t < 32) {
-            double c2 = t < GROW_THREADS / 32 ? sm.red_c[t] : INFINITY;
-            int i2 = t < GROW_THREADS / 32 ? sm.red_i[t] : -1;
-            int k2 = t < GROW_THREADS / 32 ? sm.red_k[t] : -1;
-            warp_argmin(c2, i2, k2);
-            if (t == 0 && i2 >= 0) {
-              sm.par_k = k2;
-              sm.par_node = i2;
-              sm.par_key = c2;
-              sm.par_tim = sm.u.d.tim[k2] + sm.u.d.tf[k2];
+#pragma unroll
+          for (int w = 0; w < GROW_THREADS / 32; ++w) {
+            const int wi = sm.red_i[w];
+            if (wi < 0) continue;
+            const double wc = sm.red_c[w];
+            if (bi < 0 || wc < bc || (wc == bc && wi < bi)) {
+              bc = wc;
+              bi = wi;
+              bk = sm.red_k[w];
             }
           }
-          __syncthreads();
+          park = bk;
+          par = bi;
+          ctc_new = bc;
         }
-        park = sm.par_k;
+        DBG_STAMP(4);
         if (park < 0) {
           outcome = OUT_NOFREE;
           collide_calls = K;  // a sequential planner tries every candidate before giving up
           break;
         }
-        par = sm.par_node;
-        ctc_new = sm.par_key;
-        tim_new = sm.par_tim;
+        tim_new = sm.u.d.tim[park] + sm.u.d.tf[park];
+        if (t == park) sm.par_cf = my_cf;  // (read by thread 0 in apply, barriers in between)
         // a sequential planner checks candidates in (cost, index) order until the first free one; rewire candidates:
         // near nodes that would get cheaper through the new node
         bool tried = false, cand = false;
@@ -532,40 +634,43 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           tried = c < ctc_new || (c == ctc_new && my_node <= par);  // all of these but the parent collide
           cand = my_node != par && (ctc_new + my_cb < my_ctc);
         }
-        const int tries = __syncthreads_count(tried);
+        {
+          const unsigned triedb = __ballot_sync(FULL, tried);
+          if ((t & 31) == 0 && triedb) atomicAdd(&sm.tries, __popc(triedb));
+        }
         if (cand) sm.u.d.cand[atomicAdd(&sm.ncand, 1)] = t;
         __syncthreads();
         const int ncand = sm.ncand;
-        collide_calls = tries + ncand;
+        DBG_STAMP(5);
+        collide_calls = sm.tries + ncand;
         // edges new -> candidate, started at the new node's arrival time
         if (P.m > 0 && ncand > 0) {
           for (int w = t; w < ncand * S; w += GROW_THREADS) {
             const int q = w / S, p = w - q * S;
             const int k = sm.u.d.cand[q];
             const Edge ed = make_edge(s, sm.u.d.st[k], sm.u.d.tb[k], tim_new);
-            bool h = false;
-            for (int j = 0; j < P.m; ++j) h |= edge_point_hits(ed, p, S, sm.obs[j], P.dynamic, P.R2);
-            if (h) atomicOr(&sm.u.d.flag[k], 8);
+            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+            if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) atomicOr(&sm.u.d.flag[k], 8);
           }
           __syncthreads();
         }
+        DBG_STAMP(6);
         if (cand && !(sm.u.d.flag[t] & 8)) {  // candidate and free: rewired.  Its children seed the write list
           my_q = atomicAdd(&sm.nrew, 1);
           sm.u.d.rewn[my_q] = my_node;
           atomicMax(&W.wmin[my_node], key);
-          for (int c = __ldcg(&T.head[my_node]), guard = 0; c >= 0 && guard < T.cap; c = __ldcg(&T.next[c]), ++guard) {
-            const int pos = atomicAdd(&sm.tail, 1);
-            if (pos < WAVE_QCAP) sm.u.d.wl[pos] = c;
-          }
+          push_children(T, sm, my_head, -(my_q + 1));
         }
         __syncthreads();
         nrew = sm.nrew;
-        // level-order walk of everything below the rewired nodes: write marks
+        DBG_STAMP(7);
+        // level-order walk of everything below the rewired nodes: write marks.  A near node below one of this sample's
+        // own rewired nodes would see a changed cost mid-expansion (intra): that sample takes the in-order path
         int level0 = 0;
         bool overflow = false;
         for (;;) {
           const int level1 = sm.tail;
-          if (level1 > WAVE_QCAP || (level1 > level0 && nlvl >= GROW_LEVELS)) {
+          if (level1 > GROW_QCAP || (level1 > level0 && nlvl >= GROW_LEVELS)) {
             overflow = true;
             break;
           }
@@ -580,33 +685,50 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             const int d = sm.u.d.wl[q];
             atomicMax(&W.wmin[d], key);
             atomicMax(&W.amin[d], key);
-            atomicMax(&W.dsc[d], key);
-            for (int c = __ldcg(&T.head[d]), guard = 0; c >= 0 && guard < T.cap; c = __ldcg(&T.next[c]), ++guard) {
-              const int pos = atomicAdd(&sm.tail, 1);
-              if (pos < WAVE_QCAP) sm.u.d.wl[pos] = c;
+            for (unsigned hsl = near_hash(d);; hsl = (hsl + 1) & (GROW_HASH - 1)) {
+              const int hv = sm.u.d.hash[hsl];
+              if (hv == d) sm.intra = 1;
+              if (hv == d || hv < 0) break;
             }
+            push_children(T, sm, sm.u.d.wl_head[q], q);
           }
           level0 = level1;
           __syncthreads();
         }
         nwl = overflow ? 0 : level0;
-        // a near node below one of this sample's own rewired nodes would see a changed cost mid-expansion
-        int intra = 0;
-        if (!overflow && nwl > 0) {
-          __threadfence();
-          __syncthreads();
-          intra = __syncthreads_or(my_near && mark_sample(__ldcg(&W.dsc[my_node]), round) == cta);
-        }
+        DBG_STAMP(8);
+        const int intra = sm.intra;
         outcome = (overflow || intra) ? OUT_COMPLEX : OUT_INSERT;
+        DBG_STAMP(9);
       } while (0);
       if (active && t == 0) {
         WaveRec r;
-        r.outcome = outcome; r.n_b = n_b; r.par = par; r.park = park; r.K = K; r.nrew = nrew; r.nwl = nwl; r.pad = 0;
+#ifdef KRRT_DEBUG_CLK
+        r.pad = (int)(clock64() - dec_begin);
+        if (W.dbg_log) {
+          const int e_ = atomicAdd(&W.dbg_log[0], 1);
+          if (e_ < (1 << 20)) {
+            int* L_ = W.dbg_log + 8 + 8 * (size_t)e_;
+            L_[0] = cta; L_[1] = r.pad; L_[2] = outcome; L_[3] = K; L_[4] = __ldcg(&Bt.count[b]); L_[5] = nrew; L_[6] = nwl; L_[7] = nlvl;
+          }
+        }
+#else
+        r.pad = 0;
+#endif
+        r.outcome = outcome; r.n_b = n_b; r.par = par; r.park = park; r.K = K; r.nrew = nrew; r.nwl = nwl;
         r.ctc_new = ctc_new; r.tim_new = tim_new; r.collide_calls = collide_calls; r.d2_in_max = 0.0; r.d2_out_min = 0.0;
         W.rec[b] = r;
       }
-      grid_barrier(cfg.bar, bar_target);
+#ifdef KRRT_DEBUG_CLK
+      if (active || last) cta_dec += clock64() - cta_t;
+#endif
+      DBG_START();
+      grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      DBG_STAMP(12);
       phase_done(2);
+#ifdef KRRT_DEBUG_CLK
+      cta_t = clock64();
+#endif
 
       // -------------------------------------------------------------- validate
       int n_true = n_b;
@@ -631,31 +753,59 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
         if (fail && t == 0) atomicMin(&ctl->wave_Fs[slot], cta);
       }
-      grid_barrier(cfg.bar, bar_target);
+      DBG_STAMP(13);
+#ifdef KRRT_DEBUG_CLK
+      if (active || last) cta_val += clock64() - cta_t;
+#endif
+      grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      DBG_STAMP(12);
       phase_done(3);
+#ifdef KRRT_DEBUG_CLK
+      cta_t = clock64();
+#endif
 
       // -------------------------------------------------------------- apply
       const int F = min(nb, __ldcg(&ctl->wave_Fs[slot]));
+      DBG_START();
       if (active && cta < F && outcome == OUT_INSERT) {
         const int nw = n_true;
+        // edge cost / duration of this thread's share of the descendants: in flight while the lists are edited
+        double ec[GROW_QCAP / GROW_THREADS], et[GROW_QCAP / GROW_THREADS];
+#pragma unroll
+        for (int i = 0; i < GROW_QCAP / GROW_THREADS; ++i) {
+          const int q = t + i * GROW_THREADS;
+          ec[i] = 0.0;
+          et[i] = 0.0;
+          if (q < nwl) {
+            const int d = sm.u.d.wl[q];
+            ec[i] = __ldcg(&T.ecost[d]);
+            et[i] = __ldcg(&T.etime[d]);
+          }
+        }
+        if (my_q >= 0) {
+          sm.u.d.rctc[my_q] = ctc_new + my_cb;
+          sm.u.d.rtim[my_q] = tim_new + sm.u.d.tb[t];
+        }
         if (t == 0) {
           T.pos[nw] = make_double2(s.x, s.y);
           T.vel[nw] = make_double2(s.vx, s.vy);
           T.parent[nw] = par;
-          T.ecost[nw] = __ldcg(&Bt.cf[base + park]);
+          T.ecost[nw] = sm.par_cf;
           T.etime[nw] = sm.u.d.tf[park];
           T.ctc[nw] = ctc_new;
           T.tim[nw] = tim_new;
-          T.head[nw] = nrew > 0 ? sm.u.d.rewn[0] : -1;  // the rewired nodes become the new node's children
+          T.link[nw].x = nrew > 0 ? sm.u.d.rewn[0] : -1;  // the rewired nodes become the new node's children
           list_lock(W.lock, par);
           link_child_cg(T, par, nw);
           list_unlock(W.lock, par);
           Bt.map[b] = nw;
         }
+        DBG_STAMP(10);
         if (nrew > 0) {
-          // detach each rewired node from its old parent (one thread per warp takes the lock: no spinning inside a warp)
-          if ((t & 31) == 0) {
-            for (int q = t >> 5; q < nrew; q += GROW_THREADS / 32) {
+          // detach each rewired node from its old parent (one thread per warp takes the lock: no spinning inside a warp;
+          // warps 1.. : warp 0's first lane is busy inserting the new node at the same time)
+          if ((t & 31) == 0 && t > 0) {
+            for (int q = (t >> 5) - 1; q < nrew; q += GROW_THREADS / 32 - 1) {
               const int j = sm.u.d.rewn[q];
               const int old = __ldcg(&T.parent[j]);
               list_lock(W.lock, old);
@@ -666,74 +816,90 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           __syncthreads();
           if (my_q >= 0) {
             const int j = my_node;
-            const double tb = sm.u.d.tb[t];
             T.parent[j] = nw;
-            T.next[j] = my_q + 1 < nrew ? sm.u.d.rewn[my_q + 1] : -1;
+            T.link[j].y = my_q + 1 < nrew ? sm.u.d.rewn[my_q + 1] : -1;
             T.prev[j] = my_q > 0 ? sm.u.d.rewn[my_q - 1] : -1;
             T.ecost[j] = my_cb;
-            T.etime[j] = tb;
-            T.ctc[j] = ctc_new + my_cb;
-            T.tim[j] = tim_new + tb;
+            T.etime[j] = sm.u.d.tb[t];
+            T.ctc[j] = sm.u.d.rctc[my_q];
+            T.tim[j] = sm.u.d.rtim[my_q];
           }
-          __syncthreads();
-          // level order: a node is updated one level after its parent
+          // level order: a node is updated one level after its parent; the new values travel through shared memory
           for (int l = 0; l < nlvl; ++l) {
             const int q0 = sm.u.d.lvl[l], q1 = sm.u.d.lvl[l + 1];
-            for (int q = q0 + t; q < q1; q += GROW_THREADS) {
-              const int d = sm.u.d.wl[q];
-              const int pd = __ldcg(&T.parent[d]);
-              __stcg(&T.ctc[d], __ldcg(&T.ctc[pd]) + __ldcg(&T.ecost[d]));
-              __stcg(&T.tim[d], __ldcg(&T.tim[pd]) + __ldcg(&T.etime[d]));
+#pragma unroll
+            for (int i = 0; i < GROW_QCAP / GROW_THREADS; ++i) {
+              const int q = t + i * GROW_THREADS;
+              if (q >= q0 && q < q1) {
+                const int d = sm.u.d.wl[q];
+                const int pr = sm.u.d.wl_par[q];
+                const double c = (pr >= 0 ? sm.u.d.wl_ctc[pr] : sm.u.d.rctc[-pr - 1]) + ec[i];
+                const double tt = (pr >= 0 ? sm.u.d.wl_tim[pr] : sm.u.d.rtim[-pr - 1]) + et[i];
+                sm.u.d.wl_ctc[q] = c;
+                sm.u.d.wl_tim[q] = tt;
+                __stcg(&T.ctc[d], c);
+                __stcg(&T.tim[d], tt);
+              }
             }
             __syncthreads();
           }
+          DBG_STAMP(11);
         }
       }
       // -------------------------------------------------------------- finish (last CTA, one warp)
       if (last && t < 32) {
         const int lane = t;
+#ifdef KRRT_DEBUG_CLK
+        {
+          int mx = 0;
+          for (int k = lane; k < nb; k += 32) mx = max(mx, __ldcg(&W.rec[F0 + k].pad));
+          for (int off = 16; off > 0; off >>= 1) mx = max(mx, __shfl_xor_sync(FULL, mx, off));
+          if (lane == 0) {
+            ctl->dbg_clk[14] += mx;
+            ctl->dbg_clk[15] += nb;
+          }
+        }
+#endif
         if (F > 0) {  // fold the counters of the prefix the other CTAs are committing
           long long v[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
           for (int k = lane; k < F; k += 32) {
-            const int o = __ldcg(&W.rec[F0 + k].outcome);
+            const WaveRec* rp = &W.rec[F0 + k];
+            const int o = __ldcg(&rp->outcome), rk = __ldcg(&rp->K), rr = __ldcg(&rp->nrew), rw = __ldcg(&rp->nwl);
+            const long long rc = __ldcg(&rp->collide_calls);
             v[0] += 1;
             if (o == OUT_INSERT) {
-              const int rk = __ldcg(&W.rec[F0 + k].K);
-              v[1] += 1; v[5] += __ldcg(&W.rec[F0 + k].nrew); v[6] += __ldcg(&W.rec[F0 + k].nwl); v[7] += rk;
-              v[8] += 2 * rk - 1; v[9] += __ldcg(&W.rec[F0 + k].collide_calls);
+              v[1] += 1; v[5] += rr; v[6] += rw; v[7] += rk; v[8] += 2 * rk - 1; v[9] += rc;
             } else if (o == OUT_REJECT) {
               v[2] += 1;
             } else if (o == OUT_DUP) {
               v[3] += 1;
             } else {  // OUT_NOFREE
-              const int rk = __ldcg(&W.rec[F0 + k].K);
-              v[4] += 1; v[7] += rk; v[8] += rk; v[9] += __ldcg(&W.rec[F0 + k].collide_calls);
+              v[4] += 1; v[7] += rk; v[8] += rk; v[9] += rc;
             }
           }
 #pragma unroll
           for (int k = 0; k < 10; ++k)
             for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], off);
-          if (lane == 0) {
+          int o_next = OUT_INSERT;
+          if (F < nb) o_next = __ldcg(&W.rec[F0 + F].outcome);
+          if (lane == 0) {  // only stores on this path: the other CTAs wait for this warp at the barrier
             ctl->n = nsub + (int)v[1];
-            ctl->iter += F;
-            for (int k = 0; k < 10; ++k) ctl->stats[k] += v[k];
+            ctl->iter = iter_sub + F;
+            for (int k = 0; k < 10; ++k) sm.fin[k] += v[k];
             const State4 ls = Bt.samples[F0 + F - 1];
             ctl->last_sample[0] = ls.x; ctl->last_sample[1] = ls.y; ctl->last_sample[2] = ls.vx; ctl->last_sample[3] = ls.vy;
-            ctl->ema16 = (3 * ctl->ema16 + 16 * F) / 4;
-            ctl->rounds_wave += 1;
-            ctl->wave_committed += F;
+            ctl->ema16 = (3 * ema_sub + 16 * F) / 4;
+            sm.fin[10] += 1;  // rounds_wave
+            sm.fin[12] += F;  // wave_committed
             int why = 0;
-            if (F < nb) {
-              const int o = __ldcg(&W.rec[F0 + F].outcome);
-              why = o == OUT_CONFLICT ? 1 : o == OUT_COMPLEX ? 2 : (o == OUT_NOFREE ? 3 : 4);
-            }
-            ctl->why[why] += 1;
+            if (F < nb) why = o_next == OUT_CONFLICT ? 1 : o_next == OUT_COMPLEX ? 2 : (o_next == OUT_NOFREE ? 3 : 4);
+            sm.fin[13 + why] += 1;
           }
         } else {  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
           seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1);
           if (lane == 0) {
-            ctl->ema16 = (3 * ctl->ema16 + 16) / 4;
-            ctl->rounds_seq += 1;
+            ctl->ema16 = (3 * ema_sub + 16) / 4;
+            sm.fin[11] += 1;  // rounds_seq
           }
         }
         __syncwarp();
@@ -743,11 +909,34 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           ctl->round = round + 1;
         }
       }
-      grid_barrier(cfg.bar, bar_target);
+#ifdef KRRT_DEBUG_CLK
+      if (active || last) cta_app += clock64() - cta_t;
+#endif
+      DBG_START();
+      grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      DBG_STAMP(12);
       phase_done(4);
       F0 += max(F, 1);
     }
+    grid_barrier(cfg.bar, bs_all, G, !takes_part);  // window end
+    phase_done(4);
   }
+  if (last && t == 0) {
+    for (int k = 0; k < 10; ++k) ctl->stats[k] += sm.fin[k];
+    ctl->rounds_wave += sm.fin[10];
+    ctl->rounds_seq += sm.fin[11];
+    ctl->wave_committed += sm.fin[12];
+    for (int k = 0; k < 5; ++k) ctl->why[k] += sm.fin[13 + k];
+  }
+#ifdef KRRT_DEBUG_CLK
+  if (cta == 0 && t == 0)
+    for (int k = 0; k < 14; ++k) ctl->dbg_clk[k] += dbg_acc[k];
+  if (t == 0 && cta < 160) {
+    ctl->dbg_cta[0][cta] += cta_dec;
+    ctl->dbg_cta[1][cta] += cta_val;
+    ctl->dbg_cta[2][cta] += cta_app;
+  }
+#endif
 }
 
 }  // namespace krrt

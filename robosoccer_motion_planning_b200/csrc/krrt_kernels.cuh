@@ -44,6 +44,8 @@ struct Ctl {  // device-resident control block of one single-tree context
   long long windows;      // windows scanned since the current krrt_grow call began
   long long phase_clk[8]; // SM clocks the last CTA spent per phase since the call began: 0 scan, 1 steer, 2 decide,
                           // 3 validate, 4 apply + finish, 5 sequential windows
+  long long dbg_clk[16];
+  long long dbg_cta[3][160];  // per CTA index: decide / validate / apply(+finish) cycles, sub-rounds it was active in  // KRRT_DEBUG_CLK builds: step clocks inside decide / apply of CTA 0, max over CTAs
 };
 
 struct Params {
@@ -79,7 +81,6 @@ struct Batch {
 // ---------------------------------------------------------------------------------------------------
 // Per-sample decision of a sub-round (krrt_grow.cuh) and the conflict marks it is validated with.
 enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5 };
-constexpr int WAVE_QCAP = 2048;  // write-list capacity per sample (descendants of its rewired nodes)
 
 struct WaveRec {
   int outcome;
@@ -98,14 +99,10 @@ struct WaveRec {
 
 struct Wave {
   WaveRec* rec;     // [B]
-  int* near_idx;    // [B][near_cap] near set (node indices)
-  int* rew_node;    // [B][near_cap] rewired nodes ...
-  int* rew_slot;    // [B][near_cap] ... and their slots in the candidate list
-  int* wl;          // [B][WAVE_QCAP] strict descendants of the rewired nodes / BFS scratch of the apply pass
-  unsigned* wmin;   // [capacity] mark: lowest sample of this round that WRITES the node's cost/time
-  unsigned* amin;   // [capacity] mark: lowest sample of this round that reads or writes it
-  unsigned* dsc;    // [capacity] mark: lowest sample for which the node is a strict descendant of a rewired node
+  unsigned* wmin;   // [capacity] mark: lowest sample of this sub-round that WRITES the node's cost/time
+  unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that reads or writes it
   int* lock;        // [capacity] child-list lock of a parent
+  int* dbg_log;     // KRRT_DEBUG_CLK builds: [0] = entries, then 8 ints per decided sample (else nullptr)
 };
 
 // marks carry the round id, so they never need clearing: (round << 9) | (511 - sample), combined with atomicMax

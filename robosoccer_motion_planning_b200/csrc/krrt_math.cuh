@@ -215,6 +215,24 @@ KRRT_HD bool edge_point_hits(const Edge& e, int k, int S, const double4& o, int 
   return fma(dy, dy, dx * dx) < R2;
 }
 
+// the same test against all m obstacles for the sample point at h = k / (S - 1) (position evaluated once)
+KRRT_HD bool edge_point_hits_any(const Edge& e, double h, const double4* obs, int m, int dynamic, double R2) {
+  const double px = axis_pos(e.kx, h), py = axis_pos(e.ky, h);
+  const double t = e.t0 + e.tau * h;
+  bool hit = false;
+  for (int j = 0; j < m; ++j) {
+    const double4 o = obs[j];
+    double ox = o.x, oy = o.y;
+    if (dynamic) {
+      ox = fma(o.z, t, ox);
+      oy = fma(o.w, t, oy);
+    }
+    const double dx = px - ox, dy = py - oy;
+    hit |= fma(dy, dy, dx * dx) < R2;
+  }
+  return hit;
+}
+
 KRRT_HD double dist2(const State4& a, const State4& b) {
   double d0 = a.x - b.x, d1 = a.y - b.y, d2 = a.vx - b.vx, d3 = a.vy - b.vy;
   return fma(d3, d3, fma(d2, d2, fma(d1, d1, d0 * d0)));

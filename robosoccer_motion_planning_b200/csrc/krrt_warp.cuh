@@ -23,8 +23,7 @@ struct TreeView {
   double* ecost; // cost of the edge parent -> node
   double* etime; // duration of that edge
   int* parent;
-  int* head;     // first child
-  int* next;     // sibling links
+  int2* link;    // child lists: .x = first child, .y = next sibling (one 8-byte load walks a sibling AND finds its children)
   int* prev;
   int* queue;    // scratch for subtree propagation (capacity ints)
   int cap;       // node capacity (bounds every list walk: a corrupted list can never hang the kernel)
@@ -110,15 +109,15 @@ __device__ __forceinline__ void warp_min_int(int& key, int& aux) {
 
 // child-list maintenance (one lane)
 __device__ __forceinline__ void link_child(const TreeView& T, int par, int c) {
-  int h = T.head[par];
-  T.next[c] = h;
+  int h = T.link[par].x;
+  T.link[c].y = h;
   T.prev[c] = -1;
   if (h >= 0) T.prev[h] = c;
-  T.head[par] = c;
+  T.link[par].x = c;
 }
 __device__ __forceinline__ void unlink_child(const TreeView& T, int c) {
-  int par = T.parent[c], nx = T.next[c], pv = T.prev[c];
-  if (pv >= 0) T.next[pv] = nx; else T.head[par] = nx;
+  int par = T.parent[c], nx = T.link[c].y, pv = T.prev[c];
+  if (pv >= 0) T.link[pv].y = nx; else T.link[par].x = nx;
   if (nx >= 0) T.prev[nx] = pv;
 }
 
@@ -128,11 +127,11 @@ __device__ __forceinline__ long long warp_propagate(const TreeView& T, int j) {
   const int lane = lane_id();
   int qhead = 0, qtail = 0;
   {
-    int c = (lane == 0) ? T.head[j] : -1;
+    int c = (lane == 0) ? T.link[j].x : -1;
     if (lane == 0) {
       while (c >= 0 && qtail < T.cap) {
         T.queue[qtail++] = c;
-        c = T.next[c];
+        c = T.link[c].y;
       }
     }
     qtail = __shfl_sync(FULL, qtail, 0);
@@ -146,7 +145,7 @@ __device__ __forceinline__ long long warp_propagate(const TreeView& T, int j) {
       int par = T.parent[d];
       T.ctc[d] = T.ctc[par] + T.ecost[d];
       T.tim[d] = T.tim[par] + T.etime[d];
-      c = T.head[d];
+      c = T.link[d].x;
     }
     qhead += cnt;
     for (;;) {
@@ -154,7 +153,7 @@ __device__ __forceinline__ long long warp_propagate(const TreeView& T, int j) {
       if (m == 0 || qtail + 32 > T.cap) break;
       if (c >= 0) {
         T.queue[qtail + __popc(m & ((1u << lane) - 1))] = c;
-        c = T.next[c];
+        c = T.link[c].y;
       }
       qtail += __popc(m);
     }
@@ -216,7 +215,7 @@ __device__ __forceinline__ int warp_commit(const TreeView& T, const NearView& N,
     T.etime[nw] = tfp;
     T.ctc[nw] = ctc_new;
     T.tim[nw] = tim_new;
-    T.head[nw] = -1;
+    T.link[nw].x = -1;
     link_child(T, par, nw);
   }
   __syncwarp();
