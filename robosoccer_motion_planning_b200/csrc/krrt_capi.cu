@@ -49,7 +49,8 @@ struct krrt_ctx {
   long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
   size_t user_cap = 0;
-  std::vector<void*> allocs;
+  unsigned char* arena = nullptr;
+  size_t arena_bytes = 0, arena_used = 0;
 
   // scratch for stateless operators / batched planner
   void* d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -85,11 +86,15 @@ struct krrt_ctx {
     }                            \
   } while (0)
 
+// Everything a context owns on the device comes out of ONE allocation: the sub-rounds of k_grow are chains of
+// dependent gathers over ~25 arrays, and one arena keeps them inside a handful of 2 MB pages (TLB reach).
 template <typename Tp>
 static cudaError_t dev_alloc(krrt_ctx* ctx, Tp** p, size_t count) {
-  cudaError_t e = cudaMalloc((void**)p, sizeof(Tp) * std::max<size_t>(count, 1));
-  if (e == cudaSuccess) ctx->allocs.push_back((void*)*p);
-  return e;
+  const size_t bytes = (sizeof(Tp) * std::max<size_t>(count, 1) + 255) / 256 * 256;
+  if (ctx->arena_used + bytes > ctx->arena_bytes) return cudaErrorMemoryAllocation;
+  *p = reinterpret_cast<Tp*>(ctx->arena + ctx->arena_used);
+  ctx->arena_used += bytes;
+  return cudaSuccess;
 }
 
 static int ensure_scratch(krrt_ctx* ctx, int slot, size_t bytes) {
@@ -150,7 +155,7 @@ void krrt_destroy(krrt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->cfg.device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  for (void* p : ctx->allocs) cudaFree(p);
+  if (ctx->arena) cudaFree(ctx->arena);
   for (void* p : ctx->d_scratch)
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
@@ -188,6 +193,17 @@ static int create_impl(krrt_ctx* ctx) {
   CK(cudaEventCreate(&ctx->tm0));
   CK(cudaEventCreate(&ctx->tm1));
   const size_t cap = (size_t)c.capacity;
+  {
+    const size_t bcn = (size_t)c.batch * c.near_cap;
+    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + (cap + 1) * 8 + bcn * (4 + 8 * 5) +
+                  (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
+#ifdef KRRT_DEBUG_CLK
+    need += (size_t)32 * ((1 << 20) + 1) + 4096;
+#endif
+    CK(cudaMalloc((void**)&ctx->arena, need));
+    ctx->arena_bytes = need;
+    ctx->arena_used = 0;
+  }
   CK(dev_alloc(ctx, &ctx->T.pos, cap));
   CK(dev_alloc(ctx, &ctx->T.vel, cap));
   CK(dev_alloc(ctx, &ctx->T.ctc, cap));

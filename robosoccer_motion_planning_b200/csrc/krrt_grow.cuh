@@ -81,8 +81,10 @@ __device__ __forceinline__ void append_candidate(const Batch& Bt, int b, int ref
   }
 }
 
+// (both flags are loaded before either is looked at: a short-circuit would chain two L2 round trips)
 __device__ __forceinline__ bool sample_insertable(const Batch& Bt, const Params& P, int e) {
-  return !(!P.dynamic && __ldcg(&Bt.reject[e])) && !__ldcg(&Bt.dup[e]);
+  const int rej = __ldcg(&Bt.reject[e]), dup = __ldcg(&Bt.dup[e]);
+  return !((!P.dynamic & (rej != 0)) | (dup != 0));
 }
 
 __device__ __forceinline__ State4 load_state_cg(const TreeView& T, int i) {
@@ -325,7 +327,9 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     const int n0 = __ldcg(&ctl->n);
     const long long iter0 = __ldcg(&ctl->iter);
     const long long left = __ldcg(&ctl->iter_target) - iter0;
-    if (__ldcg(&ctl->full) || __ldcg(&ctl->error) || left <= 0 || __ldcg(&ctl->round) >= (1u << 23) - 2) break;
+    const int full0 = __ldcg(&ctl->full), error0 = __ldcg(&ctl->error);
+    const unsigned round0 = __ldcg(&ctl->round);
+    if ((full0 | error0) != 0 || left <= 0 || round0 >= (1u << 23) - 2) break;
     const bool wave = cfg.wave_enabled && n0 >= cfg.wave_min_n;
     const int Wn = (int)min((long long)(wave ? Bt.B : min(Bt.B, GROW_SEQ_WINDOW)), left);
     const int user_off = (int)(iter0 - __ldcg(&ctl->iter_begin));
@@ -459,7 +463,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       const long long iter_sub = __ldcg(&ctl->iter);
       const int ema_sub = __ldcg(&ctl->ema16);
       const unsigned round = __ldcg(&ctl->round);
-      if (__ldcg(&ctl->full) || __ldcg(&ctl->error) || round >= (1u << 23) - 2) break;
+      const int full_sub = __ldcg(&ctl->full), error_sub = __ldcg(&ctl->error);  // (no short-circuit: one round trip)
+      if ((full_sub | error_sub) != 0 || round >= (1u << 23) - 2) break;
       const int slot = (int)(round & 1u);
       const int nb = min(min(Pn, Wn - F0), max(16, (2 * ema_sub) / 16 + 8));
       const bool active = cta < nb;
@@ -484,16 +489,22 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       if (active) do {
         // first round trip: everything that is addressed by the sample alone.  Slots past the candidate count hold stale
         // but allocated data; they are ignored below.
-        const bool in_list = t < cap;
-        const int ref = in_list ? __ldcg(&Bt.ref[base + t]) : 0;
-        my_d = in_list ? __ldcg(&Bt.d2[base + t]) : 0.0;
-        my_cf = in_list ? __ldcg(&Bt.cf[base + t]) : 0.0;
-        my_cb = in_list ? __ldcg(&Bt.cb[base + t]) : 0.0;
-        const double my_tf = in_list ? __ldcg(&Bt.tf[base + t]) : 0.0;
-        const double my_tb = in_list ? __ldcg(&Bt.tb[base + t]) : 0.0;
+        const bool spec = t < min(cap, 64);  // these slots are warm in L2 (every window uses them); the rest wait for the count
+        int ref = 0;
+        double my_tf = 0.0, my_tb = 0.0;
+        if (spec) {
+          ref = __ldcg(&Bt.ref[base + t]);
+          my_d = __ldcg(&Bt.d2[base + t]);
+          my_cf = __ldcg(&Bt.cf[base + t]);
+          my_cb = __ldcg(&Bt.cb[base + t]);
+          my_tf = __ldcg(&Bt.tf[base + t]);
+          my_tb = __ldcg(&Bt.tb[base + t]);
+        }
         const int cnt_raw = __ldcg(&Bt.count[b]);
-        const bool rejected = !P.dynamic && __ldcg(&Bt.reject[b]);
-        const bool earlier_ins = t < cta && sample_insertable(Bt, P, F0 + t);
+        const int rej_b = __ldcg(&Bt.reject[b]);
+        bool earlier_ins = false;
+        if (t < cta) earlier_ins = sample_insertable(Bt, P, F0 + t);
+        const bool rejected = !P.dynamic && rej_b;
         if (t <= nb) sm.rho[t] = P.rho2[min(nsub + t, P.capacity)];
         s = Bt.samples[b];
         if (t == 0) {
@@ -506,15 +517,26 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.intra = 0;
         }
         if (rejected) break;  // OUT_REJECT
+        DBG_STAMP(1);
         outcome = OUT_COMPLEX;
         // second round trip: the candidate's node (a sample committed in an earlier sub-round goes through the map)
         bool pend = false;
-        const bool listed = t < cnt_raw && in_list;
+        const bool listed = t < cnt_raw && t < cap;
+        if (listed && !spec) {
+          ref = __ldcg(&Bt.ref[base + t]);
+          my_d = __ldcg(&Bt.d2[base + t]);
+          my_cf = __ldcg(&Bt.cf[base + t]);
+          my_cb = __ldcg(&Bt.cb[base + t]);
+          my_tf = __ldcg(&Bt.tf[base + t]);
+          my_tb = __ldcg(&Bt.tb[base + t]);
+        }
         if (listed) {
           if (ref & IN_BATCH) {
             const int e = ref & ~IN_BATCH;
-            if (e < F0) my_node = __ldcg(&Bt.map[e]);  // -1: it did not insert
-            else pend = sample_insertable(Bt, P, e);    // may land inside the radius: wait for the next sub-round
+            const int mapped = __ldcg(&Bt.map[e]);            // (all three loads leave together)
+            const bool e_ins = sample_insertable(Bt, P, e);
+            if (e < F0) my_node = mapped;  // committed in an earlier sub-round (-1: it did not insert)
+            else pend = e_ins;             // may land inside the radius: wait for the next sub-round
           } else {
             my_node = ref;
           }
@@ -530,6 +552,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
         sm.u.d.hash[t] = -1;
         sm.u.d.hash[t + GROW_THREADS] = -1;
+        DBG_STAMP(13);
         // tree size this sample sees if every earlier sample of the sub-round that can insert does insert
         const int ins = __syncthreads_count(earlier_ins);
         n_b = nsub + ins;
@@ -753,7 +776,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
         if (fail && t == 0) atomicMin(&ctl->wave_Fs[slot], cta);
       }
-      DBG_STAMP(13);
 #ifdef KRRT_DEBUG_CLK
       if (active || last) cta_val += clock64() - cta_t;
 #endif
