@@ -225,29 +225,31 @@ def run_ours(args, rank, world, local_rank):
     h2d = obs.nbytes + 64
     d2h = 4 * ctl_bytes + min(path_len, 32) * 40 + 4 + 16
 
-    # ---- per-kernel shares and the roofline of the neighbour scan (profile pass: CUDA events after every kernel)
+    # ---- phase shares and the roofline.  The whole grow call is ONE persistent kernel (k_grow); its phases are timed
+    # by the kernel itself (SM clocks of its last CTA between grid barriers), scaled to the call's CUDA-event time
     peak, peak_src = peaks()
-    G.set_profile(2)
     flush_l2()
     plan_device_timed()
     lt = G.last_timing()
     kt = G.kernel_times()
     wave = G.wave_stats()
-    G.set_profile(0)
     ksum = sum(v["ms"] for v in kt.values()) or 1.0
-    shares = {k: round(v["ms"] / ksum, 4) for k, v in kt.items() if v["launches"]}
+    shares = {k: round(v["ms"] / ksum, 4) for k, v in kt.items() if v["ms"] > 0}
     scan_bytes = lt["scan_node_samples"] * 32.0
-    achieved = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k_round_scan", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    achieved = scan_bytes / (lt["total_ms"] * 1e-3) / 1e9 if lt["total_ms"] > 0 else 0.0
+    scan_only = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k_grow", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": scan_bytes / max(1, lt["scan_launches"]),
-                "avg_launch_us": 1e3 * lt["scan_ms"] / max(1, lt["scan_launches"]),
-                "share_of_step": shares.get("k_round_scan"),
-                "kernel_shares": shares,
-                "note": "algorithmic bytes = 32 B x tree nodes x samples served by the launch (SURVEY 8d: N x 32 B per "
-                        "expansion); a <= 20k-node tree is 640 KB, L2-resident, and a launch lasts ~10 us: this config is "
-                        "bound by the dependent fp64 / L2-latency chains of k_round_decide and k_round_apply, not by HBM "
-                        "(see c3_100k for the scan on a larger tree)"}
+                "algorithmic_bytes_per_launch": scan_bytes,
+                "avg_launch_us": 1e3 * lt["total_ms"],
+                "share_of_step": 1.0,
+                "phase_shares": shares,
+                "scan_phase_GBps_algorithmic": scan_only,
+                "note": "one persistent kernel per grow call; algorithmic bytes = 32 B x tree nodes x samples scanned "
+                        "(SURVEY 8d: N x 32 B per expansion) over the kernel's whole duration.  A <= 20k-node tree is "
+                        "640 KB and L2-resident: this config is bound by the latency chain of the commit sub-rounds "
+                        "(decide / validate / apply, three grid barriers each), not by HBM; scan_phase_GBps is the "
+                        "same byte count over the scan phase alone (see c3_100k / c3_1m for larger trees)"}
     # ---- batched queries (configs 3/4): one warp per query, sharded over ranks, NCCL all-gather of the results
     q_total = BATCH_Q * world
     lo, hi = sweep.shard_bounds(q_total, rank, world)
@@ -315,7 +317,7 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "replicas": world, "speculative_batch": int(G.cfg.batch),
+        "config": {"workload": WORKLOAD, "replicas": world, "window": int(G.cfg.batch),
                    "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only (single tree); "
                    "batched queries shard by contiguous blocks"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -357,23 +359,22 @@ def run_ours(args, rank, world, local_rank):
         # config 3: single large tree, 100k iterations, static obstacles (+ the 1M-iteration tree with --c3-1m)
         if not args.skip_c3:
             for label, iters in (("c3_100k", 100000),) + ((("c3_1m", 1000000),) if args.c3_1m else ()):
-                G3 = capi.Planner(device=local_rank, capacity=iters + 2, batch=args.batch or 128)
+                G3 = capi.Planner(device=local_rank, capacity=iters + 2, batch=args.batch)
                 G3.set_obstacles(scenes.static_obstacles(), 0)
                 G3.set_start(start)
-                flush_l2()
-                G3.grow(None, iters)
-                t_plain = G3.last_timing()["total_ms"]
-                G3.set_profile(2)
+                G3.grow(None, min(iters, 20000))     # warm-up
                 G3.set_start(start)
                 flush_l2()
                 G3.grow(None, iters)
                 t3 = G3.last_timing()
+                t_plain = t3["total_ms"]
                 k3 = G3.kernel_times()
                 ks = sum(v["ms"] for v in k3.values()) or 1.0
                 line[label] = {"expansions_per_sec": iters / (t_plain * 1e-3), "ms": t_plain, "nodes": G3.size,
-                               "scan_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
-                               "scan_frac_of_hbm_peak": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9 / peak,
-                               "kernel_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["launches"]},
+                               "kernel_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t_plain * 1e-3) / 1e9,
+                               "kernel_frac_of_hbm_peak": t3["scan_node_samples"] * 32 / (t_plain * 1e-3) / 1e9 / peak,
+                               "scan_phase_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
+                               "phase_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["ms"] > 0},
                                "rounds": G3.wave_stats()}
                 G3.close()
     if rank == 0:
@@ -388,7 +389,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=0, help="speculative batch size (0 = library default)")
+    ap.add_argument("--batch", type=int, default=0, help="window size: samples scanned + steered at once (0 = library default)")
     ap.add_argument("--skip-c3", action="store_true")
     ap.add_argument("--c3-1m", action="store_true", help="also grow the 1M-iteration single tree (a few seconds)")
     args = ap.parse_args()

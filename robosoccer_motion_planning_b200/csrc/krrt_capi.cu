@@ -248,6 +248,8 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &W.wmin, cap));
   CK(dev_alloc(ctx, &W.amin, cap));
   CK(dev_alloc(ctx, &W.lock, cap));
+  CK(dev_alloc(ctx, &W.nn_d2, (size_t)1024));
+  CK(dev_alloc(ctx, &W.nn_idx, (size_t)1024));
 #ifdef KRRT_DEBUG_CLK
   CK(dev_alloc(ctx, &W.dbg_log, (size_t)8 * ((1 << 20) + 1)));
   CK(cudaMemsetAsync(W.dbg_log, 0, sizeof(int) * 8, ctx->stream));

@@ -171,8 +171,9 @@ __device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm,
 // ---------------------------------------------------------------------------------------------------
 // In-order commit of window samples [b0, b1) by ONE warp (the whole window while the tree is small; a single sample
 // when it needs the sequential path).  smem: obstacles + near list (commit_smem_bytes).
+// nn_idx >= 0: the nearest node of sample b0 over the whole tree (found by a grid-wide scan), used if its near set is empty.
 __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
-                                        unsigned char* smem, int b0, int b1) {
+                                        unsigned char* smem, int b0, int b1, int nn_idx, double nn_d2) {
   const int lane = lane_id();
   const int cap = Bt.near_cap;
   double4* s_obs = reinterpret_cast<double4*>(smem);
@@ -242,9 +243,9 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
       continue;
     }
     if (K == 0) {  // empty near set: exact nearest over the whole tree (rare once the tree is dense)
-      int ni;
-      double nd2;
-      warp_nearest(T, n, s, ni, nd2);
+      int ni = nn_idx;
+      double nd2 = nn_d2;
+      if (ni < 0 || b != b0) warp_nearest(T, n, s, ni, nd2);
       if (nd2 == 0.0) {
         st.fail_dup++;
         continue;
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 
     if (!wave) {  // small tree: the whole window in order, one warp
       if (last && t < 32) {
-        seq_commit(ctl, P, T, Bt, dyn_smem, 0, Wn);
+        seq_commit(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0);
         __syncwarp();
         clear_window(Bt);
         if (t == 0) ctl->rounds_seq += 1;
@@ -587,7 +588,10 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           outcome = OUT_CONFLICT;
           break;
         }
-        if (K == 0) break;  // nearest-node fallback scans the whole tree: sequential path
+        if (K == 0) {  // nearest-node fallback: a grid-wide scan, then the in-order path
+          outcome = OUT_NEAREST;
+          break;
+        }
         if (my_near) {  // membership table of the near set (the table was cleared before the barrier above)
           unsigned hsl = near_hash(my_node);
           while (atomicCAS(&sm.u.d.hash[hsl], -1, my_node) != -1) hsl = (hsl + 1) & (GROW_HASH - 1);
@@ -756,7 +760,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       // -------------------------------------------------------------- validate
       int n_true = n_b;
       if (active) {
-        bool fail = outcome == OUT_COMPLEX || outcome == OUT_CONFLICT;
+        bool fail = outcome == OUT_COMPLEX || outcome == OUT_CONFLICT || outcome == OUT_NEAREST;
         if (outcome == OUT_NOFREE || outcome == OUT_INSERT) {
           // the node index / tree size this sample really gets: earlier samples that found no free parent did not insert.
           // The decision was taken at the radius of n_b; it stands if no candidate changes sides between the two radii.
@@ -788,6 +792,45 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 
       // -------------------------------------------------------------- apply
       const int F = min(nb, __ldcg(&ctl->wave_Fs[slot]));
+      // the first sample has an empty near set: every CTA of the sub-round scans its share of the tree for the nearest
+      // node (lowest index among equal distances), the last CTA folds the partials and commits the sample in order
+      const bool need_nn = F == 0 && __ldcg(&W.rec[F0].outcome) == OUT_NEAREST;
+      if (need_nn) {
+        const State4 s0 = Bt.samples[F0];
+        const int pidx = last ? Pn : cta;
+        double bd = INFINITY;
+        int bi = 0x7fffffff;
+        for (int i = pidx * GROW_THREADS + t; i < nsub; i += (Pn + 1) * GROW_THREADS) {
+          const double d = dist2(load_state_cg(T, i), s0);
+          if (d < bd) {
+            bd = d;
+            bi = i;
+          }
+        }
+        // (distance, index) arg-min: distances are >= 0, their bit patterns order like unsigned integers
+        const unsigned long long kb = (unsigned long long)__double_as_longlong(bd);
+        const unsigned hi = (unsigned)(kb >> 32), lo = (unsigned)kb;
+        const unsigned mh = __reduce_min_sync(FULL, hi);
+        const unsigned ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
+        const unsigned mn = __reduce_min_sync(FULL, (hi == mh && lo == ml) ? (unsigned)bi : 0xffffffffu);
+        if ((t & 31) == 0) {
+          sm.red_c[t >> 5] = __longlong_as_double((long long)(((unsigned long long)mh << 32) | ml));
+          sm.red_i[t >> 5] = (int)mn;
+        }
+        __syncthreads();
+        if (t == 0) {
+          double c = sm.red_c[0];
+          int ci = sm.red_i[0];
+          for (int w = 1; w < GROW_THREADS / 32; ++w)
+            if (sm.red_c[w] < c || (sm.red_c[w] == c && sm.red_i[w] < ci)) {
+              c = sm.red_c[w];
+              ci = sm.red_i[w];
+            }
+          W.nn_d2[pidx] = c;
+          W.nn_idx[pidx] = ci;
+        }
+        grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      }
       DBG_START();
       if (active && cta < F && outcome == OUT_INSERT) {
         const int nw = n_true;
@@ -914,11 +957,33 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             sm.fin[10] += 1;  // rounds_wave
             sm.fin[12] += F;  // wave_committed
             int why = 0;
-            if (F < nb) why = o_next == OUT_CONFLICT ? 1 : o_next == OUT_COMPLEX ? 2 : (o_next == OUT_NOFREE ? 3 : 4);
+            if (F < nb) why = o_next == OUT_CONFLICT ? 1 : (o_next == OUT_COMPLEX || o_next == OUT_NEAREST) ? 2 : (o_next == OUT_NOFREE ? 3 : 4);
             sm.fin[13 + why] += 1;
           }
         } else {  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1);
+          int ni = -1;
+          double nd2 = 0.0;
+          if (need_nn) {
+            nd2 = INFINITY;
+            ni = 0x7fffffff;
+            for (int k = lane; k <= Pn; k += 32) {
+              const double c = __ldcg(&W.nn_d2[k]);
+              const int ci = __ldcg(&W.nn_idx[k]);
+              if (c < nd2 || (c == nd2 && ci < ni)) {
+                nd2 = c;
+                ni = ci;
+              }
+            }
+            for (int off = 16; off > 0; off >>= 1) {
+              const double c = __shfl_xor_sync(FULL, nd2, off);
+              const int ci = __shfl_xor_sync(FULL, ni, off);
+              if (c < nd2 || (c == nd2 && ci < ni)) {
+                nd2 = c;
+                ni = ci;
+              }
+            }
+          }
+          seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2);
           if (lane == 0) {
             ctl->ema16 = (3 * ema_sub + 16) / 4;
             sm.fin[11] += 1;  // rounds_seq

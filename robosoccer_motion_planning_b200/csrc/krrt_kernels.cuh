@@ -80,7 +80,8 @@ struct Batch {
 
 // ---------------------------------------------------------------------------------------------------
 // Per-sample decision of a sub-round (krrt_grow.cuh) and the conflict marks it is validated with.
-enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5 };
+enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5,
+       OUT_NEAREST = 6 };  // empty near set: the in-order path with a grid-wide nearest-node scan in front
 
 struct WaveRec {
   int outcome;
@@ -102,6 +103,8 @@ struct Wave {
   unsigned* wmin;   // [capacity] mark: lowest sample of this sub-round that WRITES the node's cost/time
   unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that reads or writes it
   int* lock;        // [capacity] child-list lock of a parent
+  double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...
+  int* nn_idx;      // ... (squared distance, node index)
   int* dbg_log;     // KRRT_DEBUG_CLK builds: [0] = entries, then 8 ints per decided sample (else nullptr)
 };
 
