@@ -23,6 +23,9 @@
  *   krrt_tree_download  tree.tree.cloud.states / tree.parent / tree.trajectories    robosoccer_visual.hpp:18
  *   krrt_path           tree.states(idx) root->idx chain        …node.cpp:237
  *   krrt_trajectory     get_trajectory(): per edge solver.solve(a,b,0.1) appended   …node.cpp:232-249
+ *   krrt_yaw_profiles   Trajectory1D::AngleController::angleControl + getAngleTrajectory for q queries
+ *                                                               robosoccer_motion_planning/src/trajectory1d.cpp:23-51,203-394 ;
+ *                                                               …node.cpp:306-314 ; trajectory_generator_node.cpp:6-53
  *   krrt_plan_batch     solve_rrt() (…node.cpp:167-196) for q independent queries at once
  */
 #ifndef KRRT_H
@@ -139,6 +142,18 @@ int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, co
 int krrt_plan_batch_device(krrt_ctx* ctx, const double* d_starts, const double* d_goals,
                            const double* d_obstacles, int q, int m, int dynamic, int n_iter,
                            uint32_t query_base, krrt_result* d_out, void* cuda_stream);
+/* Yaw (heading) profiles for q independent queries: (w, dw) = current heading / rate, yaw = target heading, limits
+ * v_max / a_max (Controller::setLimit), n sample rows over [0, final_time] as getAngleTrajectory(ctrl, offset, 0, t, n,
+ * &inputs) returns them.  states: q x max(n,1) x 2 (w wrapped to [-pi, pi], dw), times / inputs: q x max(n,1),
+ * status: 0 ok, 1 = the reference's "case not match!" exception, 2 = its "control sequence error!" (rows are zero),
+ * n_seg: entries of the control sequence incl. the initial state.  Bit-identical with the reference library.   */
+int krrt_yaw_profiles(krrt_ctx* ctx, const double* w, const double* dw, const double* yaw, int q, double v_max,
+                      double a_max, int n, double* states, double* times, double* inputs, double* final_time,
+                      int32_t* status, int32_t* n_seg);
+/* same with device-resident buffers (asynchronous on cuda_stream, or the ctx stream when NULL)                 */
+int krrt_yaw_profiles_device(krrt_ctx* ctx, const double* d_w, const double* d_dw, const double* d_yaw, int q,
+                             double v_max, double a_max, int n, double* d_states, double* d_times, double* d_inputs,
+                             double* d_final_time, int32_t* d_status, int32_t* d_n_seg, void* cuda_stream);
 /* oracle-comparable counters summed over the queries of the last batched plan                    */
 int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out);
 /* kernels launched by this ctx since creation (bench.py's gpu_launches)                          */

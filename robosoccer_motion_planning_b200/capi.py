@@ -30,6 +30,7 @@ EXPORTS = (
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
+    "krrt_yaw_profiles", "krrt_yaw_profiles_device",
 )
 
 
@@ -117,6 +118,9 @@ def lib():
     L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
     L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
     L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]
+    L.krrt_yaw_profiles.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int, D, D, D, D, I, I]
+    L.krrt_yaw_profiles_device.argtypes = [P] + [ctypes.c_void_p] * 3 + [ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                                                         ctypes.c_int] + [ctypes.c_void_p] * 7
     L.krrt_debug_clocks.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
@@ -347,6 +351,25 @@ class Planner:
         """Device-pointer variant (ints from tensor.data_ptr()); asynchronous on `stream`."""
         self._ck(lib().krrt_plan_batch_device(self.h, d_starts, d_goals, d_obstacles, int(q), int(m), int(dynamic),
                                               int(n_iter), int(query_base), d_out, stream or None))
+
+    def yaw_profiles(self, w, dw, yaw, v_max=1.0, a_max=1.0, n=25):
+        """Trajectory1D::AngleController::angleControl + getAngleTrajectory (trajectory1d.cpp:326-346) for q queries."""
+        w = np.ascontiguousarray(w, dtype=np.float64)
+        dw = np.ascontiguousarray(dw, dtype=np.float64)
+        yaw = np.ascontiguousarray(yaw, dtype=np.float64)
+        q = w.shape[0]
+        rows = max(int(n), 1)
+        out = {"states": np.zeros((q, rows, 2)), "times": np.zeros((q, rows)), "inputs": np.zeros((q, rows)),
+               "final_time": np.zeros(q), "status": np.zeros(q, dtype=np.int32), "n_seg": np.zeros(q, dtype=np.int32)}
+        self._ck(lib().krrt_yaw_profiles(self.h, _d(w), _d(dw), _d(yaw), q, float(v_max), float(a_max), int(n),
+                                         _d(out["states"]), _d(out["times"]), _d(out["inputs"]), _d(out["final_time"]),
+                                         out["status"].ctypes.data_as(I), out["n_seg"].ctypes.data_as(I)))
+        return out
+
+    def yaw_profiles_device(self, d_w, d_dw, d_yaw, q, v_max, a_max, n, d_states, d_times, d_inputs, d_ft, d_status,
+                            d_nseg, stream=0):
+        self._ck(lib().krrt_yaw_profiles_device(self.h, d_w, d_dw, d_yaw, int(q), float(v_max), float(a_max), int(n),
+                                                d_states, d_times, d_inputs, d_ft, d_status, d_nseg, stream or None))
 
     @property
     def launch_count(self):

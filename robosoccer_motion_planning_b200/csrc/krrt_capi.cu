@@ -16,6 +16,7 @@
 #include "krrt_kernels.cuh"
 #include "krrt_grow.cuh"
 #include "krrt_ops.cuh"
+#include "krrt_yaw.cuh"
 
 using namespace krrt;
 

@@ -446,4 +446,69 @@ int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes) {
   return KRRT_OK;
 }
 
+// ---- yaw profiles: Trajectory1D::AngleController for q queries at once
+static int launch_yaw(krrt_ctx* ctx, const double* d_w, const double* d_dw, const double* d_yaw, int q, double v_max,
+                      double a_max, int n, double* d_states, double* d_times, double* d_inputs, double* d_ft,
+                      int32_t* d_status, int32_t* d_nseg, cudaStream_t st) {
+  YawJob J;
+  J.w = d_w; J.dw = d_dw; J.yaw = d_yaw;
+  J.q = q; J.n = n; J.v_max = v_max; J.a_max = a_max;
+  J.states = d_states; J.times = d_times; J.inputs = d_inputs; J.final_time = d_ft;
+  J.status = d_status; J.n_seg = d_nseg;
+  const int ctas = (int)std::min<long long>(((long long)q + YAW_WARPS - 1) / YAW_WARPS,
+                                            (long long)ctx->prop.multiProcessorCount * 16);
+  k_yaw_profiles<<<std::max(1, ctas), YAW_WARPS * 32, 0, st>>>(J);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return KRRT_OK;
+}
+
+int krrt_yaw_profiles_device(krrt_ctx* ctx, const double* d_w, const double* d_dw, const double* d_yaw, int q,
+                             double v_max, double a_max, int n, double* d_states, double* d_times, double* d_inputs,
+                             double* d_final_time, int32_t* d_status, int32_t* d_n_seg, void* cuda_stream) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(q >= 0 && n >= 0 && v_max > 0.0 && a_max > 0.0, KRRT_ERR_INVALID, "q, n >= 0 and v_max, a_max > 0");
+  if (q == 0) return KRRT_OK;
+  REQUIRE(d_w && d_dw && d_yaw && d_states && d_times && d_inputs && d_final_time && d_status && d_n_seg,
+          KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  return launch_yaw(ctx, d_w, d_dw, d_yaw, q, v_max, a_max, n, d_states, d_times, d_inputs, d_final_time, d_status,
+                    d_n_seg, cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream);
+}
+
+int krrt_yaw_profiles(krrt_ctx* ctx, const double* w, const double* dw, const double* yaw, int q, double v_max,
+                      double a_max, int n, double* states, double* times, double* inputs, double* final_time,
+                      int32_t* status, int32_t* n_seg) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(q >= 0 && n >= 0 && v_max > 0.0 && a_max > 0.0, KRRT_ERR_INVALID, "q, n >= 0 and v_max, a_max > 0");
+  if (q == 0) return KRRT_OK;
+  REQUIRE(w && dw && yaw && states && times && inputs && final_time && status && n_seg, KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  const size_t rows = (size_t)q * (size_t)(n > 0 ? n : 1);
+  const size_t qb = sizeof(double) * (size_t)q;
+  int rc;
+  if ((rc = ensure_scratch(ctx, 0, 3 * qb)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sizeof(double) * 4 * rows)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 2, qb + 2 * sizeof(int32_t) * (size_t)q)) != KRRT_OK) return rc;
+  double* d_in = (double*)ctx->d_scratch[0];
+  double* d_rows = (double*)ctx->d_scratch[1];
+  double* d_ft = (double*)ctx->d_scratch[2];
+  int32_t* d_st = (int32_t*)(d_ft + q);
+  CK(cudaMemcpyAsync(d_in, w, qb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(d_in + q, dw, qb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(d_in + 2 * (size_t)q, yaw, qb, cudaMemcpyHostToDevice, st));
+  rc = launch_yaw(ctx, d_in, d_in + q, d_in + 2 * (size_t)q, q, v_max, a_max, n, d_rows, d_rows + 2 * rows,
+                  d_rows + 3 * rows, d_ft, d_st, d_st + q, st);
+  if (rc != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(states, d_rows, sizeof(double) * 2 * rows, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(times, d_rows + 2 * rows, sizeof(double) * rows, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(inputs, d_rows + 3 * rows, sizeof(double) * rows, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(final_time, d_ft, qb, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(status, d_st, sizeof(int32_t) * (size_t)q, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(n_seg, d_st + q, sizeof(int32_t) * (size_t)q, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
 }  // extern "C"
