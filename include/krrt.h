@@ -154,6 +154,23 @@ int krrt_yaw_profiles(krrt_ctx* ctx, const double* w, const double* dw, const do
 int krrt_yaw_profiles_device(krrt_ctx* ctx, const double* d_w, const double* d_dw, const double* d_yaw, int q,
                              double v_max, double a_max, int n, double* d_states, double* d_times, double* d_inputs,
                              double* d_final_time, int32_t* d_status, int32_t* d_n_seg, void* cuda_stream);
+/* Obstacle ingest for f frames at once: OminiVisionInfo robotinfo[] in nubot units (float32 cm, cm/s:
+ * nubot_common/msgs/RobotInfo.msg:2,9-12) -> the robot's own state and the obstacle rows (x,y,vx,vy) in metres that
+ * krrt_set_obstacles / krrt_plan_batch take.  Replaces RobotSubscriber::callback (robotsubscriber.cpp:44-77: own team,
+ * x / 100.), ::rival_callback (robotsubscriber.cpp:29-42: rivals sign-flipped, -x * 1e-2) and ::getObstacles
+ * (robotsubscriber.h:50-55: friends without the robot itself, then rivals).
+ * team f x n_team x 5 (pos.x, pos.y, vtrans.x, vtrans.y, heading.theta), agent_id f x n_team, rival f x n_rival x 4,
+ * self_id f.  Out: self_state f x 4 (zeros when no entry carries self_id), heading f, self_index f (-1 = absent,
+ * else the LAST matching entry), obstacles f x (n_team + n_rival) x 4 (unused rows zero), n_obs f.               */
+int krrt_ingest_vision(krrt_ctx* ctx, const float* team, const int32_t* agent_id, int n_team, const float* rival,
+                       int n_rival, const int32_t* self_id, int f, double* self_state, double* heading,
+                       int32_t* self_index, double* obstacles, int32_t* n_obs);
+/* same with device-resident buffers (16-byte aligned; asynchronous on cuda_stream, or the ctx stream when NULL):
+ * d_obstacles can be handed to krrt_plan_batch_device as is                                                       */
+int krrt_ingest_vision_device(krrt_ctx* ctx, const float* d_team, const int32_t* d_agent_id, int n_team,
+                              const float* d_rival, int n_rival, const int32_t* d_self_id, int f,
+                              double* d_self_state, double* d_heading, int32_t* d_self_index, double* d_obstacles,
+                              int32_t* d_n_obs, void* cuda_stream);
 /* oracle-comparable counters summed over the queries of the last batched plan                    */
 int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out);
 /* kernels launched by this ctx since creation (bench.py's gpu_launches)                          */

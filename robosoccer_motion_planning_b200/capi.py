@@ -30,7 +30,7 @@ EXPORTS = (
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
-    "krrt_yaw_profiles", "krrt_yaw_profiles_device",
+    "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
 )
 
 
@@ -121,6 +121,10 @@ def lib():
     L.krrt_yaw_profiles.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int, D, D, D, D, I, I]
     L.krrt_yaw_profiles_device.argtypes = [P] + [ctypes.c_void_p] * 3 + [ctypes.c_int, ctypes.c_double, ctypes.c_double,
                                                                          ctypes.c_int] + [ctypes.c_void_p] * 7
+    F = ctypes.POINTER(ctypes.c_float)
+    L.krrt_ingest_vision.argtypes = [P, F, I, ctypes.c_int, F, ctypes.c_int, I, ctypes.c_int, D, D, I, D, I]
+    L.krrt_ingest_vision_device.argtypes = ([P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 6)
     L.krrt_debug_clocks.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
@@ -370,6 +374,31 @@ class Planner:
                             d_nseg, stream=0):
         self._ck(lib().krrt_yaw_profiles_device(self.h, d_w, d_dw, d_yaw, int(q), float(v_max), float(a_max), int(n),
                                                 d_states, d_times, d_inputs, d_ft, d_status, d_nseg, stream or None))
+
+    def ingest_vision(self, team, agent_id, rival, self_id):
+        """RobotSubscriber::callback / rival_callback / getObstacles (robotsubscriber.cpp:29-77, robotsubscriber.h:50-55)
+        for f frames: team f x n_team x 5 float32, agent_id f x n_team, rival f x n_rival x 4 float32, self_id f."""
+        team = np.ascontiguousarray(team, dtype=np.float32)
+        rival = np.ascontiguousarray(rival, dtype=np.float32)
+        agent_id = np.ascontiguousarray(agent_id, dtype=np.int32)
+        self_id = np.ascontiguousarray(self_id, dtype=np.int32)
+        f = self_id.shape[0]
+        n_team = team.shape[1] if team.ndim == 3 else 0
+        n_rival = rival.shape[1] if rival.ndim == 3 else 0
+        out = {"self_state": np.zeros((f, 4)), "heading": np.zeros(f), "self_index": np.zeros(f, dtype=np.int32),
+               "obstacles": np.zeros((f, n_team + n_rival, 4)), "n_obs": np.zeros(f, dtype=np.int32)}
+        F = ctypes.POINTER(ctypes.c_float)
+        self._ck(lib().krrt_ingest_vision(self.h, team.ctypes.data_as(F), agent_id.ctypes.data_as(I), n_team,
+                                          rival.ctypes.data_as(F), n_rival, self_id.ctypes.data_as(I), f,
+                                          _d(out["self_state"]), _d(out["heading"]), out["self_index"].ctypes.data_as(I),
+                                          _d(out["obstacles"]), out["n_obs"].ctypes.data_as(I)))
+        return out
+
+    def ingest_vision_device(self, d_team, d_agent_id, n_team, d_rival, n_rival, d_self_id, f, d_self_state, d_heading,
+                             d_self_index, d_obstacles, d_n_obs, stream=0):
+        self._ck(lib().krrt_ingest_vision_device(self.h, d_team, d_agent_id, int(n_team), d_rival, int(n_rival), d_self_id,
+                                                 int(f), d_self_state, d_heading, d_self_index, d_obstacles, d_n_obs,
+                                                 stream or None))
 
     @property
     def launch_count(self):

@@ -511,4 +511,77 @@ int krrt_yaw_profiles(krrt_ctx* ctx, const double* w, const double* dw, const do
   return KRRT_OK;
 }
 
+// ---- obstacle ingest: RobotSubscriber callbacks for f frames at once
+static int launch_ingest(krrt_ctx* ctx, const IngestJob& J, cudaStream_t st) {
+  const long long total = (long long)J.f * (J.n_team + J.n_rival + 1);
+  const long long ctas = std::min<long long>((total + 255) / 256, (long long)ctx->prop.multiProcessorCount * 8);
+  k_ingest_vision<<<(unsigned)std::max<long long>(1, ctas), 256, 0, st>>>(J);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return KRRT_OK;
+}
+
+int krrt_ingest_vision_device(krrt_ctx* ctx, const float* d_team, const int32_t* d_agent_id, int n_team,
+                              const float* d_rival, int n_rival, const int32_t* d_self_id, int f,
+                              double* d_self_state, double* d_heading, int32_t* d_self_index, double* d_obstacles,
+                              int32_t* d_n_obs, void* cuda_stream) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(f >= 0 && n_team >= 0 && n_rival >= 0, KRRT_ERR_INVALID, "f, n_team, n_rival >= 0");
+  if (f == 0) return KRRT_OK;
+  REQUIRE((d_team && d_agent_id) || n_team == 0, KRRT_ERR_INVALID, "null team buffer");
+  REQUIRE(d_rival || n_rival == 0, KRRT_ERR_INVALID, "null rival buffer");
+  REQUIRE(d_self_id && d_self_state && d_heading && d_self_index && d_n_obs && (d_obstacles || n_team + n_rival == 0),
+          KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  IngestJob J = {d_team, d_agent_id, d_rival, d_self_id, d_self_state, d_heading, d_self_index, d_obstacles, d_n_obs,
+                 f, n_team, n_rival};
+  return launch_ingest(ctx, J, cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream);
+}
+
+int krrt_ingest_vision(krrt_ctx* ctx, const float* team, const int32_t* agent_id, int n_team, const float* rival,
+                       int n_rival, const int32_t* self_id, int f, double* self_state, double* heading,
+                       int32_t* self_index, double* obstacles, int32_t* n_obs) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(f >= 0 && n_team >= 0 && n_rival >= 0, KRRT_ERR_INVALID, "f, n_team, n_rival >= 0");
+  if (f == 0) return KRRT_OK;
+  REQUIRE((team && agent_id) || n_team == 0, KRRT_ERR_INVALID, "null team buffer");
+  REQUIRE(rival || n_rival == 0, KRRT_ERR_INVALID, "null rival buffer");
+  REQUIRE(self_id && self_state && heading && self_index && n_obs && (obstacles || n_team + n_rival == 0),
+          KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  const size_t F = (size_t)f, slots = (size_t)n_team + n_rival;
+  const size_t b_team = sizeof(float) * 5 * F * n_team, b_ids = sizeof(int32_t) * F * n_team;
+  const size_t b_rival = sizeof(float) * 4 * F * n_rival, b_self = sizeof(int32_t) * F;
+  const size_t b_obs = sizeof(double) * 4 * F * slots;
+  int rc;
+  if ((rc = ensure_scratch(ctx, 0, b_team + 16)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, b_rival + 16)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 2, b_ids + b_self + 16)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 3, b_obs + 16)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 4, sizeof(double) * 5 * F + 2 * sizeof(int32_t) * F)) != KRRT_OK) return rc;
+  float* d_team = (float*)ctx->d_scratch[0];
+  float* d_rival = (float*)ctx->d_scratch[1];
+  int32_t* d_ids = (int32_t*)ctx->d_scratch[2];
+  int32_t* d_self = d_ids + F * n_team;
+  double* d_obs = (double*)ctx->d_scratch[3];
+  double* d_state = (double*)ctx->d_scratch[4];
+  double* d_head = d_state + 4 * F;
+  int32_t* d_sidx = (int32_t*)(d_head + F);
+  int32_t* d_nobs = d_sidx + F;
+  if (b_team) CK(cudaMemcpyAsync(d_team, team, b_team, cudaMemcpyHostToDevice, st));
+  if (b_ids) CK(cudaMemcpyAsync(d_ids, agent_id, b_ids, cudaMemcpyHostToDevice, st));
+  if (b_rival) CK(cudaMemcpyAsync(d_rival, rival, b_rival, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(d_self, self_id, b_self, cudaMemcpyHostToDevice, st));
+  IngestJob J = {d_team, d_ids, d_rival, d_self, d_state, d_head, d_sidx, d_obs, d_nobs, f, n_team, n_rival};
+  if ((rc = launch_ingest(ctx, J, st)) != KRRT_OK) return rc;
+  CK(cudaMemcpyAsync(self_state, d_state, sizeof(double) * 4 * F, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(heading, d_head, sizeof(double) * F, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(self_index, d_sidx, sizeof(int32_t) * F, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(n_obs, d_nobs, sizeof(int32_t) * F, cudaMemcpyDeviceToHost, st));
+  if (b_obs) CK(cudaMemcpyAsync(obstacles, d_obs, b_obs, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
 }  // extern "C"

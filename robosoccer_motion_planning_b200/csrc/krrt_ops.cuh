@@ -219,4 +219,73 @@ __global__ void __launch_bounds__(128) k_tree_edges(TreeView T, int n, int S, do
   write_edge_sample(load_state(T, p), x1, T.etime[i], T.tim[p], k, S, rows + 5 * g);
 }
 
+// Obstacle ingest: f frames of OminiVisionInfo robotinfo[] (float32, cm and cm/s:
+// nubot_common/msgs/RobotInfo.msg:2,9-12) -> the planner's own state + obstacle rows in metres, as
+// RobotSubscriber::callback (robotsubscriber.cpp:44-77: own team, x / 100.), ::rival_callback
+// (robotsubscriber.cpp:29-42: rivals flipped, -x * 1e-2 — a different rounding than / 100., kept) and
+// ::getObstacles (robotsubscriber.h:50-55: friends without self, then rivals) build them.
+// One thread per (frame, output slot); slot n_team + n_rival of each frame writes the frame's scalars.
+// HBM-bound: 24 n_team + 16 n_rival + 4 B in, 32 (n_team + n_rival) + 48 B out per frame.
+struct IngestJob {
+  const float* team;        // f x n_team x 5
+  const int32_t* agent_id;  // f x n_team
+  const float* rival;       // f x n_rival x 4
+  const int32_t* self_id;   // f
+  double* self_state;       // f x 4
+  double* heading;          // f
+  int32_t* self_index;      // f
+  double* obstacles;        // f x (n_team + n_rival) x 4
+  int32_t* n_obs;           // f
+  int f, n_team, n_rival;
+};
+
+__global__ void __launch_bounds__(256) k_ingest_vision(IngestJob J) {
+  const int slots = J.n_team + J.n_rival;
+  const long long total = (long long)J.f * (slots + 1);
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total;
+       g += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(g / (slots + 1)), s = (int)(g - (long long)q * (slots + 1));
+    const int32_t* ids = J.agent_id + (size_t)q * J.n_team;
+    const int32_t me = J.self_id[q];
+    int n_self = 0, last = -1;
+    for (int i = 0; i < J.n_team; ++i) {
+      if (ids[i] == me) {
+        ++n_self;
+        last = i;
+      }
+    }
+    const int n_friend = J.n_team - n_self;
+    if (s == slots) {  // the frame's scalars
+      double4 st = make_double4(0.0, 0.0, 0.0, 0.0);
+      double hd = 0.0;
+      if (last >= 0) {
+        const float* r = J.team + ((size_t)q * J.n_team + last) * 5;
+        st = make_double4((double)r[0] / 100., (double)r[1] / 100., (double)r[2] / 100., (double)r[3] / 100.);
+        hd = (double)r[4];
+      }
+      reinterpret_cast<double4*>(J.self_state)[q] = st;
+      J.heading[q] = hd;
+      J.self_index[q] = last;
+      J.n_obs[q] = n_friend + J.n_rival;
+      continue;
+    }
+    double4 o = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (s < n_friend) {  // the s-th team entry that is not the robot itself
+      int seen = 0, src = -1;
+      for (int i = 0; i < J.n_team; ++i) {
+        if (ids[i] != me) {
+          if (seen == s) src = i;
+          ++seen;
+        }
+      }
+      const float* r = J.team + ((size_t)q * J.n_team + src) * 5;
+      o = make_double4((double)r[0] / 100., (double)r[1] / 100., (double)r[2] / 100., (double)r[3] / 100.);
+    } else if (s < n_friend + J.n_rival) {
+      const float4 r = reinterpret_cast<const float4*>(J.rival)[(size_t)q * J.n_rival + (s - n_friend)];
+      o = make_double4(-(double)r.x * 1e-2, -(double)r.y * 1e-2, -(double)r.z * 1e-2, -(double)r.w * 1e-2);
+    }
+    reinterpret_cast<double4*>(J.obstacles)[(size_t)q * slots + s] = o;
+  }
+}
+
 }  // namespace krrt
