@@ -124,6 +124,10 @@ int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_row
 int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, double* t, double* c);
 int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                int cap_rows, int* n_rows);
+/* krrt_solve plus the control inputs (ax, ay) at the same rows: inputs n x 2.  Serves the 2-D integrator model of the
+ * compute_trajectory service (trajectory_generator_node.cpp:6-53 answers "angular_trajectory" only) */
+int krrt_solve_inputs(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
+                      double* inputs, int cap_rows, int* n_rows);
 /* Connector slot on its own: the optimal edge of each of n pairs as S rows (x,y,vx,vy,t0+t); rows: n x S x 5 */
 int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const double* t0, int n, int S,
                       double* rows);

@@ -195,6 +195,34 @@ int ko_solve(const double x0[4], const double x1[4], double r, double dt, double
   return n;
 }
 
+/* control input of the optimal edge: u(t) = p''(t) = (2B + 6C h) / tau^2 per axis, at the rows ko_solve emits
+ * (TrajectoryService response `inputs`, trajectory_generator_node.cpp:33-47, for the 2-D integrator model) */
+static inline double ko_axis_acc(const ko_axis* k, double h, double tau) {
+  if (tau == 0.0) return 0.0;
+  return fma(6.0 * h, k->C, 2.0 * k->B) / (tau * tau);
+}
+int ko_solve_inputs(const double x0[4], const double x1[4], double r, double dt, double* rows, int cap) {
+  double tau, cost;
+  ko_steer(x0, x1, r, &tau, &cost);
+  ko_axis kx, ky;
+  ko_axis_coef(x0[0], x0[2], x1[0], x1[2], tau, &kx);
+  ko_axis_coef(x0[1], x0[3], x1[1], x1[3], tau, &ky);
+  int n = 0;
+  for (int k = 0;; ++k) {
+    double t = (double)k * dt;
+    int last = !(t < tau);
+    if (last) t = tau;
+    if (n < cap) {
+      double h = (tau == 0.0) ? 0.0 : t / tau;
+      rows[2 * n + 0] = ko_axis_acc(&kx, h, tau);
+      rows[2 * n + 1] = ko_axis_acc(&ky, h, tau);
+    }
+    ++n;
+    if (last) break;
+  }
+  return n;
+}
+
 /* Environment::collide for one edge — static (dynamic=0) or time-space (dynamic=1);
  * stands in for the Environment slot (…node.cpp:84-85,140; robosoccer_visual.hpp:35) */
 int ko_edge_collide(const double x0[4], const double x1[4], double tau, double t0, const double* obs, int m,

@@ -78,6 +78,8 @@ void ko_steer_batch(const double* x0, const double* x1, int n, double r, double*
 void ko_edge_state(const double x0[4], const double x1[4], double tau, double h, double out[4]);
 /* == solver.solve(xi,xf,dt): rows (x,y,vx,vy,t0+t) at t = 0,dt,2dt,.. < tau, then tau. returns rows */
 int ko_solve(const double x0[4], const double x1[4], double r, double dt, double t0, double* rows, int cap);
+/* accelerations (ax, ay) at the same rows: the service response's `inputs` for the 2-D integrator model */
+int ko_solve_inputs(const double x0[4], const double x1[4], double r, double dt, double* rows, int cap);
 /* time-space disc collision of the optimal edge started at absolute time t0 */
 int ko_edge_collide(const double x0[4], const double x1[4], double tau, double t0,
                     const double* obs, int m, int dynamic, double R, int S);

@@ -31,6 +31,7 @@ EXPORTS = (
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
+    "krrt_solve_inputs",
 )
 
 
@@ -108,6 +109,7 @@ def lib():
     L.krrt_trajectory.argtypes = [P, ctypes.c_int, ctypes.c_double, D, ctypes.c_int, I]
     L.krrt_steer_cost.argtypes = [P, D, D, ctypes.c_int, D, D]
     L.krrt_solve.argtypes = [P, D, D, ctypes.c_double, ctypes.c_double, D, ctypes.c_int, I]
+    L.krrt_solve_inputs.argtypes = [P, D, D, ctypes.c_double, ctypes.c_double, D, D, ctypes.c_int, I]
     L.krrt_edge_collide.argtypes = [P, D, D, D, D, ctypes.c_int, ctypes.POINTER(ctypes.c_ubyte)]
     L.krrt_near.argtypes = [P, D, ctypes.c_double, I, ctypes.c_int, I, I, D]
     L.krrt_plan_batch.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
@@ -289,6 +291,18 @@ class Planner:
         n = ctypes.c_int32(0)
         self._ck(lib().krrt_solve(self.h, _d(xi), _d(xf), float(dt), float(t0), _d(rows), cap_rows, ctypes.byref(n)))
         return rows[:min(n.value, cap_rows)].copy()
+
+    def solve_inputs(self, xi, xf, dt=0.1, t0=0.0, cap_rows=4096):
+        """solve() plus the control inputs (ax, ay) at the same rows."""
+        xi = _f64(xi, (4,))
+        xf = _f64(xf, (4,))
+        rows = np.empty((cap_rows, 5))
+        inputs = np.empty((cap_rows, 2))
+        n = ctypes.c_int32(0)
+        self._ck(lib().krrt_solve_inputs(self.h, _d(xi), _d(xf), float(dt), float(t0), _d(rows), _d(inputs), cap_rows,
+                                         ctypes.byref(n)))
+        k = min(n.value, cap_rows)
+        return rows[:k].copy(), inputs[:k].copy()
 
     # Connector slot: S samples (x,y,vx,vy,t0+t) of each optimal edge
     def edge_samples(self, xi, xf, t0, S=10):

@@ -92,7 +92,7 @@ int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out) 
 
 // rows of every edge of a device-resident chain of `len` states
 static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const double* d_t0, int len, double dt,
-                               double* rows, int cap_rows, int* n_rows) {
+                               double* rows, int cap_rows, int* n_rows, double* inputs = nullptr) {
   cudaStream_t st = ctx->stream;
   const int ne = len - 1;
   if (ne <= 0) {
@@ -114,12 +114,14 @@ static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const doub
   *n_rows = total;
   const int got = std::min(total, cap_rows);
   if (!rows || got <= 0) return KRRT_OK;
-  if ((rc = ensure_scratch(ctx, 5, sizeof(double) * 5 * (size_t)got)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 5, sizeof(double) * 7 * (size_t)got)) != KRRT_OK) return rc;
   double* d_out = (double*)ctx->d_scratch[5];
-  k_traj_fill<<<ne, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, dt, d_out, got);
+  double* d_inp = inputs ? d_out + 5 * (size_t)got : nullptr;
+  k_traj_fill<<<ne, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, dt, d_out, got, d_inp);
   ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(rows, d_out, sizeof(double) * 5 * (size_t)got, cudaMemcpyDeviceToHost, st));
+  if (inputs) CK(cudaMemcpyAsync(inputs, d_inp, sizeof(double) * 2 * (size_t)got, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return KRRT_OK;
 }
@@ -162,6 +164,23 @@ int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt,
   CK(cudaStreamSynchronize(ctx->stream));
   return trajectory_of_chain(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], 2, dt, rows,
                              cap_rows, n_rows);
+}
+
+int krrt_solve_inputs(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
+                      double* inputs, int cap_rows, int* n_rows) {
+  if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
+  REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
+  REQUIRE(cap_rows == 0 || (rows && inputs), KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int rc;
+  if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 8)) != KRRT_OK) return rc;
+  if ((rc = ensure_scratch(ctx, 1, sizeof(double) * 2)) != KRRT_OK) return rc;
+  double h[8] = {xi[0], xi[1], xi[2], xi[3], xf[0], xf[1], xf[2], xf[3]};
+  CK(cudaMemcpyAsync(ctx->d_scratch[0], h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->d_scratch[1], &t0, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return trajectory_of_chain(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], 2, dt, rows,
+                             cap_rows, n_rows, inputs);
 }
 
 int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, double* t, double* c) {

@@ -186,6 +186,12 @@ KRRT_HD double axis_vel(const AxisCubic& k, double h, double v0, double tau) {
   return v0 + (h * fma(3.0 * h, k.C, 2.0 * k.B)) / tau;
 }
 
+// control input u = p'' of the edge at h (the service response's `inputs` for the 2-D integrator model)
+KRRT_HD double axis_acc(const AxisCubic& k, double h, double tau) {
+  if (tau == 0.0) return 0.0;
+  return fma(6.0 * h, k.C, 2.0 * k.B) / (tau * tau);
+}
+
 struct Edge {
   AxisCubic kx, ky;
   double tau, t0, vx0, vy0;

@@ -156,7 +156,8 @@ __global__ void k_traj_offsets(const int* rows, int n_edges, int* offs) {
 // one CTA per edge: rows (x, y, vx, vy, t0 + t)
 __global__ void __launch_bounds__(128) k_traj_fill(const double* __restrict__ states, const double* __restrict__ t0s,
                                                      const double* __restrict__ tau, const int* __restrict__ offs,
-                                                     double dt, double* out, int cap_rows) {
+                                                     double dt, double* out, int cap_rows,
+                                                     double* __restrict__ inputs) {
   const int e = blockIdx.x;
   const double4 a = reinterpret_cast<const double4*>(states)[e];
   const double4 b = reinterpret_cast<const double4*>(states)[e + 1];
@@ -174,6 +175,10 @@ __global__ void __launch_bounds__(128) k_traj_fill(const double* __restrict__ st
     row[2] = axis_vel(ed.kx, h, x0.vx, T);
     row[3] = axis_vel(ed.ky, h, x0.vy, T);
     row[4] = t0 + t;
+    if (inputs) {  // (ax, ay) at the same row
+      inputs[2 * (size_t)(o + k) + 0] = axis_acc(ed.kx, h, T);
+      inputs[2 * (size_t)(o + k) + 1] = axis_acc(ed.ky, h, T);
+    }
   }
 }
 

@@ -82,6 +82,8 @@ def lib():
     L.ko_edge_state.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D]
     L.ko_solve.argtypes = [D, D, ctypes.c_double, ctypes.c_double, ctypes.c_double, D, ctypes.c_int]
     L.ko_solve.restype = ctypes.c_int
+    L.ko_solve_inputs.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D, ctypes.c_int]
+    L.ko_solve_inputs.restype = ctypes.c_int
     L.ko_edge_collide.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D, ctypes.c_int, ctypes.c_int,
                                   ctypes.c_double, ctypes.c_int]
     L.ko_edge_collide.restype = ctypes.c_int

@@ -25,3 +25,22 @@ def test_node_style_caller_matches_oracle(gpu_required, env, iters):
     r = subprocess.run([exe, env, str(iters)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "0 check failure(s)" in r.stdout
+
+
+def test_service_compiles_and_has_no_cpu_fallback():
+    exe = native_build.build_service_check()
+    from robosoccer_motion_planning_b200 import capi
+    if capi.lib().krrt_device_count() > 0:
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3, r.stdout + r.stderr
+    assert "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_trajectory_service_matches_checkers(gpu_required):
+    """compute_trajectory (trajectory_generator_node.cpp:6-53) for "angular_trajectory" and the 2-D integrator model."""
+    exe = native_build.build_service_check()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "0 check failure(s)" in r.stdout
