@@ -66,8 +66,22 @@ __device__ __forceinline__ void grid_barrier(GridBar* bar, BarState& st, int n, 
   st.arrived += (unsigned long long)n;
   if (threadIdx.x == 0) {
     asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(&bar->arrive) : "memory");
+    // watchdog: no barrier of a healthy plan waits longer than a window (< 1 ms); a wait of 5 s means the grid is wedged,
+    // and a trap (the host sees cudaErrorLaunchFailure -> KRRT_ERR_CUDA) is better than a kernel that never returns
+    unsigned spins = 0;
+    unsigned long long t_first = 0;
     while (ld_acquire_u64(&bar->arrive) < st.arrived) {
       if (relaxed) __nanosleep(400);
+      if ((++spins & 0x3fffu) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+        if (t_first == 0) t_first = now;
+        else if (now - t_first > 5000000000ull) {
+          printf("krrt k_grow: grid barrier wedged (cta %d, expected %llu, seen %llu)\n", (int)blockIdx.x, st.arrived,
+                 ld_acquire_u64(&bar->arrive));
+          __trap();
+        }
+      }
     }
   }
   __syncthreads();
@@ -435,6 +449,12 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
       }
     }
+    // What the sub-rounds of this window start from is read BEFORE the barrier: after it, a CTA that has nothing to decide
+    // arrives at the sub-round barrier within one L2 round trip, and the last CTA updates ema16 a few microseconds later —
+    // a CTA that read either value late would wait for one arrival too many (or disagree on who takes part) and hang the
+    // grid.  Here nothing is in flight: every sub-round barrier of the previous window completed before its end barrier.
+    const unsigned long long sub_base = __ldcg(&cfg.bar[1].arrive);
+    const int ema_win = __ldcg(&ctl->ema16);
     grid_barrier(cfg.bar, bs_all, G, false);
     phase_done(1);
 
@@ -454,10 +474,10 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     for (int j = t; j < P.m; j += GROW_THREADS) sm.obs[j] = P.obs[j];
     // the CTAs that take part in this window's sub-rounds: enough for twice the prefixes seen lately + the last CTA;
     // the others go straight to the window's end and doze there
-    const int Pn = min(G - 1, max(48, (3 * __ldcg(&ctl->ema16)) / 16 + 16));
+    const int Pn = min(G - 1, max(48, (3 * ema_win) / 16 + 16));
     const bool takes_part = cta < Pn || last;
-    // the set changes from window to window: pick the barrier's counters up where they stand (nothing is in flight)
-    bs_sub.arrived = __ldcg(&cfg.bar[1].arrive);
+    // the set changes from window to window: pick the barrier's counters up where they stood before the window's barrier
+    bs_sub.arrived = sub_base;
     int F0 = 0;
     while (takes_part && F0 < Wn) {
       const int nsub = __ldcg(&ctl->n);
