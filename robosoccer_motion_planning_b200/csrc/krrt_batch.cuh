@@ -20,6 +20,8 @@ struct BatchJob {
   const double* obstacles;  // q x m x 4
   ResultRec* out;           // q
   int* next_query;          // work counter
+  const int* list;          // when set: plan only the queries list[0 .. *list_count) (k_plan_batch2's redo list)
+  const int* list_count;
   long long* stats;         // [10] accumulated over queries
   const double* rho2;       // [cap + 1]
   int q, m, dynamic, n_iter, cap;
@@ -68,11 +70,13 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
   EnvView E = {s_obs, J.m, J.dynamic, J.R2, J.S};
   Stats st = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 
+  const int n_work = J.list ? *J.list_count : J.q;
   for (;;) {
     int qi = 0;
     if (lane == 0) qi = atomicAdd(J.next_query, 1);
     qi = __shfl_sync(FULL, qi, 0);
-    if (qi >= J.q) break;
+    if (qi >= n_work) break;
+    if (J.list) qi = J.list[qi];
     const uint32_t query_id = J.query_base + (uint32_t)qi;
     const double* gs = J.goals + 4 * (size_t)qi;
     const double* xs = J.starts + 4 * (size_t)qi;

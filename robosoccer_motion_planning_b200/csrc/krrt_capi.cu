@@ -13,6 +13,7 @@
 
 #include "../../include/krrt.h"
 #include "krrt_batch.cuh"
+#include "krrt_batch2.cuh"
 #include "krrt_kernels.cuh"
 #include "krrt_grow.cuh"
 #include "krrt_ops.cuh"
@@ -57,6 +58,9 @@ struct krrt_ctx {
   void* d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   size_t scratch_cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_rho2_batch = nullptr;
+  int* d_redo = nullptr;      // k_plan_batch2: [0] work counter of the redo pass, [1] redo count, [2..] redo list
+  size_t redo_cap = 0;
+  int batch_v1 = 0;           // KRRT_BATCH_V1=1 in the environment: the shared-memory-list kernel only (A-B timing)
   int rho2_batch_cap = -1;
   int* d_counter = nullptr;
   long long* d_batch_stats = nullptr;
@@ -161,6 +165,7 @@ void krrt_destroy(krrt_ctx* ctx) {
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
+  if (ctx->d_redo) cudaFree(ctx->d_redo);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->tm0) cudaEventDestroy(ctx->tm0);
   if (ctx->tm1) cudaEventDestroy(ctx->tm1);
@@ -260,6 +265,7 @@ static int create_impl(krrt_ctx* ctx) {
   CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
   CK(dev_alloc(ctx, &ctx->d_bar, (size_t)2));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KRRT_BATCH_V1")) ctx->batch_v1 = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
   {
     const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));

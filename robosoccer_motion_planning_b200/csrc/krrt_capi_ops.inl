@@ -286,9 +286,56 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
     CK(cudaMemcpy(ctx->d_rho2_batch, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice));
     ctx->rho2_batch_cap = cap;
   }
-  const size_t pw = batch_warp_smem_bytes(cap, m);
+  BatchJob J;
+  J.starts = d_starts; J.goals = d_goals; J.obstacles = d_obs;
+  J.out = reinterpret_cast<ResultRec*>(d_out);
+  J.next_query = ctx->d_counter;
+  J.list = nullptr; J.list_count = nullptr;
+  J.stats = ctx->d_batch_stats;
+  J.rho2 = ctx->d_rho2_batch;
+  J.q = q; J.m = m; J.dynamic = dynamic ? 1 : 0; J.n_iter = n_iter; J.cap = cap;
+  J.query_base = query_base;
+  J.r = c.r; J.R2 = c.R * c.R; J.goal_tol2 = c.goal_tol * c.goal_tol; J.S = c.S;
+  for (int k = 0; k < 4; ++k) { J.sp.lo[k] = c.lo[k]; J.sp.hi[k] = c.hi[k]; }
+  J.sp.p_direct = c.p_direct;
+  J.sp.seed = c.seed;
   const size_t smem_max = ctx->prop.sharedMemPerBlockOptin;            // 227 KB on sm_100
   const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
+  CK(cudaMemsetAsync(ctx->d_counter, 0, sizeof(int), st));
+  CK(cudaMemsetAsync(ctx->d_batch_stats, 0, sizeof(long long) * 10, st));
+
+  // ---- k_plan_batch2: near lists in registers, 16-bit links, one CTA of up to 16 warps per SM
+  const size_t pw2 = batch2_warp_smem_bytes(cap, m);
+  const int w2 = (int)std::min<size_t>(B2_MAX_WARPS, (smem_max - 1024) / pw2);
+  const bool use_v2 = !ctx->batch_v1 && cap <= 65534 && w2 >= 1;
+  if (use_v2) {
+    if (ctx->redo_cap < (size_t)q + 2) {
+      if (ctx->d_redo) CK(cudaFree(ctx->d_redo));
+      ctx->d_redo = nullptr;
+      ctx->redo_cap = 0;
+      CK(cudaMalloc((void**)&ctx->d_redo, sizeof(int) * ((size_t)q + 2)));
+      ctx->redo_cap = (size_t)q + 2;
+    }
+    CK(cudaMemsetAsync(ctx->d_redo, 0, sizeof(int) * 2, st));
+    Batch2Job J2;
+    J2.b = J;
+    J2.redo_count = ctx->d_redo + 1;
+    J2.redo_list = ctx->d_redo + 2;
+    const size_t smem2 = (size_t)w2 * pw2;
+    CK(cudaFuncSetAttribute(k_plan_batch2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    int grid2 = ctx->prop.multiProcessorCount;
+    grid2 = (int)std::max<long long>(1, std::min<long long>(grid2, ((long long)q + w2 - 1) / w2));
+    k_plan_batch2<<<grid2, w2 * 32, smem2, st>>>(J2);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    // queries whose near set outgrew the registers (none on the soccer-field configurations) are planned by k_plan_batch
+    J.next_query = ctx->d_redo;
+    J.list = ctx->d_redo + 2;
+    J.list_count = ctx->d_redo + 1;
+  }
+
+  // ---- k_plan_batch: every list in shared memory (the whole batch, or k_plan_batch2's redo list)
+  const size_t pw = batch_warp_smem_bytes(cap, m);
   REQUIRE(pw <= smem_max, KRRT_ERR_UNSUPPORTED,
           "n_iter too large for the shared-memory batched planner; use krrt_grow per query");
   int best_w = 1, best_total = 0, best_ctas = 1;
@@ -306,21 +353,7 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
   }
   const size_t smem = (size_t)best_w * pw;
   CK(cudaFuncSetAttribute(k_plan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  BatchJob J;
-  J.starts = d_starts; J.goals = d_goals; J.obstacles = d_obs;
-  J.out = reinterpret_cast<ResultRec*>(d_out);
-  J.next_query = ctx->d_counter;
-  J.stats = ctx->d_batch_stats;
-  J.rho2 = ctx->d_rho2_batch;
-  J.q = q; J.m = m; J.dynamic = dynamic ? 1 : 0; J.n_iter = n_iter; J.cap = cap;
-  J.query_base = query_base;
-  J.r = c.r; J.R2 = c.R * c.R; J.goal_tol2 = c.goal_tol * c.goal_tol; J.S = c.S;
-  for (int k = 0; k < 4; ++k) { J.sp.lo[k] = c.lo[k]; J.sp.hi[k] = c.hi[k]; }
-  J.sp.p_direct = c.p_direct;
-  J.sp.seed = c.seed;
-  CK(cudaMemsetAsync(ctx->d_counter, 0, sizeof(int), st));
-  CK(cudaMemsetAsync(ctx->d_batch_stats, 0, sizeof(long long) * 10, st));
-  long long warps_needed = q;
+  long long warps_needed = q;   // (as the redo pass: every warp exits after one atomic when the list is empty)
   int grid = ctx->prop.multiProcessorCount * best_ctas;
   grid = (int)std::max<long long>(1, std::min<long long>(grid, (warps_needed + best_w - 1) / best_w));
   k_plan_batch<<<grid, best_w * 32, smem, st>>>(J);

@@ -282,6 +282,65 @@ def test_plan_batch_no_obstacles_and_stats(gpu_required):
     assert G.batch_stats() == tot
 
 
+def _oracle_batch_stats(starts, goals, obs, dynamic, n_iter, **cfg_kw):
+    tot = None
+    for i in range(len(starts)):
+        P = ob.OraclePlanner(capacity=n_iter + 2, query_id=i, **cfg_kw)
+        P.set_obstacles(obs[i], dynamic)
+        P.set_start(starts[i])
+        P.grow(goals[i], n_iter)
+        s = P.stats()
+        tot = s if tot is None else {k: tot[k] + s[k] for k in s}
+    return tot
+
+
+def test_plan_batch_near_overflow_takes_the_redo_pass(gpu_required):
+    """A radius that makes every node a neighbour: near sets pass 64 entries (what k_plan_batch2 keeps in registers), so the
+    queries are handed to k_plan_batch through the redo list — results and counters must not show it."""
+    q, n_iter = 48, 130
+    starts, goals, obs = scenes.batch_queries(q, 9, seed=4)
+    kw = dict(p_direct=0.1, gamma=60.0, rho_max=40.0)
+    G = capi.Planner(**kw)
+    out = G.plan_batch(starts, goals, obs, 1, n_iter)
+    ref = ob.plan_batch(ob.default_config(**kw), starts, goals, obs, 1, n_iter, nthreads=8)
+    for f in out.dtype.names:
+        assert np.array_equal(out[f], ref[f]), f
+    tot = _oracle_batch_stats(starts, goals, obs, 1, n_iter, **kw)
+    assert tot["sum_near"] > 64 * q            # the near sets did outgrow the registers
+    assert G.batch_stats() == tot
+
+
+@pytest.mark.parametrize("dynamic,S,m", [(1, 10, 9), (0, 10, 9), (1, 7, 3), (1, 40, 2), (1, 1, 5), (1, 70, 1), (1, 16, 64)])
+def test_plan_batch_edge_test_lane_maps(gpu_required, dynamic, S, m):
+    """k_plan_batch2 tests an edge with lane = (sample point, obstacle group): every split of the 32 lanes (S x m below,
+    at, and above 32; S above the h table) must give the sequential planner's trees and counters."""
+    q, n_iter = 32, 90
+    starts, goals, obs = scenes.batch_queries(q, m, seed=9)
+    kw = dict(p_direct=0.1, S=S)
+    G = capi.Planner(**kw)
+    out = G.plan_batch(starts, goals, obs, dynamic, n_iter)
+    ref = ob.plan_batch(ob.default_config(**kw), starts, goals, obs, dynamic, n_iter, nthreads=8)
+    for f in out.dtype.names:
+        assert np.array_equal(out[f], ref[f]), f
+    assert G.batch_stats() == _oracle_batch_stats(starts, goals, obs, dynamic, n_iter, **kw)
+
+
+def test_plan_batch_both_kernels_agree(gpu_required, monkeypatch):
+    """KRRT_BATCH_V1=1 plans the whole batch with k_plan_batch (lists in shared memory); the default is k_plan_batch2."""
+    q, n_iter = 500, 200
+    starts, goals, obs = scenes.batch_queries(q, 9, seed=21)
+    G2 = capi.Planner(p_direct=0.1)
+    out2 = G2.plan_batch(starts, goals, obs, 1, n_iter, query_base=77)
+    st2 = G2.batch_stats()
+    monkeypatch.setenv("KRRT_BATCH_V1", "1")
+    G1 = capi.Planner(p_direct=0.1)
+    monkeypatch.delenv("KRRT_BATCH_V1")
+    out1 = G1.plan_batch(starts, goals, obs, 1, n_iter, query_base=77)
+    assert np.array_equal(out1.view(np.uint8), out2.view(np.uint8))
+    assert G1.batch_stats() == st2
+    assert G1.launch_count == 1 and G2.launch_count == 2     # k_plan_batch | k_plan_batch2 + the (empty) redo pass
+
+
 def test_large_tree_100k_properties_and_parity(gpu_required):
     """BASELINE config 3 (single large tree, 100k iterations): size-independent invariants on the GPU tree,
     then full bit parity (the oracle's kd-tree finishes this in a few seconds)."""
