@@ -45,6 +45,15 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def fp64_peak():
+    """FP64 vector peak in TFLOP/s: measured on this pool's B200 by tests/native/fp_peak.cu (profiles/r1_fp_peak.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_fp_peak.json")) as f:
+            return float(json.load(f)["fp64_fma_tflops"]), "measured (profiles/r1_fp_peak.json, FMA-chain microbenchmark)"
+    except Exception:
+        return 37.0, "fallback (nominal B200 FP64 vector)"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -293,16 +302,27 @@ def run_ours(args, rank, world, local_rank):
     p_s = torch.from_numpy(bs).pin_memory().numpy()
     p_g = torch.from_numpy(bg).pin_memory().numpy()
     p_o = torch.from_numpy(bo).pin_memory().numpy()
-    Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo)
+    p_out = torch.zeros((hi - lo) * item, dtype=torch.uint8).pin_memory().numpy().view(capi.RESULT_DTYPE)
+    Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo, out=p_out)
     be_ms = 0.0
     for _ in range(bsteps):
         flush_l2()
         Gb.timer_begin()
-        out_h = Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo)
+        out_h = Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo, out=p_out)
         be_ms += Gb.timer_end()
     barrier()
     be_ms = max_over_ranks(be_ms)
+    bst = Gb.batch_stats()
+    b_flop = 134.0 * bst["steer_calls"] + 1180.0 * bst["collide_calls"]      # SURVEY 8(d) accounting, one rank's shard
+    f64_peak, f64_src = fp64_peak()
+    b_tflops = b_flop * bsteps / (b_ms * 1e-3) / 1e12
     batched = {
+        "roofline": {"bound": "fp64 pipe / latency", "kernel": "k_plan_batch2", "achieved": b_tflops, "peak": f64_peak,
+                     "unit": "TFLOP/s", "frac": b_tflops / f64_peak, "peak_source": f64_src,
+                     "algorithmic_flop_per_launch": b_flop,
+                     "note": "134 flop per steering pair + 1180 flop per edge test (SURVEY 8d), counted from the "
+                             "kernel's own steer_calls / collide_calls; trees live in shared memory, HBM traffic is the "
+                             "inputs and the 1304-byte result records only"},
         "workload": f"{BATCH_Q} queries/GPU x {BATCH_ITERS} iterations, 9 moving obstacles, p_direct=0.1 (C4; sharded sweep C5 for N>1)",
         "queries_per_sec": q_total * bsteps / (b_ms * 1e-3),
         "expansions_per_sec": q_total * BATCH_ITERS * bsteps / (b_ms * 1e-3),
@@ -376,6 +396,18 @@ def run_ours(args, rank, world, local_rank):
                                "scan_phase_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
                                "phase_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["ms"] > 0},
                                "rounds": G3.wave_stats()}
+                if label == "c3_100k":   # the same plan on one host core (kd-tree near search), once
+                    O3 = ob.OraclePlanner(capacity=iters + 2, query_id=0)
+                    O3.set_obstacles(scenes.static_obstacles(), 0)
+                    O3.set_start(start)
+                    t0 = time.perf_counter()
+                    O3.grow(None, iters)
+                    dt3 = time.perf_counter() - t0
+                    same3 = all(np.array_equal(a, b) for a, b in zip(G3.tree(), O3.tree()))
+                    line[label]["cpu_baseline"] = {"value": iters / dt3, "unit": UNIT, "cores": 1, "kind": "port",
+                                                   "sample": f"the full {iters}-iteration plan, once, kd-tree near search"}
+                    line[label]["gpu_over_cpu"] = line[label]["expansions_per_sec"] / (iters / dt3)
+                    line[label]["parity_vs_oracle"] = "bit-exact" if same3 else "MISMATCH"
                 G3.close()
     if rank == 0:
         print(json.dumps(line), flush=True)

@@ -353,14 +353,18 @@ class Planner:
         return idx[:min(cnt.value, cap)].copy(), nearest.value, nd2.value
 
     # solve_rrt() for q independent queries (…node.cpp:167-196)
-    def plan_batch(self, starts, goals, obstacles, dynamic, n_iter, query_base=0):
+    def plan_batch(self, starts, goals, obstacles, dynamic, n_iter, query_base=0, out=None):
+        """krrt_plan_batch on host buffers.  `out`: a caller-owned array of RESULT_DTYPE records (e.g. pinned memory, so
+        the device-to-host copy of the 1304-byte records runs at full PCIe rate); allocated when None."""
         starts = _f64(starts, (-1, 4))
         goals = _f64(goals, (-1, 4))
         q = starts.shape[0]
         obstacles = np.asarray(obstacles, dtype=np.float64)
         obstacles = _f64(obstacles, (q, -1, 4)) if obstacles.size else np.zeros((q, 0, 4))
         m = obstacles.shape[1]
-        out = np.zeros(q, dtype=RESULT_DTYPE)
+        if out is None:
+            out = np.zeros(q, dtype=RESULT_DTYPE)
+        assert out.dtype == RESULT_DTYPE and out.shape == (q,) and out.flags.c_contiguous
         self._ck(lib().krrt_plan_batch(self.h, _d(starts), _d(goals), _d(obstacles), q, m, int(dynamic), int(n_iter),
                                        int(query_base), out.ctypes.data))
         return out
