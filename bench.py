@@ -104,6 +104,26 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Everything a library prints on stdout (NCCL's version banner, ...) goes to stderr: stdout carries ONE JSON line."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def c2_scene():
     from robosoccer_motion_planning_b200 import scenes
     return scenes.dynamic_obstacles(), scenes.START, scenes.GOAL
@@ -151,7 +171,7 @@ def run_reference(args, rank, world):
                     "iters": BATCH_ITERS, "cores": allc},
         "solved": int(out["solved"].sum()),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------- our arm
@@ -410,7 +430,7 @@ def run_ours(args, rank, world, local_rank):
                     line[label]["parity_vs_oracle"] = "bit-exact" if same3 else "MISMATCH"
                 G3.close()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -428,6 +448,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args, rank, max(world, args.gpus if world == 1 else world))
     else:
