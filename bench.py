@@ -274,7 +274,9 @@ def run_ours(args, rank, world, local_rank):
                 "share_of_step": 1.0,
                 "phase_shares": shares,
                 "scan_phase_GBps_algorithmic": scan_only,
+                "scan_index": dict(G.scan_stats(), visited_bytes=32.0 * G.scan_stats()["visited_pairs"]),
                 "note": "one persistent kernel per grow call; algorithmic bytes = 32 B x tree nodes x samples scanned "
+                        "(brute-force equivalent; scan_index.visited_bytes is what the grid-indexed scan really read) "
                         "(SURVEY 8d: N x 32 B per expansion) over the kernel's whole duration.  A <= 20k-node tree is "
                         "640 KB and L2-resident: this config is bound by the latency chain of the commit sub-rounds "
                         "(decide / validate / apply, three grid barriers each), not by HBM; scan_phase_GBps is the "
@@ -415,6 +417,7 @@ def run_ours(args, rank, world, local_rank):
                                "kernel_frac_of_hbm_peak": t3["scan_node_samples"] * 32 / (t_plain * 1e-3) / 1e9 / peak,
                                "scan_phase_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
                                "phase_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["ms"] > 0},
+                               "scan_index": dict(G3.scan_stats(), visited_bytes=32.0 * G3.scan_stats()["visited_pairs"]),
                                "rounds": G3.wave_stats()}
                 if label == "c3_100k":   # the same plan on one host core (kd-tree near search), once
                     O3 = ob.OraclePlanner(capacity=iters + 2, query_id=0)

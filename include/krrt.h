@@ -199,6 +199,9 @@ int krrt_debug_clocks(krrt_ctx* ctx, int64_t out[16]);
  * spent in the neighbour-scan kernel (for the roofline line).                                   */
 int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* scan_launches,
                      double* scan_node_samples);
+/* Neighbour scan of the last krrt_grow call: (node, sample) pairs really evaluated (scan_node_samples above is the
+ * brute-force equivalent), rebuilds of the spatial index since krrt_set_start, nodes it covers now.  */
+int krrt_scan_stats(krrt_ctx* ctx, double* visited_pairs, int64_t* rebuilds, int32_t* indexed_nodes);
 
 #ifdef __cplusplus
 }

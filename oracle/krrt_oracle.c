@@ -410,6 +410,13 @@ static void unlink_child(ko_planner* p, int c) {
 }
 
 /* == rrt.setStart(xs); rrt.setIteration(0) (…node.cpp:135-136) */
+/* NeighborRadius parameters changed on a live planner (what krrt_set_params does for gamma / rho_max) */
+void ko_set_near_radius(ko_planner* p, double gamma, double rho_max) {
+  p->cfg.gamma = gamma;
+  p->cfg.rho_max = rho_max;
+  for (int n = 0; n <= p->cfg.capacity; ++n) p->rho2[n] = ko_rho2(&p->cfg, n);
+}
+
 void ko_set_start(ko_planner* p, const double x0[4]) {
   p->n = 1; p->iter = 0;
   memcpy(p->state, x0, sizeof(double) * 4);

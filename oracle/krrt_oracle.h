@@ -92,6 +92,7 @@ ko_planner* ko_create(const ko_config* c);
 void ko_destroy(ko_planner* p);
 void ko_set_obstacles(ko_planner* p, const double* xyvxvy, int m, int dynamic);
 void ko_set_start(ko_planner* p, const double x0[4]);
+void ko_set_near_radius(ko_planner* p, double gamma, double rho_max);
 /* n_iter expansions. samples: NULL or n_iter x 4 (a row whose first entry is NaN
  * means "draw internally").  returns 1 when a goal node exists at the end.      */
 int ko_grow(ko_planner* p, const double* goal, int n_iter, const double* samples, int* goal_index);

@@ -31,7 +31,7 @@ EXPORTS = (
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
-    "krrt_solve_inputs",
+    "krrt_solve_inputs", "krrt_scan_stats",
 )
 
 
@@ -127,6 +127,7 @@ def lib():
     L.krrt_ingest_vision.argtypes = [P, F, I, ctypes.c_int, F, ctypes.c_int, I, ctypes.c_int, D, D, I, D, I]
     L.krrt_ingest_vision_device.argtypes = ([P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                              ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 6)
+    L.krrt_scan_stats.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64), I]
     L.krrt_debug_clocks.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
@@ -417,6 +418,11 @@ class Planner:
         self._ck(lib().krrt_ingest_vision_device(self.h, d_team, d_agent_id, int(n_team), d_rival, int(n_rival), d_self_id,
                                                  int(f), d_self_state, d_heading, d_self_index, d_obstacles, d_n_obs,
                                                  stream or None))
+
+    def scan_stats(self):
+        v, r, g = ctypes.c_double(0), ctypes.c_int64(0), ctypes.c_int32(0)
+        self._ck(lib().krrt_scan_stats(self.h, ctypes.byref(v), ctypes.byref(r), ctypes.byref(g)))
+        return {"visited_pairs": v.value, "index_rebuilds": r.value, "indexed_nodes": g.value}
 
     @property
     def launch_count(self):

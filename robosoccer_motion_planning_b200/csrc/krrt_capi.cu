@@ -47,6 +47,7 @@ struct krrt_ctx {
   int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
   int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
   GridBar* d_bar = nullptr;    // its two grid barriers
+  GridIndex gi{};              // spatial index of its neighbour scan
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
@@ -201,7 +202,8 @@ static int create_impl(krrt_ctx* ctx) {
   const size_t cap = (size_t)c.capacity;
   {
     const size_t bcn = (size_t)c.batch * c.near_cap;
-    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + (cap + 1) * 8 + bcn * (4 + 8 * 5) +
+    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + (GRID_CELLS_MAX + 1) * 4 +
+                  (cap + 1) * 8 + bcn * (4 + 8 * 5) +
                   (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
 #ifdef KRRT_DEBUG_CLK
     need += (size_t)32 * ((1 << 20) + 1) + 4096;
@@ -254,6 +256,15 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &W.wmin, cap));
   CK(dev_alloc(ctx, &W.amin, cap));
   CK(dev_alloc(ctx, &W.lock, cap));
+  CK(dev_alloc(ctx, &ctx->gi.pos, cap));
+  CK(dev_alloc(ctx, &ctx->gi.vel, cap));
+  CK(dev_alloc(ctx, &ctx->gi.id, cap));
+  CK(dev_alloc(ctx, &ctx->gi.off, cap));
+  CK(dev_alloc(ctx, &ctx->gi.cell, (size_t)GRID_CELLS_MAX + 1));
+  ctx->gi.enabled = 1;
+  ctx->gi.min_n = 8192;
+  if (const char* e = std::getenv("KRRT_GRID_INDEX")) ctx->gi.enabled = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KRRT_GRID_MIN_N")) ctx->gi.min_n = std::max(2, std::atoi(e));
   CK(dev_alloc(ctx, &W.nn_d2, (size_t)1024));
   CK(dev_alloc(ctx, &W.nn_idx, (size_t)1024));
 #ifdef KRRT_DEBUG_CLK
@@ -403,6 +414,7 @@ __global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_
   ctl->full = 0;
   ctl->scan_pairs = 0.0;
   ctl->scan_nodes = 0.0;
+  ctl->scan_visited = 0.0;
   ctl->windows = 0;
   for (int k = 0; k < 8; ++k) ctl->phase_clk[k] = 0;
   for (int k = 0; k < 16; ++k) ctl->dbg_clk[k] = 0;
@@ -443,6 +455,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   gcfg.wave_min_n = ctx->wave_min_n;
   gcfg.user_samples = samples ? ctx->d_user : nullptr;
   gcfg.bar = ctx->d_bar;
+  gcfg.gi = ctx->gi;
   const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(ctx->Bt.near_cap));
   Ctl h;
   // ONE persistent kernel does the whole call; it only comes back early when the 23-bit epoch of the conflict marks
@@ -598,6 +611,18 @@ int krrt_last_timing(krrt_ctx* ctx, double* total_ms, double* scan_ms, int64_t* 
   if (scan_ms) *scan_ms = ctx->last_scan_ms;
   if (scan_launches) *scan_launches = ctx->last_scan_launches;
   if (scan_node_samples) *scan_node_samples = ctx->last_scan_node_samples;
+  return KRRT_OK;
+}
+
+int krrt_scan_stats(krrt_ctx* ctx, double* visited_pairs, int64_t* rebuilds, int32_t* indexed_nodes) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  if (visited_pairs) *visited_pairs = h.scan_visited;
+  if (rebuilds) *rebuilds = h.grid_rebuilds;
+  if (indexed_nodes) *indexed_nodes = h.grid_n;
   return KRRT_OK;
 }
 

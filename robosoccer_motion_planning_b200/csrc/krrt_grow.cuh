@@ -59,6 +59,7 @@ struct GrowCfg {
   int wave_min_n;
   const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
   GridBar* bar;                // [0] all CTAs, [1] the CTAs that take part in a window's sub-rounds (zero at launch)
+  GridIndex gi;                // spatial index of the neighbour scan
 };
 
 __device__ __forceinline__ void grid_barrier(GridBar* bar, BarState& st, int n, bool relaxed) {
@@ -396,14 +397,137 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       ctl->scan_nodes += (double)n0;
       ctl->windows += 1;
     }
-    // ---- scan: item = (tile of GROW_THREADS frozen nodes, chunk of the window's samples)
+    // ---- spatial index: (re)built when the part of the tree it does not cover has outgrown 1/16 of the tree, or when its
+    // cells are too small for this window's radius (krrt_set_params raised it).  Every CTA takes the same decision from the
+    // same values (read after the previous window's end barrier; written below by one thread, a barrier before any use).
+    int gn = 0, gw = 1, gh = 1;
+    double g_lox = 0.0, g_loy = 0.0, g_invx = 0.0, g_invy = 0.0;
+    if (cfg.gi.enabled && n0 >= cfg.gi.min_n) {
+      gn = __ldcg(&ctl->grid_n);
+      const double gcs = __ldcg(&ctl->grid_cs);
+      const bool stale = gn == 0 || n0 - gn > max(2048, n0 >> 4) || !(gcs * gcs >= 1.001 * rmax);
+      if (stale) {
+        // geometry: cells at least 1.001 x the near radius wide (the margin dwarfs the rounding of the cell arithmetic,
+        // so two points closer than the radius on an axis are never more than one cell apart on it)
+        const double rad = sqrt(rmax);
+        const double cs = 1.001 * rad;
+        g_lox = P.sp.lo[0];
+        g_loy = P.sp.lo[1];
+        const double wx = P.sp.hi[0] - P.sp.lo[0], wy = P.sp.hi[1] - P.sp.lo[1];
+        gw = (cs > 0.0 && wx > 0.0) ? (int)fmin((double)GRID_W_MAX, fmax(1.0, floor(wx / cs))) : 1;
+        gh = (cs > 0.0 && wy > 0.0) ? (int)fmin((double)GRID_H_MAX, fmax(1.0, floor(wy / cs))) : 1;
+        g_invx = wx > 0.0 ? (double)gw / wx : 0.0;
+        g_invy = wy > 0.0 ? (double)gh / wy : 0.0;
+        const int ncell = gw * gh;
+        for (int c = cta * GROW_THREADS + t; c <= ncell; c += G * GROW_THREADS) cfg.gi.cell[c] = 0;
+        grid_barrier(cfg.bar, bs_all, G, false);
+        for (int i = cta * GROW_THREADS + t; i < n0; i += G * GROW_THREADS) {
+          const double2 p = __ldcg(&T.pos[i]);
+          const int cx = min(gw - 1, max(0, (int)floor((p.x - g_lox) * g_invx)));
+          const int cy = min(gh - 1, max(0, (int)floor((p.y - g_loy) * g_invy)));
+          cfg.gi.off[i] = atomicAdd(&cfg.gi.cell[cy * gw + cx], 1);
+        }
+        grid_barrier(cfg.bar, bs_all, G, false);
+        if (cta == 0) {  // exclusive prefix of the counts, in place: a run of cells per thread
+          int* part = reinterpret_cast<int*>(dyn_smem);
+          const int per = (ncell + GROW_THREADS - 1) / GROW_THREADS;
+          const int c0 = min(ncell, t * per), c1 = min(ncell, c0 + per);
+          int sum = 0;
+          for (int c = c0; c < c1; ++c) sum += __ldcg(&cfg.gi.cell[c]);
+          part[t] = sum;
+          __syncthreads();
+          if (t == 0) {
+            int acc = 0;
+            for (int k = 0; k < GROW_THREADS; ++k) {
+              const int v = part[k];
+              part[k] = acc;
+              acc += v;
+            }
+            cfg.gi.cell[ncell] = acc;
+          }
+          __syncthreads();
+          int acc = part[t];
+          for (int c = c0; c < c1; ++c) {
+            const int v = __ldcg(&cfg.gi.cell[c]);
+            cfg.gi.cell[c] = acc;
+            acc += v;
+          }
+        }
+        grid_barrier(cfg.bar, bs_all, G, false);
+        for (int i = cta * GROW_THREADS + t; i < n0; i += G * GROW_THREADS) {
+          const double2 p = __ldcg(&T.pos[i]);
+          const int cx = min(gw - 1, max(0, (int)floor((p.x - g_lox) * g_invx)));
+          const int cy = min(gh - 1, max(0, (int)floor((p.y - g_loy) * g_invy)));
+          const int slot = __ldcg(&cfg.gi.cell[cy * gw + cx]) + cfg.gi.off[i];
+          cfg.gi.pos[slot] = p;
+          cfg.gi.vel[slot] = __ldcg(&T.vel[i]);
+          cfg.gi.id[slot] = i;
+        }
+        if (last && t == 0) {
+          ctl->grid_n = n0;
+          ctl->grid_w = gw;
+          ctl->grid_h = gh;
+          ctl->grid_cs = cs;
+          ctl->grid_lox = g_lox; ctl->grid_loy = g_loy; ctl->grid_invx = g_invx; ctl->grid_invy = g_invy;
+          ctl->grid_rebuilds += 1;
+        }
+        gn = n0;
+        grid_barrier(cfg.bar, bs_all, G, false);
+      } else {
+        gw = __ldcg(&ctl->grid_w);
+        gh = __ldcg(&ctl->grid_h);
+        g_lox = __ldcg(&ctl->grid_lox); g_loy = __ldcg(&ctl->grid_loy);
+        g_invx = __ldcg(&ctl->grid_invx); g_invy = __ldcg(&ctl->grid_invy);
+      }
+    }
+    // ---- scan, indexed part: item = (sample, cell row of its 3 x 3 block) = one contiguous range of the sorted copy
+    if (gn > 0) {
+      for (int item = cta; item < 3 * Wn; item += G) {
+        const int b = item / 3, dy = item - 3 * b - 1;
+        const State4 sb = sm.u.ss[b];
+        const int cx = min(gw - 1, max(0, (int)floor((sb.x - g_lox) * g_invx)));
+        const int cy = min(gh - 1, max(0, (int)floor((sb.y - g_loy) * g_invy)));
+        const int row = cy + dy;
+        if (row < 0 || row >= gh) continue;
+        const int begin = __ldcg(&cfg.gi.cell[row * gw + max(cx - 1, 0)]);
+        const int end = __ldcg(&cfg.gi.cell[row * gw + min(cx + 1, gw - 1) + 1]);
+        // four slots per thread and trip, all loads issued before the first use: the range is read at L2 latency
+        for (int slot0 = begin + t; slot0 < end; slot0 += 4 * GROW_THREADS) {
+          double2 p[4], v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int slot = slot0 + u * GROW_THREADS;
+            if (slot < end) {
+              p[u] = __ldcg(&cfg.gi.pos[slot]);
+              v[u] = __ldcg(&cfg.gi.vel[slot]);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int slot = slot0 + u * GROW_THREADS;
+            if (slot < end) {
+              const State4 a = {p[u].x, p[u].y, v[u].x, v[u].y};
+              const double d = dist2(a, sb);
+              if (d <= rmax) {
+                if (d == 0.0) Bt.dup[b] = 1;
+                append_candidate(Bt, b, __ldcg(&cfg.gi.id[slot]), d);
+              }
+            }
+          }
+        }
+        if (t == 0 && end > begin) atomicAdd(&ctl->scan_visited, (double)(end - begin));
+      }
+    }
+    if (last && t == 0) atomicAdd(&ctl->scan_visited, (double)(n0 - gn) * (double)Wn);
+    // ---- scan, direct part (the whole tree while there is no index): item = (tile of GROW_THREADS frozen nodes,
+    // chunk of the window's samples)
     {
-      const int tiles = (n0 + GROW_THREADS - 1) / GROW_THREADS;
-      const int chunks = max(1, min(8, (2 * G + tiles - 1) / tiles));
+      const int tiles = (n0 - gn + GROW_THREADS - 1) / GROW_THREADS;
+      const int chunks = max(1, min(8, (2 * G + tiles - 1) / max(tiles, 1)));
       const int per = (Wn + chunks - 1) / chunks;
       for (int item = cta; item < tiles * chunks; item += G) {
         const int tile = item / chunks, ch = item - tile * chunks;
-        const int i = tile * GROW_THREADS + t;
+        const int i = gn + tile * GROW_THREADS + t;
         const int c0 = ch * per, c1 = min(Wn, c0 + per);
         if (i < n0) {
           const State4 a = load_state_cg(T, i);

@@ -44,6 +44,14 @@ struct Ctl {  // device-resident control block of one single-tree context
   long long windows;      // windows scanned since the current krrt_grow call began
   long long phase_clk[8]; // SM clocks the last CTA spent per phase since the call began: 0 scan, 1 steer, 2 decide,
                           // 3 validate, 4 apply + finish, 5 sequential windows
+  // spatial index of the neighbour scan (krrt_grow.cuh: uniform grid over the position plane, rebuilt as the tree grows)
+  int grid_n;             // nodes [0, grid_n) are in the sorted copy; the rest of the tree is scanned directly (0: no index)
+  int grid_w, grid_h;     // cells per axis
+  int grid_pad;
+  double grid_cs;         // the near radius the cell size was chosen for (cells are at least 1.001 x that wide)
+  double grid_lox, grid_loy, grid_invx, grid_invy;  // cell = clamp(floor((p - lo) * inv), 0, cells - 1)
+  double scan_visited;    // (node, sample) pairs the scan really evaluated since the current krrt_grow call began
+  long long grid_rebuilds;
   long long dbg_clk[16];
   long long dbg_cta[3][160];  // per CTA index: decide / validate / apply(+finish) cycles, sub-rounds it was active in  // KRRT_DEBUG_CLK builds: step clocks inside decide / apply of CTA 0, max over CTAs
 };
@@ -106,6 +114,20 @@ struct Wave {
   double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...
   int* nn_idx;      // ... (squared distance, node index)
   int* dbg_log;     // KRRT_DEBUG_CLK builds: [0] = entries, then 8 ints per decided sample (else nullptr)
+};
+
+// Uniform grid over the position plane for the neighbour scan of a big tree: a copy of the node states sorted by cell
+// (cells of at least the near radius, so a sample's neighbours lie in its 3 x 3 block = three contiguous cell ranges).
+constexpr int GRID_W_MAX = 96, GRID_H_MAX = 64;
+constexpr int GRID_CELLS_MAX = GRID_W_MAX * GRID_H_MAX;
+struct GridIndex {
+  double2* pos;   // [capacity] sorted copy of T.pos
+  double2* vel;   // [capacity] ... of T.vel
+  int* id;        // [capacity] node index of each sorted slot
+  int* off;       // [capacity] rebuild scratch: rank of node i inside its cell
+  int* cell;      // [GRID_CELLS_MAX + 1] rebuild: counts; afterwards exclusive starts, cell[cells] = grid_n
+  int enabled;    // KRRT_GRID_INDEX=0 in the environment: every window scans the whole tree
+  int min_n;      // smallest tree that gets an index
 };
 
 // marks carry the round id, so they never need clearing: (round << 9) | (511 - sample), combined with atomicMax

@@ -82,6 +82,8 @@ def lib():
     L.ko_edge_state.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D]
     L.ko_solve.argtypes = [D, D, ctypes.c_double, ctypes.c_double, ctypes.c_double, D, ctypes.c_int]
     L.ko_solve.restype = ctypes.c_int
+    L.ko_set_near_radius.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_double]
+    L.ko_set_near_radius.restype = None
     L.ko_solve_inputs.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D, ctypes.c_int]
     L.ko_solve_inputs.restype = ctypes.c_int
     L.ko_edge_collide.argtypes = [D, D, ctypes.c_double, ctypes.c_double, D, ctypes.c_int, ctypes.c_int,
@@ -211,6 +213,9 @@ class OraclePlanner:
     def set_obstacles(self, obs, dynamic):
         obs = np.ascontiguousarray(obs, dtype=np.float64).reshape(-1, 4)
         lib().ko_set_obstacles(self.h, _d(obs), obs.shape[0], int(dynamic))
+
+    def set_params(self, gamma, rho_max):
+        lib().ko_set_near_radius(self.h, float(gamma), float(rho_max))
 
     def set_start(self, x0):
         x0 = np.ascontiguousarray(x0, dtype=np.float64)

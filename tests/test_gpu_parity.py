@@ -410,3 +410,46 @@ def test_set_params_equals_fresh_context(gpu_required):
     assert_same_tree(G, O)
     with pytest.raises(capi.KrrtError):
         G.set_params(capacity=8192)
+
+
+@pytest.mark.parametrize("dynamic,batch,min_n", [(0, 0, 300), (1, 0, 300), (1, 37, 1000), (0, 512, 2100)])
+def test_grid_index_small_threshold(gpu_required, monkeypatch, dynamic, batch, min_n):
+    """The spatial index of the neighbour scan (uniform grid over the position plane, rebuilt as the tree grows) switched
+    on for small trees, so a 6000-iteration plan sees many rebuilds: same tree, same counters, fewer pairs visited."""
+    monkeypatch.setenv("KRRT_GRID_MIN_N", str(min_n))
+    G, O = make_pair(gpu_required, dynamic=dynamic, p_direct=0.1 if dynamic else 0.0, batch=batch)
+    monkeypatch.delenv("KRRT_GRID_MIN_N")
+    for k in range(3):                       # three calls: the index survives from one krrt_grow call to the next
+        assert G.grow(scenes.GOAL, 2000) == O.grow(scenes.GOAL, 2000)
+    assert_same_tree(G, O)
+    ss = G.scan_stats()
+    assert ss["index_rebuilds"] >= (2 if min_n <= 1000 else 1) and 0 < ss["indexed_nodes"] <= G.size
+    assert ss["visited_pairs"] < 0.7 * G.last_timing()["scan_node_samples"]
+
+
+def test_grid_index_off_is_the_same_tree(gpu_required, monkeypatch):
+    monkeypatch.setenv("KRRT_GRID_INDEX", "0")
+    G, O = make_pair(gpu_required, dynamic=0, capacity=30002)
+    monkeypatch.delenv("KRRT_GRID_INDEX")
+    G.grow(None, 30000)
+    O.grow(None, 30000)
+    assert_same_tree(G, O)
+    ss = G.scan_stats()
+    assert ss["index_rebuilds"] == 0 and ss["visited_pairs"] == G.last_timing()["scan_node_samples"]
+
+
+def test_grid_index_survives_a_larger_radius(gpu_required, monkeypatch):
+    """krrt_set_params raises the near radius on a live tree: the cells of the index are too small for it, so the next
+    window rebuilds it (a stale index would silently drop neighbours)."""
+    monkeypatch.setenv("KRRT_GRID_MIN_N", "500")
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, gamma=4.0, rho_max=2.0)
+    monkeypatch.delenv("KRRT_GRID_MIN_N")
+    assert G.grow(scenes.GOAL, 3000) == O.grow(scenes.GOAL, 3000)
+    r0 = G.scan_stats()["index_rebuilds"]
+    assert r0 >= 1
+    G.set_params(gamma=7.0, rho_max=4.0)
+    O.set_params(gamma=7.0, rho_max=4.0)
+    assert G.grow(scenes.GOAL, 200) == O.grow(scenes.GOAL, 200)
+    assert G.scan_stats()["index_rebuilds"] > r0
+    assert G.grow(scenes.GOAL, 1500) == O.grow(scenes.GOAL, 1500)
+    assert_same_tree(G, O)
