@@ -267,8 +267,14 @@ def run_ours(args, rank, world, local_rank):
     scan_bytes = lt["scan_node_samples"] * 32.0
     achieved = scan_bytes / (lt["total_ms"] * 1e-3) / 1e9 if lt["total_ms"] > 0 else 0.0
     scan_only = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_k_grow_traffic.json")) as f:
+            tr = json.load(f)
+        traffic = float(tr["dram_bytes_read"] + tr["dram_bytes_write"])   # one ncu --set full capture of this kernel
+    except Exception:
+        traffic = None
     roofline = {"bound": "hbm", "kernel": "k_grow", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": scan_bytes,
                 "avg_launch_us": 1e3 * lt["total_ms"],
                 "share_of_step": 1.0,
@@ -398,6 +404,56 @@ def run_ours(args, rank, world, local_rank):
                                            "sample": f"{qs} of the {BATCH_Q} queries"}
         line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
                                                else "MISMATCH")
+        # config 0 (rrtstar_benchmark, C1): static obstacles, fixed seed, 10k iterations — GPU and the CPU port, same plan
+        G1 = capi.Planner(device=local_rank, capacity=10002, batch=args.batch, goal_tol=0.5)
+        O1 = ob.OraclePlanner(capacity=10002, query_id=0, goal_tol=0.5)
+        for P_ in (G1, O1):
+            P_.set_obstacles(scenes.static_obstacles(), 0)
+            P_.set_start(start)
+        G1.grow(goal, 10000)                       # warm-up
+        G1.set_start(start)
+        flush_l2()
+        r1 = G1.grow(goal, 10000)
+        ms1 = G1.last_timing()["total_ms"]
+        t0 = time.perf_counter()
+        ro1 = O1.grow(goal, 10000)
+        dt1 = time.perf_counter() - t0
+        same1 = r1 == ro1 and all(np.array_equal(a, b) for a, b in zip(G1.tree(), O1.tree()))
+        line["c1_rrtstar_benchmark"] = {
+            "workload": "C1: 9 static obstacles, fixed seed, 10000 iterations, p_direct = 0, goal region 0.5",
+            "cost": float(G1.result(*r1)["cost"]) if r1[0] else None,
+            "expansions_per_sec": 10000 / (ms1 * 1e-3), "ms": ms1, "nodes": G1.size, "solved": bool(r1[0]),
+            "cpu_baseline": {"value": 10000 / dt1, "unit": UNIT, "cores": 1, "kind": "port", "sample": "the full plan, once"},
+            "parity_vs_oracle": "bit-exact" if same1 else "MISMATCH"}
+        G1.close()
+        # the README's curves: computation time and solution cost against node size on the C1 scene,
+        # 1024 seeds per size through the batched planner; CPU port on all host cores beside it (context: the README's
+        # numbers are an i3 at 2.0 GHz, scene and trial count not stated)
+        curve = []
+        qn = 1024
+        c_s = np.tile(start, (qn, 1))
+        c_g = np.tile(goal, (qn, 1))
+        c_o = np.tile(scenes.static_obstacles(), (qn, 1, 1))
+        for p_dir in (0.0, 0.1):
+            Gc = capi.Planner(device=local_rank, p_direct=p_dir, goal_tol=0.5)
+            for nodes in (10, 25, 50, 75, 100, 150, 200):
+                Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
+                Gc.timer_begin()
+                oc = Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
+                msb = Gc.timer_end()
+                tcp = time.perf_counter()
+                rc_ = ob.plan_batch(ob.default_config(p_direct=p_dir, goal_tol=0.5), c_s[:4 * allc], c_g[:4 * allc], c_o[:4 * allc], 0,
+                                    nodes, nthreads=allc)
+                tcp = time.perf_counter() - tcp
+                sv = oc["solved"] != 0
+                curve.append({"p_direct": p_dir, "node_size": nodes, "gpu_ms_per_plan_batched": msb / qn,
+                              "cpu_port_ms_per_plan_1core": 1e3 * tcp / 4.0,   # 4 plans per thread, all threads busy
+                              "solved_frac": float(sv.mean()),
+                              "mean_cost": float(oc["cost"][sv].mean()) if sv.any() else None,
+                              "parity": bool(np.array_equal(oc[:4 * allc].view(np.uint8), rc_.view(np.uint8)))})
+            Gc.close()
+        line["readme_curve"] = {"scene": "C1 start/goal, 9 static obstacles, goal region 0.5 (state-space distance), 1024 seeds per point (query_id = seed)",
+                                "points": curve}
         # config 3: single large tree, 100k iterations, static obstacles (+ the 1M-iteration tree with --c3-1m)
         if not args.skip_c3:
             for label, iters in (("c3_100k", 100000),) + ((("c3_1m", 1000000),) if args.c3_1m else ()):
