@@ -59,12 +59,14 @@ def test_invalid_config_rejected(built):
 
 def test_product_does_not_touch_the_oracle():
     """Nothing under the package or include/ may reference oracle/ (the oracle is test infrastructure)."""
-    pkg = os.path.join(ROOT, "robosoccer_motion_planning_b200")
-    for base, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".hpp", "Makefile")):
-                txt = open(os.path.join(base, f), errors="ignore").read()
-                assert "krrt_oracle" not in txt and "oracle_binding" not in txt, os.path.join(base, f)
+    for top in ("robosoccer_motion_planning_b200", "include"):
+        for base, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".hpp", "Makefile")):
+                    txt = open(os.path.join(base, f), errors="ignore").read()
+                    for word in ("krrt_oracle", "yaw_oracle", "ingest_oracle", "oracle_binding", "yaw_binding",
+                                 "ingest_binding", "oracle/"):
+                        assert word not in txt, (os.path.join(base, f), word)
     out = os.popen(f"ldd {capi.LIB_PATH}").read()
     assert "oracle" not in out
 
