@@ -6,8 +6,10 @@ collision checks, direct-goal sampling p = 0.1, 20 000 iterations.  A "step" is 
   value  RRT* expansions/s, device time of the grow call only (inputs resident in HBM)
   e2e    the same metric through the C ABI with HOST buffers: obstacle upload + start + grow + result read-back,
          CUDA events on the context's stream around the whole sequence
-N > 1: a single tree does not shard ("replicas only"): every rank plans the same scene with its own
-Philox stream (query_id = rank); value = all ranks' expansions / max-over-ranks time.  The batched-query sweep, which
+N > 1: a single tree does not shard ("replicas only"): every rank plans the same scene with the same
+Philox stream, so the per-GPU work is exactly the N = 1 work (with one stream per rank the plans differ in length by
++-30 % and the max over ranks measures the unluckiest seed: 4.88 M expansions/s at N = 8, profiles/r1_bench_n8_s25.json);
+value = all ranks' expansions / max-over-ranks time.  The batched-query sweep, which
 DOES shard (contiguous blocks + one NCCL all-gather of results), is reported in the same line under "batched".
 
 --impl reference: the CPU oracle (oracle/krrt_oracle.c — the reference's own RRT* sources are an absent submodule,
@@ -205,7 +207,7 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     obs, start, goal = c2_scene()
-    G = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, query_id=rank, batch=args.batch)
+    G = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, query_id=0, batch=args.batch)
 
     def plan_device_timed():
         G.set_obstacles(obs, 1)
@@ -366,7 +368,7 @@ def run_ours(args, rank, world, local_rank):
         "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "replicas": world, "window": int(G.cfg.batch),
-                   "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only (single tree); "
+                   "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only (single tree; every rank grows the same plan, same seed); "
                    "batched queries shard by contiguous blocks"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / args.steps},
