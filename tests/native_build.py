@@ -47,3 +47,20 @@ def build_service_check():
            "-Wl,-rpath,$ORIGIN/../../../robosoccer_motion_planning_b200/lib", "-Wl,-rpath,$ORIGIN/../../../oracle/_build"]
     subprocess.check_call(cmd)
     return exe
+
+
+def build_custom_benchmark():
+    """robosoccer_motion_planning_b200/tools/rrtstar_custom_benchmark.cpp (product tool: links libkrrt only)."""
+    from robosoccer_motion_planning_b200 import capi
+    capi.build_library()
+    os.makedirs(OUT, exist_ok=True)
+    exe = os.path.join(OUT, "rrtstar_custom_benchmark")
+    src = os.path.join(ROOT, "robosoccer_motion_planning_b200", "tools", "rrtstar_custom_benchmark.cpp")
+    deps = [src, os.path.join(ROOT, "include", "rrtstar.hpp"), os.path.join(ROOT, "include", "integrator2drrt.hpp"),
+            os.path.join(ROOT, "include", "krrt.h"), capi.LIB_PATH]
+    if os.path.exists(exe) and all(os.path.getmtime(exe) >= os.path.getmtime(d) for d in deps):
+        return exe
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-o", exe, src,
+                           "-L" + os.path.dirname(capi.LIB_PATH), "-lkrrt", "-Wl,-rpath," + os.path.dirname(capi.LIB_PATH),
+                           "-Wl,-rpath,$ORIGIN/../../../robosoccer_motion_planning_b200/lib"])
+    return exe

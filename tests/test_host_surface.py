@@ -44,3 +44,26 @@ def test_trajectory_service_matches_checkers(gpu_required):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "0 check failure(s)" in r.stdout
+
+
+def test_custom_benchmark_builds_and_fails_loudly_without_gpu():
+    exe = native_build.build_custom_benchmark()
+    from robosoccer_motion_planning_b200 import capi
+    if capi.lib().krrt_device_count() > 0:
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe, "1"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_custom_benchmark_runs(gpu_required):
+    """The reference's `rrtstar_custom_benchmark` (README.md:39-42) over the component surface: 4 sampling settings x 7
+    node sizes, min / mean / max of time and cost; with direct sampling p >= 0.1 and 200 nodes most trials find the goal."""
+    exe = native_build.build_custom_benchmark()
+    r = subprocess.run([exe, "8"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    rows = [ln.split() for ln in r.stdout.splitlines() if ln.startswith("  ")]
+    assert len(rows) == 28
+    last = [w for w in rows if w[0] == "0.50" and w[1] == "200"][0]
+    assert int(last[5].split("/")[0]) >= 6 and float(last[7]) > 0.0
+    assert float(last[8]) > float(last[6])                     # trials differ (one sample stream per trial)
