@@ -342,7 +342,47 @@ def run_ours(args, rank, world, local_rank):
         be_ms += Gb.timer_end()
     barrier()
     be_ms = max_over_ranks(be_ms)
-    bst = Gb.batch_stats()
+    bst = Gb.batch_stats()          # counters of the last C4 launch (one rank's shard)
+    # ---- config 4 (C5): ONE Monte-Carlo sweep of 65536 queries sharded over the ranks (strong scaling: the sweep is fixed,
+    # the shard shrinks with N) + NCCL all-gather of all 65536 result records.  Scenes: the 4096 C4 scenes, each planned
+    # with 16 different Philox streams (global query id = stream of the query)
+    SWEEP_Q = 65536
+    slo, shi = sweep.shard_bounds(SWEEP_Q, rank, world)
+    base_s, base_g, base_o = scenes.batch_queries(BATCH_Q, 9, seed=0)
+    sel = np.arange(slo, shi) % BATCH_Q
+    d_ss = torch.from_numpy(np.ascontiguousarray(base_s[sel])).to(dev)
+    d_sg = torch.from_numpy(np.ascontiguousarray(base_g[sel])).to(dev)
+    d_so = torch.from_numpy(np.ascontiguousarray(base_o[sel])).to(dev)
+    spad = sweep.max_shard(SWEEP_Q, world)
+    d_sout = torch.zeros(spad * item, dtype=torch.uint8, device=dev)
+    d_sall = torch.zeros(world * spad * item, dtype=torch.uint8, device=dev)
+
+    def sweep_step():
+        Gb.plan_batch_device(d_ss.data_ptr(), d_sg.data_ptr(), d_so.data_ptr(), shi - slo, 9, 1, BATCH_ITERS, slo,
+                             d_sout.data_ptr(), tstream.cuda_stream)
+        if world > 1:
+            dist.all_gather_into_tensor(d_sall, d_sout)
+
+    torch.cuda.synchronize()
+    with torch.cuda.stream(tstream):
+        sweep_step()
+    barrier()
+    s_ms = 0.0
+    for _ in range(3):
+        flush_l2()
+        with torch.cuda.stream(tstream):
+            e0.record(tstream)
+            sweep_step()
+            e1.record(tstream)
+        e1.synchronize()
+        s_ms += e0.elapsed_time(e1)
+    barrier()
+    s_ms = max_over_ranks(s_ms)
+    sweep_line = {"workload": f"C5: one sweep of {SWEEP_Q} queries x {BATCH_ITERS} iterations sharded over {world} GPU(s) "
+                              "(strong scaling), results all-gathered" + (" over NCCL" if world > 1 else " (1 GPU: no gather)"),
+                  "queries_per_sec": SWEEP_Q * 3 / (s_ms * 1e-3), "ms_per_sweep": s_ms / 3,
+                  "gather_bytes": int(SWEEP_Q * item) if world > 1 else 0,
+                  "solved_frac": float((d_sout.cpu().numpy()[: (shi - slo) * item].view(capi.RESULT_DTYPE)["solved"] != 0).mean())}
     b_flop = 134.0 * bst["steer_calls"] + 1180.0 * bst["collide_calls"]      # SURVEY 8(d) accounting, one rank's shard
     f64_peak, f64_src = fp64_peak()
     b_tflops = b_flop * bsteps / (b_ms * 1e-3) / 1e12
@@ -376,6 +416,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks,
         "roofline": roofline,
         "batched": batched,
+        "sweep_c5": sweep_line,
         "tree_nodes": int(res["n_nodes"]), "solved": bool(res["solved"]), "cost": float(res["cost"]),
         "rounds": wave,
     }
