@@ -61,6 +61,8 @@ struct krrt_ctx {
   double* d_rho2_batch = nullptr;
   int* d_redo = nullptr;      // k_plan_batch2: [0] work counter of the redo pass, [1] redo count, [2..] redo list
   size_t redo_cap = 0;
+  Ctl* h_ctl = nullptr;       // pinned host copy of the control block ...
+  bool ctl_valid = false;     // ... current until the next call that changes the tree (krrt_set_start, krrt_grow)
   int batch_v1 = 0;           // KRRT_BATCH_V1=1 in the environment: the shared-memory-list kernel only (A-B timing)
   int rho2_batch_cap = -1;
   int* d_counter = nullptr;
@@ -167,6 +169,7 @@ void krrt_destroy(krrt_ctx* ctx) {
   if (ctx->d_user) cudaFree(ctx->d_user);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
   if (ctx->d_redo) cudaFree(ctx->d_redo);
+  if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->tm0) cudaEventDestroy(ctx->tm0);
   if (ctx->tm1) cudaEventDestroy(ctx->tm1);
@@ -386,6 +389,7 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   if (!ctx || !x0) return KRRT_ERR_INVALID;
   CK(cudaSetDevice(ctx->cfg.device));
   State4 s = {x0[0], x0[1], x0[2], x0[3]};
+  ctx->ctl_valid = false;
   k_set_start<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, ctx->T, s);
   ctx->launches++;
   CK(cudaGetLastError());
@@ -424,8 +428,15 @@ __global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_
 }
 
 static int fetch_ctl(krrt_ctx* ctx, Ctl* h) {
-  CK(cudaMemcpyAsync(h, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  // One read-back serves every getter until the tree changes again: the node-style caller asks for the tree size and
+  // the last sample after every single grow(xg) (robosoccer_motion_planning_node.cpp:175-179).
+  if (!ctx->ctl_valid) {
+    if (!ctx->h_ctl) CK(cudaHostAlloc((void**)&ctx->h_ctl, sizeof(Ctl), cudaHostAllocDefault));
+    CK(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->ctl_valid = true;
+  }
+  *h = *ctx->h_ctl;
   ctx->n_upper = h->n;
   return KRRT_OK;
 }
@@ -467,22 +478,29 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
     }
+    ctx->ctl_valid = false;
     k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);
     void* args[] = {(void*)&ctx->d_ctl, (void*)&ctx->P, (void*)&ctx->T, (void*)&ctx->Bt, (void*)&ctx->W, (void*)&gcfg};
-    CK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(ctx->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
-    ctx->launches += 2;
+    // A call of a few expansions that leaves the tree below the size where sub-rounds start (the node's own pattern:
+    // one grow(xg) per iteration on 75-200-node trees, config/config.yaml:3) is committed in order by one warp whatever
+    // the grid: it gets ONE CTA and a plain launch — no co-residency check, no grid-wide barriers (85 -> 58 us per call).
+    // Longer calls keep the full grid: their windows of 32 samples are scanned and steered by all SMs.
+    const bool small = n_iter <= 4 && ctx->n_upper + n_iter < ctx->wave_min_n && !std::getenv("KRRT_NO_SMALL");
+    if (small) {
+      k_grow<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, gcfg);
+    } else {
+      CK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(ctx->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
+    }
+    // the goal lookup and the end-of-call event follow at once: ONE read-back per launch (when the kernel came back early
+    // to have its conflict marks cleared, the lookup and the event are simply repeated after the next launch)
+    k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
+    CK(cudaEventRecord(ctx->ev1, st));
+    ctx->launches += 3;
+    CK(cudaGetLastError());
     int rc = fetch_ctl(ctx, &h);
     if (rc != KRRT_OK) return rc;
     if (h.full || h.error || h.iter >= h.iter_target) break;
     REQUIRE(h.round >= (1u << 23) - 2, KRRT_ERR_CUDA, "k_grow returned before its target");
-  }
-  k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
-  ctx->launches++;
-  CK(cudaEventRecord(ctx->ev1, st));
-  CK(cudaGetLastError());
-  {
-    int rc = fetch_ctl(ctx, &h);
-    if (rc != KRRT_OK) return rc;
   }
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));

@@ -453,3 +453,21 @@ def test_grid_index_survives_a_larger_radius(gpu_required, monkeypatch):
     assert G.scan_stats()["index_rebuilds"] > r0
     assert G.grow(scenes.GOAL, 1500) == O.grow(scenes.GOAL, 1500)
     assert_same_tree(G, O)
+
+
+@pytest.mark.parametrize("no_small", [False, True])
+def test_single_expansion_calls_cross_the_small_tree_launch(gpu_required, monkeypatch, no_small):
+    """The node's call pattern: one krrt_grow per iteration (…node.cpp:176-185).  While the tree stays below the size where
+    sub-rounds start, a call is ONE CTA in a plain launch; past it, the cooperative grid.  Same tree either way, and the
+    getters between two calls are served from one read-back."""
+    if no_small:
+        monkeypatch.setenv("KRRT_NO_SMALL", "1")
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, capacity=2048)
+    for k in range(330):
+        step = 1 if k % 7 else 3
+        assert G.grow(scenes.GOAL, step) == O.grow(scenes.GOAL, step)
+        if k % 50 == 0:
+            assert G.size == O.size and np.array_equal(G.last_sample(), O.last_sample())
+            assert G.iteration == O.iteration
+    assert G.size > 256
+    assert_same_tree(G, O)
