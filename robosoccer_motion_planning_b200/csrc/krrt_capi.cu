@@ -44,7 +44,8 @@ struct krrt_ctx {
   Wave W{};
   Params P{};
   int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the in-order commit (debugging / A-B timing)
-  int wave_min_n = 256;       // trees smaller than this commit in order (conflicts everywhere, nothing to gain)
+  int wave_min_n = 64;        // trees smaller than this commit in order (conflicts everywhere; profiles/r1_param_sweep.txt)
+  int small_max_n = 256;      // few-expansion calls on trees below this: one CTA, plain launch, in-order commit
   int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
   GridBar* d_bar = nullptr;    // its two grid barriers
   GridIndex gi{};              // spatial index of its neighbour scan
@@ -320,7 +321,7 @@ int krrt_create(const krrt_config* c, krrt_ctx** out) {
   *out = nullptr;
   krrt_ctx* ctx = new krrt_ctx();
   ctx->cfg = *c;
-  if (ctx->cfg.batch == 0) ctx->cfg.batch = 256;
+  if (ctx->cfg.batch == 0) ctx->cfg.batch = 512;   // profiles/r1_param_sweep.txt
   if (const char* e = std::getenv("KRRT_WINDOW")) ctx->cfg.batch = std::max(1, std::min(GROW_WMAX, std::atoi(e)));
   if (ctx->cfg.near_cap == 0) ctx->cfg.near_cap = 1024;
   int rc = create_impl(ctx);
@@ -485,9 +486,11 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     // one grow(xg) per iteration on 75-200-node trees, config/config.yaml:3) is committed in order by one warp whatever
     // the grid: it gets ONE CTA and a plain launch — no co-residency check, no grid-wide barriers (85 -> 58 us per call).
     // Longer calls keep the full grid: their windows of 32 samples are scanned and steered by all SMs.
-    const bool small = n_iter <= 4 && ctx->n_upper + n_iter < ctx->wave_min_n && !std::getenv("KRRT_NO_SMALL");
+    const bool small = n_iter <= 4 && ctx->n_upper + n_iter < ctx->small_max_n && !std::getenv("KRRT_NO_SMALL");
     if (small) {
-      k_grow<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, gcfg);
+      GrowCfg one = gcfg;
+      one.wave_enabled = 0;  // a single CTA cannot run sub-rounds; in order is what a sequential planner does anyway
+      k_grow<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, one);
     } else {
       CK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(ctx->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
     }
