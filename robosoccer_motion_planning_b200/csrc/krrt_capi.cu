@@ -468,6 +468,11 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   gcfg.user_samples = samples ? ctx->d_user : nullptr;
   gcfg.bar = ctx->d_bar;
   gcfg.gi = ctx->gi;
+  {  // sub-round sizing (profiles/r1_param_sweep.txt); the environment overrides are for sweeps
+    auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
+    gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
+    gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
+  }
   const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(ctx->Bt.near_cap));
   Ctl h;
   // ONE persistent kernel does the whole call; it only comes back early when the 23-bit epoch of the conflict marks

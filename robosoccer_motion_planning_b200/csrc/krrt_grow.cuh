@@ -60,6 +60,8 @@ struct GrowCfg {
   const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
   GridBar* bar;                // [0] all CTAs, [1] the CTAs that take part in a window's sub-rounds (zero at launch)
   GridIndex gi;                // spatial index of the neighbour scan
+  int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
+  int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
 };
 
 __device__ __forceinline__ void grid_barrier(GridBar* bar, BarState& st, int n, bool relaxed) {
@@ -598,7 +600,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     for (int j = t; j < P.m; j += GROW_THREADS) sm.obs[j] = P.obs[j];
     // the CTAs that take part in this window's sub-rounds: enough for twice the prefixes seen lately + the last CTA;
     // the others go straight to the window's end and doze there
-    const int Pn = min(G - 1, max(48, (3 * ema_win) / 16 + 16));
+    const int Pn = min(G - 1, max(cfg.pn_min, (cfg.pn_mul * ema_win) / 16 + cfg.pn_add));
     const bool takes_part = cta < Pn || last;
     // the set changes from window to window: pick the barrier's counters up where they stood before the window's barrier
     bs_sub.arrived = sub_base;
@@ -611,7 +613,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       const int full_sub = __ldcg(&ctl->full), error_sub = __ldcg(&ctl->error);  // (no short-circuit: one round trip)
       if ((full_sub | error_sub) != 0 || round >= (1u << 23) - 2) break;
       const int slot = (int)(round & 1u);
-      const int nb = min(min(Pn, Wn - F0), max(16, (2 * ema_sub) / 16 + 8));
+      const int nb = min(min(Pn, Wn - F0), max(cfg.nb_min, (cfg.nb_mul * ema_sub) / 16 + cfg.nb_add));
       const bool active = cta < nb;
       const int b = F0 + cta;
       const size_t base = (size_t)b * cap;
