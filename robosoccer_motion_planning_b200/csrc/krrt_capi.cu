@@ -470,6 +470,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   gcfg.gi = ctx->gi;
   {  // sub-round sizing (profiles/r1_param_sweep.txt); the environment overrides are for sweeps
     auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
+    gcfg.pend_resolve = envi("KRRT_PEND", 1);
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
   }

@@ -60,6 +60,7 @@ struct GrowCfg {
   const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
   GridBar* bar;                // [0] all CTAs, [1] the CTAs that take part in a window's sub-rounds (zero at launch)
   GridIndex gi;                // spatial index of the neighbour scan
+  int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
 };
@@ -623,6 +624,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       long long collide_calls = 0;
       double ctc_new = 0.0, tim_new = 0.0, rho2n = 0.0;
       int my_node = -1, my_q = -1;
+      int pend_e = -1;  // this thread's candidate is an earlier sample of the SAME sub-round (window index): see validate
       double my_d = 0.0, my_cf = 0.0, my_cb = 0.0, my_ctc = 0.0;
       bool my_near = false;
       State4 s = {0, 0, 0, 0};
@@ -683,6 +685,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             const int mapped = __ldcg(&Bt.map[e]);            // (all three loads leave together)
             const bool e_ins = sample_insertable(Bt, P, e);
             if (e < F0) my_node = mapped;  // committed in an earlier sub-round (-1: it did not insert)
+            else if (cfg.pend_resolve) pend_e = e_ins ? e : -1;  // decided in this sub-round: settled at validation
             else pend = e_ins;             // may land inside the radius: wait for the next sub-round
           } else {
             my_node = ref;
@@ -918,6 +921,23 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             conf = (my_d <= rho2n) != (my_d <= rt);
           }
           if (my_near) conf |= mark_sample(__ldcg(&W.wmin[my_node]), round) < cta;
+          // A candidate that is an earlier sample of this very sub-round: its decision is on record now.  If it inserts
+          // inside this sample's radius it joins the near set (counters), and the decision taken without it stands as
+          // long as the newcomer would be neither the parent (it is tried before the chosen one only if strictly cheaper:
+          // it has the highest index) nor a rewire candidate, and is not a duplicate.  Nobody changes its cost in between:
+          // a later sample that rewires it fails here, one that rewires an ancestor fails on the read marks of its parent.
+          bool joins = false;
+          if (pend_e >= 0) {
+            const WaveRec* re = &W.rec[pend_e];
+            const int oe = __ldcg(&re->outcome);
+            const double ce = __ldcg(&re->ctc_new);
+            if (oe == OUT_INSERT && my_d <= P.rho2[n_true]) {
+              joins = true;
+              conf |= outcome == OUT_NOFREE || my_d == 0.0 || ce + my_cf < ctc_new || ctc_new + my_cb < ce;
+            }
+          }
+          const int n_join = __syncthreads_count(joins);
+          if (n_join > 0 && t == 0) W.rec[b].K = K + n_join;
           if (outcome == OUT_INSERT) {
             if (t < nrew) conf |= mark_sample(__ldcg(&W.amin[sm.u.d.rewn[t]]), round) < cta;
             for (int q = t; q < nwl; q += GROW_THREADS) conf |= mark_sample(__ldcg(&W.amin[sm.u.d.wl[q]]), round) < cta;
