@@ -1,4 +1,5 @@
-/* ingest_oracle.c — see ingest_oracle.h (test infrastructure, CPU restatement of robotsubscriber.cpp:29-77). */
+/* ingest_oracle.c — see ingest_oracle.h (TEST INFRASTRUCTURE ONLY; PARITY UNPINNED; CPU restatement of
+ * robotsubscriber.cpp:29-77). */
 #include "ingest_oracle.h"
 
 #include <string.h>

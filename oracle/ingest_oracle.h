@@ -3,8 +3,9 @@
  * Follows RobotSubscriber::callback (robotsubscriber.cpp:44-77), ::rival_callback (robotsubscriber.cpp:29-42) and
  * ::getObstacles (robotsubscriber.h:50-55) of /root/reference/src/robosoccer_motion_planning; field types from
  * gazebo_visual/src/nubot_common/msgs/RobotInfo.msg:2,9-12 (int32 AgentID, float32 Point2d pos / vtrans, float32 heading).
- * The reference source for this piece IS present but needs ROS to compile, so the restatement is pinned by hand-computed
- * known answers in tests/test_ingest.py, not by a compiled reference. */
+ * PARITY UNPINNED: the reference source for this piece IS present (and is restated line by line here) but needs ROS to
+ * compile and no reference test or fixture covers it; the restatement is checked against hand-computed known answers
+ * in tests/test_ingest.py only. */
 #ifndef INGEST_ORACLE_H
 #define INGEST_ORACLE_H
 #include <stdint.h>
