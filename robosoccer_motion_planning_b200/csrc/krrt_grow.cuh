@@ -724,7 +724,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.u.d.tim[t] = my_tim;
           sm.u.d.tf[t] = my_tf;
           sm.u.d.tb[t] = my_tb;
-          atomicMax(&W.amin[my_node], key);  // read mark
         }
         sm.u.d.flag[t] = my_near ? 1 : 0;
         __syncthreads();
@@ -801,7 +800,14 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           break;
         }
         tim_new = sm.u.d.tim[park] + sm.u.d.tf[park];
-        if (t == park) sm.par_cf = my_cf;  // (read by thread 0 in apply, barriers in between)
+        if (t == park) {
+          sm.par_cf = my_cf;  // (read by thread 0 in apply, barriers in between)
+          // parent mark: this sample's cost is DERIVED from the parent's.  A later sample of the sub-round that changes the
+          // parent's cost (rewires it, or an ancestor of it) would have to propagate into this sample's new node, which
+          // its write list cannot contain.  Plain reads of the other near nodes leave no such trace: a later write to
+          // them is a write-after-read, harmless because this decision is already taken (sequential order).
+          atomicMax(&W.amin[par], key);
+        }
         // a sequential planner checks candidates in (cost, index) order until the first free one; rewire candidates:
         // near nodes that would get cheaper through the new node
         bool tried = false, cand = false;
@@ -860,7 +866,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           for (int q = level0 + t; q < level1; q += GROW_THREADS) {
             const int d = sm.u.d.wl[q];
             atomicMax(&W.wmin[d], key);
-            atomicMax(&W.amin[d], key);
             for (unsigned hsl = near_hash(d);; hsl = (hsl + 1) & (GROW_HASH - 1)) {
               const int hv = sm.u.d.hash[hsl];
               if (hv == d) sm.intra = 1;
@@ -907,6 +912,12 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 #endif
 
       // -------------------------------------------------------------- validate
+#ifdef KRRT_WHY  // diagnostic build: what made the sample that ended the prefix fail (counted after F is known)
+      int why_bits = 0;
+#define WHY(cond, bit) do { if (cond) why_bits |= (bit); } while (0)
+#else
+#define WHY(cond, bit)
+#endif
       int n_true = n_b;
       if (active) {
         bool fail = outcome == OUT_COMPLEX || outcome == OUT_CONFLICT || outcome == OUT_NEAREST;
@@ -920,7 +931,9 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             const double rt = P.rho2[n_true];
             conf = (my_d <= rho2n) != (my_d <= rt);
           }
+          WHY(conf, 1);
           if (my_near) conf |= mark_sample(__ldcg(&W.wmin[my_node]), round) < cta;
+          WHY(my_near && mark_sample(__ldcg(&W.wmin[my_node]), round) < cta, 2);
           // A candidate that is an earlier sample of this very sub-round: its decision is on record now.  If it inserts
           // inside this sample's radius it joins the near set (counters), and the decision taken without it stands as
           // long as the newcomer would be neither the parent (it is tried before the chosen one only if strictly cheaper:
@@ -934,13 +947,25 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             if (oe == OUT_INSERT && my_d <= P.rho2[n_true]) {
               joins = true;
               conf |= outcome == OUT_NOFREE || my_d == 0.0 || ce + my_cf < ctc_new || ctc_new + my_cb < ce;
+              WHY(outcome == OUT_NOFREE, 4); WHY(my_d == 0.0, 8); WHY(ce + my_cf < ctc_new, 16); WHY(ctc_new + my_cb < ce, 32);
             }
           }
           const int n_join = __syncthreads_count(joins);
           if (n_join > 0 && t == 0) W.rec[b].K = K + n_join;
           if (outcome == OUT_INSERT) {
-            if (t < nrew) conf |= mark_sample(__ldcg(&W.amin[sm.u.d.rewn[t]]), round) < cta;
-            for (int q = t; q < nwl; q += GROW_THREADS) conf |= mark_sample(__ldcg(&W.amin[sm.u.d.wl[q]]), round) < cta;
+            // nodes this sample writes: none may have been written, or chosen as parent, by an earlier sample
+            if (t < nrew) {
+              const int j = sm.u.d.rewn[t];
+              const bool c = min(mark_sample(__ldcg(&W.wmin[j]), round), mark_sample(__ldcg(&W.amin[j]), round)) < cta;
+              conf |= c;
+              WHY(c, 64);
+            }
+            for (int q = t; q < nwl; q += GROW_THREADS) {
+              const int j = sm.u.d.wl[q];
+              const bool c = min(mark_sample(__ldcg(&W.wmin[j]), round), mark_sample(__ldcg(&W.amin[j]), round)) < cta;
+              conf |= c;
+              WHY(c, 128);
+            }
           }
           fail = __syncthreads_or(conf) != 0;
         }
@@ -958,6 +983,15 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 
       // -------------------------------------------------------------- apply
       const int F = min(nb, __ldcg(&ctl->wave_Fs[slot]));
+#ifdef KRRT_WHY
+      if (active && cta == F) {
+        if (why_bits) atomicOr(&sm.flags, why_bits << 8);  // (sm.flags is re-initialised by the next decide)
+        __syncthreads();
+        const int all = sm.flags >> 8;
+        if (t < 8 && ((all >> t) & 1)) atomicAdd((unsigned long long*)&ctl->dbg_clk[t], 1ull);
+        if (t == 8) atomicAdd((unsigned long long*)&ctl->dbg_clk[8 + min(outcome, 6)], 1ull);  // (9..14: by outcome)
+      }
+#endif
       // the first sample has an empty near set: every CTA of the sub-round scans its share of the tree for the nearest
       // node (lowest index among equal distances), the last CTA folds the partials and commits the sample in order
       const bool need_nn = F == 0 && __ldcg(&W.rec[F0].outcome) == OUT_NEAREST;

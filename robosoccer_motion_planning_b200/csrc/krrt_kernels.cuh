@@ -109,7 +109,7 @@ struct WaveRec {
 struct Wave {
   WaveRec* rec;     // [B]
   unsigned* wmin;   // [capacity] mark: lowest sample of this sub-round that WRITES the node's cost/time
-  unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that reads or writes it
+  unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that chose the node as PARENT (derived its cost from it)
   int* lock;        // [capacity] child-list lock of a parent
   double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...
   int* nn_idx;      // ... (squared distance, node index)
