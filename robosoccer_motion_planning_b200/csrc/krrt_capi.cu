@@ -206,7 +206,7 @@ static int create_impl(krrt_ctx* ctx) {
   const size_t cap = (size_t)c.capacity;
   {
     const size_t bcn = (size_t)c.batch * c.near_cap;
-    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + (GRID_CELLS_MAX + 1) * 4 +
+    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + cap * 4 + (GRID_CELLS_MAX + 1) * 4 +
                   (cap + 1) * 8 + bcn * (4 + 8 * 5) +
                   (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
 #ifdef KRRT_DEBUG_CLK
@@ -259,6 +259,7 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &W.rec, (size_t)B.B));
   CK(dev_alloc(ctx, &W.wmin, cap));
   CK(dev_alloc(ctx, &W.amin, cap));
+  CK(dev_alloc(ctx, &W.rmin, cap));
   CK(dev_alloc(ctx, &W.lock, cap));
   CK(dev_alloc(ctx, &ctx->gi.pos, cap));
   CK(dev_alloc(ctx, &ctx->gi.vel, cap));
@@ -277,6 +278,7 @@ static int create_impl(krrt_ctx* ctx) {
 #endif
   CK(cudaMemsetAsync(W.wmin, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, ctx->stream));
+  CK(cudaMemsetAsync(W.rmin, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
   CK(dev_alloc(ctx, &ctx->d_bar, (size_t)2));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
@@ -471,6 +473,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   {  // sub-round sizing (profiles/r1_param_sweep.txt); the environment overrides are for sweeps
     auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
     gcfg.pend_resolve = envi("KRRT_PEND", 1);
+    gcfg.raw_forward = envi("KRRT_RAW_FORWARD", 1);
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
   }
@@ -484,6 +487,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       const size_t cap = (size_t)ctx->cfg.capacity;
       CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
+      CK(cudaMemsetAsync(ctx->W.rmin, 0, sizeof(unsigned) * cap, st));
     }
     ctx->ctl_valid = false;
     k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);

@@ -60,6 +60,7 @@ struct GrowCfg {
   const double* user_samples;  // device copy of the caller's explicit samples, or nullptr
   GridBar* bar;                // [0] all CTAs, [1] the CTAs that take part in a window's sub-rounds (zero at launch)
   GridIndex gi;                // spatial index of the neighbour scan
+  int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
@@ -624,6 +625,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       long long collide_calls = 0;
       double ctc_new = 0.0, tim_new = 0.0, rho2n = 0.0;
       int my_node = -1, my_q = -1;
+      bool my_tried = false, my_cand = false;  // this thread's near node was tried as parent / is a rewire candidate
       int pend_e = -1;  // this thread's candidate is an earlier sample of the SAME sub-round (window index): see validate
       double my_d = 0.0, my_cf = 0.0, my_cb = 0.0, my_ctc = 0.0;
       bool my_near = false;
@@ -820,6 +822,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           const unsigned triedb = __ballot_sync(FULL, tried);
           if ((t & 31) == 0 && triedb) atomicAdd(&sm.tries, __popc(triedb));
         }
+        my_tried = tried;
+        my_cand = cand;
         if (cand) sm.u.d.cand[atomicAdd(&sm.ncand, 1)] = t;
         __syncthreads();
         const int ncand = sm.ncand;
@@ -841,6 +845,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           my_q = atomicAdd(&sm.nrew, 1);
           sm.u.d.rewn[my_q] = my_node;
           atomicMax(&W.wmin[my_node], key);
+          atomicMax(&W.rmin[my_node], key);
           push_children(T, sm, my_head, -(my_q + 1));
         }
         __syncthreads();
@@ -932,8 +937,28 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             conf = (my_d <= rho2n) != (my_d <= rt);
           }
           WHY(conf, 1);
-          if (my_near) conf |= mark_sample(__ldcg(&W.wmin[my_node]), round) < cta;
-          WHY(my_near && mark_sample(__ldcg(&W.wmin[my_node]), round) < cta, 2);
+          // A near node whose cost an earlier sample of the sub-round changes.  If that sample REWIRED it, the new cost is
+          // that sample's cost + c*(sample -> node), recomputed here with the very call the writer made; it only went
+          // down, so this decision stands unless the node is the parent, was tried as parent, is a rewire candidate, or
+          // would now be tried before the chosen parent.  A cost changed by propagation ends the prefix as before.
+          if (my_near) {
+            const int w = mark_sample(__ldcg(&W.wmin[my_node]), round);
+            if (w < cta) {
+              bool c = true;
+              if (cfg.raw_forward && outcome == OUT_INSERT && mark_sample(__ldcg(&W.rmin[my_node]), round) == w &&
+                  t != park && !my_tried && !my_cand) {
+                const WaveRec* re = &W.rec[F0 + w];
+                const double ce = __ldcg(&re->ctc_new);
+                double tau_e, c_e;
+                steer(Bt.samples[F0 + w], sm.u.d.st[t], P.r, tau_e, c_e);
+                const double cn = (ce + c_e) + my_cf;
+                c = cn < ctc_new || (cn == ctc_new && my_node < par);
+                WHY(!c, 256);
+              }
+              conf |= c;
+              WHY(c, 2);
+            }
+          }
           // A candidate that is an earlier sample of this very sub-round: its decision is on record now.  If it inserts
           // inside this sample's radius it joins the near set (counters), and the decision taken without it stands as
           // long as the newcomer would be neither the parent (it is tried before the chosen one only if strictly cheaper:
@@ -989,6 +1014,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         __syncthreads();
         const int all = sm.flags >> 8;
         if (t < 8 && ((all >> t) & 1)) atomicAdd((unsigned long long*)&ctl->dbg_clk[t], 1ull);
+        if (t == 9 && ((all >> 8) & 1)) atomicAdd((unsigned long long*)&ctl->dbg_clk[15], 1ull);
         if (t == 8) atomicAdd((unsigned long long*)&ctl->dbg_clk[8 + min(outcome, 6)], 1ull);  // (9..14: by outcome)
       }
 #endif
