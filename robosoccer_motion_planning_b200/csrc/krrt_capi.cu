@@ -206,7 +206,7 @@ static int create_impl(krrt_ctx* ctx) {
   const size_t cap = (size_t)c.capacity;
   {
     const size_t bcn = (size_t)c.batch * c.near_cap;
-    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + cap * 4 + (GRID_CELLS_MAX + 1) * 4 +
+    size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + cap * 8 + (GRID_CELLS_MAX + 1) * 4 +
                   (cap + 1) * 8 + bcn * (4 + 8 * 5) +
                   (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
 #ifdef KRRT_DEBUG_CLK
@@ -278,7 +278,7 @@ static int create_impl(krrt_ctx* ctx) {
 #endif
   CK(cudaMemsetAsync(W.wmin, 0, sizeof(unsigned) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, ctx->stream));
-  CK(cudaMemsetAsync(W.rmin, 0, sizeof(unsigned) * cap, ctx->stream));
+  CK(cudaMemsetAsync(W.rmin, 0, sizeof(unsigned long long) * cap, ctx->stream));
   CK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, ctx->stream));
   CK(dev_alloc(ctx, &ctx->d_bar, (size_t)2));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
@@ -487,7 +487,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       const size_t cap = (size_t)ctx->cfg.capacity;
       CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
-      CK(cudaMemsetAsync(ctx->W.rmin, 0, sizeof(unsigned) * cap, st));
+      CK(cudaMemsetAsync(ctx->W.rmin, 0, sizeof(unsigned long long) * cap, st));
     }
     ctx->ctl_valid = false;
     k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);

@@ -845,7 +845,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           my_q = atomicAdd(&sm.nrew, 1);
           sm.u.d.rewn[my_q] = my_node;
           atomicMax(&W.wmin[my_node], key);
-          atomicMax(&W.rmin[my_node], key);
+          atomicMax(&W.rmin[my_node], ((unsigned long long)key << 32) | (unsigned)t);
           push_children(T, sm, my_head, -(my_q + 1));
         }
         __syncthreads();
@@ -938,22 +938,22 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           }
           WHY(conf, 1);
           // A near node whose cost an earlier sample of the sub-round changes.  If that sample REWIRED it, the new cost is
-          // that sample's cost + c*(sample -> node), recomputed here with the very call the writer made; it only went
-          // down, so this decision stands unless the node is the parent, was tried as parent, is a rewire candidate, or
+          // that sample's cost + c*(sample -> node), both on record (the rewire mark carries the node's slot in the writer's
+          // candidate list); it only went down, so this decision stands unless the node is the parent, was tried as parent, is a rewire candidate, or
           // would now be tried before the chosen parent.  A cost changed by propagation ends the prefix as before.
           if (my_near) {
-            const int w = mark_sample(__ldcg(&W.wmin[my_node]), round);
+            const unsigned mw = __ldcg(&W.wmin[my_node]);
+            const unsigned long long mr = __ldcg(&W.rmin[my_node]);  // (one round trip for both)
+            const int w = mark_sample(mw, round);
             if (w < cta) {
               bool c = true;
-              if (cfg.raw_forward && outcome == OUT_INSERT && mark_sample(__ldcg(&W.rmin[my_node]), round) == w &&
+              if (cfg.raw_forward && outcome == OUT_INSERT && mark_sample((unsigned)(mr >> 32), round) == w &&
                   t != park && !my_tried && !my_cand) {
-                const WaveRec* re = &W.rec[F0 + w];
-                const double ce = __ldcg(&re->ctc_new);
-                double tau_e, c_e;
-                steer(Bt.samples[F0 + w], sm.u.d.st[t], P.r, tau_e, c_e);
+                // new cost of the node = the rewiring sample's cost + its c*(sample -> node), both on record
+                const double ce = __ldcg(&W.rec[F0 + w].ctc_new);
+                const double c_e = __ldcg(&Bt.cb[(size_t)(F0 + w) * cap + (unsigned)mr]);
                 const double cn = (ce + c_e) + my_cf;
                 c = cn < ctc_new || (cn == ctc_new && my_node < par);
-                WHY(!c, 256);
               }
               conf |= c;
               WHY(c, 2);

@@ -110,7 +110,8 @@ struct Wave {
   WaveRec* rec;     // [B]
   unsigned* wmin;   // [capacity] mark: lowest sample of this sub-round that WRITES the node's cost/time
   unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that chose the node as PARENT (derived its cost from it)
-  unsigned* rmin;   // [capacity] mark: lowest sample of this sub-round that REWIRES the node (its new cost can be recomputed)
+  unsigned long long* rmin;  // [capacity] (mark << 32 | slot): lowest sample of this sub-round that REWIRES the node, and the
+                             // node's slot in that sample's candidate list (where c*(sample -> node) is)
   int* lock;        // [capacity] child-list lock of a parent
   double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...
   int* nn_idx;      // ... (squared distance, node index)

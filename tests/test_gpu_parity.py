@@ -471,3 +471,23 @@ def test_single_expansion_calls_cross_the_small_tree_launch(gpu_required, monkey
             assert G.iteration == O.iteration
     assert G.size > 256
     assert_same_tree(G, O)
+
+
+@pytest.mark.parametrize("pend,raw", [("0", "0"), ("1", "0"), ("0", "1")])
+def test_prefix_relaxations_can_be_switched_off(gpu_required, monkeypatch, pend, raw):
+    """KRRT_PEND / KRRT_RAW_FORWARD (read at every krrt_grow call) switch off the two ways a sub-round's validated prefix is
+    extended (same-sub-round neighbours settled at validation; rewired near nodes re-checked with their new cost).  The
+    tree must not depend on them — they only change how many expansions a sub-round commits."""
+    monkeypatch.setenv("KRRT_PEND", pend)
+    monkeypatch.setenv("KRRT_RAW_FORWARD", raw)
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1)
+    assert G.grow(scenes.GOAL, 8000) == O.grow(scenes.GOAL, 8000)
+    assert_same_tree(G, O)
+    off = G.wave_stats()["rounds_parallel"]
+    monkeypatch.setenv("KRRT_PEND", "1")
+    monkeypatch.setenv("KRRT_RAW_FORWARD", "1")
+    G2, _ = make_pair(gpu_required, dynamic=1, p_direct=0.1)
+    G2.grow(scenes.GOAL, 8000)
+    assert G2.wave_stats()["rounds_parallel"] < off
+    for a, b in zip(G.tree(), G2.tree()):
+        assert np.array_equal(a, b)
