@@ -742,10 +742,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           outcome = OUT_NEAREST;
           break;
         }
-        if (my_near) {  // membership table of the near set (the table was cleared before the barrier above)
-          unsigned hsl = near_hash(my_node);
-          while (atomicCAS(&sm.u.d.hash[hsl], -1, my_node) != -1) hsl = (hsl + 1) & (GROW_HASH - 1);
-        }
         DBG_STAMP(2);
         // forward edges of ALL near nodes at once: one thread per (edge, sample point)
         if (P.m > 0) {
@@ -824,7 +820,16 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
         my_tried = tried;
         my_cand = cand;
-        if (cand) sm.u.d.cand[atomicAdd(&sm.ncand, 1)] = t;
+        if (cand) {
+          sm.u.d.cand[atomicAdd(&sm.ncand, 1)] = t;
+          // membership table of the REWIRE CANDIDATES (cleared before the barrier above): a candidate below another rewired
+          // node would be tested against a cost that the first rewire has just lowered (rewires go in ascending index,
+          // each sees the costs the previous one left) — that sample takes the in-order path.  A near node that is no
+          // candidate at its old cost is none at a lower one, and the parent is chosen before any rewire: no need to
+          // look for those below the rewired nodes.
+          unsigned hsl = near_hash(my_node);
+          while (atomicCAS(&sm.u.d.hash[hsl], -1, my_node) != -1) hsl = (hsl + 1) & (GROW_HASH - 1);
+        }
         __syncthreads();
         const int ncand = sm.ncand;
         DBG_STAMP(5);
