@@ -193,6 +193,9 @@ int krrt_kernel_times(krrt_ctx* ctx, double ms[8], int64_t launches[8]);
  * ended the parallel prefixes: end of batch, in-batch neighbour, sample needing the sequential path, sample with
  * no collision-free parent, read/write conflict                                                             */
 int krrt_wave_stats(krrt_ctx* ctx, int64_t out[8]);
+/* of out[1] above: samples that needed the in-order path right behind a parallel prefix and were committed by the
+ * sequential warp inside the same sub-round (one extra grid barrier instead of a sub-round of their own)        */
+int krrt_tail_commits(krrt_ctx* ctx, int64_t* out);
 /* development builds (-DKRRT_DEBUG_CLK): SM-clock sums of the steps inside decide / apply of CTA 0; zeros otherwise */
 int krrt_debug_clocks(krrt_ctx* ctx, int64_t out[16]);
 /* device time of the last krrt_grow / krrt_plan_batch in ms (CUDA events on the ctx stream), and the share

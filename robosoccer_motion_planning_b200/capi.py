@@ -29,7 +29,7 @@ EXPORTS = (
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
-    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_debug_clocks",
+    "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_tail_commits", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
     "krrt_solve_inputs", "krrt_scan_stats",
 )
@@ -131,6 +131,7 @@ def lib():
     L.krrt_debug_clocks.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_kernel_times.argtypes = [P, D, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_wave_stats.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
+    L.krrt_tail_commits.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_launch_count.argtypes = [P]
     L.krrt_launch_count.restype = ctypes.c_int64
     L.krrt_set_profile.argtypes = [P, ctypes.c_int]
@@ -451,6 +452,11 @@ class Planner:
         return {"rounds_parallel": int(o[0]), "rounds_sequential": int(o[1]), "expansions_parallel": int(o[2]),
                 "prefix_ended_by": {"batch_end": int(o[3]), "in_batch_neighbour": int(o[4]), "sequential_sample": int(o[5]),
                                     "no_free_parent": int(o[6]), "rw_conflict": int(o[7])}}
+
+    def tail_commits(self):
+        o = ctypes.c_int64(0)
+        self._ck(lib().krrt_tail_commits(self.h, ctypes.byref(o)))
+        return int(o.value)
 
     def debug_clocks(self):
         o = np.zeros(16, dtype=np.int64)

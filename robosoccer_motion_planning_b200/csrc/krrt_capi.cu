@@ -474,6 +474,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
     gcfg.pend_resolve = envi("KRRT_PEND", 1);
     gcfg.raw_forward = envi("KRRT_RAW_FORWARD", 1);
+    gcfg.tail_seq = envi("KRRT_TAIL_SEQ", 1);
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
   }
@@ -523,7 +524,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     // phase clocks of the kernel's last CTA -> shares of the call's device time
     double tot = 0.0;
     for (int k = 0; k < 8; ++k) tot += (double)h.phase_clk[k];
-    const long long subs = h.rounds_wave + h.rounds_seq;
+    const long long subs = h.rounds_wave + h.rounds_seq - h.tail_commits;
     for (int k = 0; k < 8; ++k) {
       ctx->phase_ms[k] = tot > 0.0 ? ms * (double)h.phase_clk[k] / tot : 0.0;
       ctx->phase_n[k] = k < 2 ? h.windows : (k < 5 ? subs : 0);
@@ -632,6 +633,17 @@ int krrt_wave_stats(krrt_ctx* ctx, int64_t out[8]) {
   out[1] = h.rounds_seq;
   out[2] = h.wave_committed;
   for (int k = 0; k < 5; ++k) out[3 + k] = h.why[k];
+  return KRRT_OK;
+}
+
+int krrt_tail_commits(krrt_ctx* ctx, int64_t* out) {
+  if (!ctx || !out) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  *out = h.tail_commits;
   return KRRT_OK;
 }
 

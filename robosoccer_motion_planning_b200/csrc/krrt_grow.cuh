@@ -62,6 +62,7 @@ struct GrowCfg {
   GridIndex gi;                // spatial index of the neighbour scan
   int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
+  int tail_seq;                // a sample that needs the in-order path right behind the prefix is committed in the same sub-round
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
 };
@@ -1026,6 +1027,10 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       // the first sample has an empty near set: every CTA of the sub-round scans its share of the tree for the nearest
       // node (lowest index among equal distances), the last CTA folds the partials and commits the sample in order
       const bool need_nn = F == 0 && __ldcg(&W.rec[F0].outcome) == OUT_NEAREST;
+      // the sample that ended the prefix needs the in-order path anyway (it rewires a node below another node it
+      // rewires): the last CTA commits it right behind the prefix, one barrier later, instead of spending a whole
+      // sub-round on it
+      const bool tail_seq = cfg.tail_seq && F > 0 && F < nb && __ldcg(&W.rec[F0 + F].outcome) == OUT_COMPLEX;
       if (need_nn) {
         const State4 s0 = Bt.samples[F0];
         const int pidx = last ? Pn : cta;
@@ -1220,9 +1225,16 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             sm.fin[11] += 1;  // rounds_seq
           }
         }
+      }
+      if (tail_seq) grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);  // the prefix is in the tree, ctl is up to date
+      if (last && t < 32) {
+        if (tail_seq) {
+          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, -1, 0.0);
+          if (t == 0) sm.fin[18] += 1;  // tail commits
+        }
         __syncwarp();
-        if (F0 + max(F, 1) >= Wn) clear_window(Bt);
-        if (lane == 0) {
+        if (F0 + max(F, 1) + (tail_seq ? 1 : 0) >= Wn) clear_window(Bt);
+        if (t == 0) {
           ctl->wave_Fs[slot ^ 1] = 0x7fffffff;
           ctl->round = round + 1;
         }
@@ -1234,7 +1246,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
       DBG_STAMP(12);
       phase_done(4);
-      F0 += max(F, 1);
+      F0 += max(F, 1) + (tail_seq ? 1 : 0);
     }
     grid_barrier(cfg.bar, bs_all, G, !takes_part);  // window end
     phase_done(4);
@@ -1242,7 +1254,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
   if (last && t == 0) {
     for (int k = 0; k < 10; ++k) ctl->stats[k] += sm.fin[k];
     ctl->rounds_wave += sm.fin[10];
-    ctl->rounds_seq += sm.fin[11];
+    ctl->rounds_seq += sm.fin[11] + sm.fin[18];
+    ctl->tail_commits += sm.fin[18];
     ctl->wave_committed += sm.fin[12];
     for (int k = 0; k < 5; ++k) ctl->why[k] += sm.fin[13 + k];
   }

@@ -39,6 +39,7 @@ struct Ctl {  // device-resident control block of one single-tree context
   int wave_F;             // length of that prefix
   int ema16;              // 16 x running mean of the prefix length: sizes the next round's batch
   long long rounds_wave, rounds_seq, wave_committed;  // diagnostics since set_start
+  long long tail_commits;  // of rounds_seq: single samples committed in order right behind a parallel prefix (no sub-round of their own)
   long long why[5];  // what ended the prefix: batch end, in-batch neighbour, needs sequential path, no free parent, read/write conflict
   int wave_Fs[2];         // prefix length of the current sub-round (slot = round & 1; the other slot is being re-armed)
   long long windows;      // windows scanned since the current krrt_grow call began
