@@ -14,4 +14,4 @@ for k in ('c1','c3_100k','c3_1m'):
     c=d.get(k)
     if c: print(k, c['expansions_per_sec'], c['ms'], c.get('gpu_over_cpu'), c.get('parity_vs_oracle'))
 PY
-timeout 400 python profiles/ab_probe.py - KRRT_TAIL_SEQ=0 - 2>&1 | tee gpurun_out/ab_tail.txt
+timeout 400 python profiles/ab_probe.py - KRRT_INTRA_FIX=0 KRRT_INTRA_FIX=0,KRRT_TAIL_SEQ=0 - 2>&1 | tee gpurun_out/ab_tail.txt

@@ -475,6 +475,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     gcfg.pend_resolve = envi("KRRT_PEND", 1);
     gcfg.raw_forward = envi("KRRT_RAW_FORWARD", 1);
     gcfg.tail_seq = envi("KRRT_TAIL_SEQ", 1);
+    gcfg.intra_fix = envi("KRRT_INTRA_FIX", 1);
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
   }

@@ -62,6 +62,7 @@ struct GrowCfg {
   GridIndex gi;                // spatial index of the neighbour scan
   int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
+  int intra_fix;               // a rewire candidate that is a CHILD of a node the same sample rewires is settled in decide (0: in-order path)
   int tail_seq;                // a sample that needs the in-order path right behind the prefix is committed in the same sub-round
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
@@ -136,6 +137,7 @@ __device__ __forceinline__ void unlink_child_cg(const TreeView& T, int par, int 
 }
 
 constexpr int GROW_QCAP = 1024;   // strict descendants of one sample's rewired nodes that the parallel path handles
+constexpr int WL_DEAD = (int)0x80000000;  // wl_par of a write-list entry that is rewired in its own right
 constexpr int GROW_HASH = 512;    // near-set membership table (>= 2 x GROW_THREADS)
 
 struct GrowShared {  // lives in dynamic shared memory, in front of the in-order commit's scratch
@@ -146,12 +148,16 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
       double tf[GROW_THREADS];   // tau*(node -> sample)
       double tb[GROW_THREADS];   // tau*(sample -> node)
       double tim[GROW_THREADS];  // arrival time of the node
-      int flag[GROW_THREADS];    // 1 in near set, 2 forward edge collides, 8 rewire edge collides
+      double cb[GROW_THREADS];   // c*(sample -> node)
+      int flag[GROW_THREADS];    // 1 in near set, 2 forward edge collides, 8 rewire edge collides; 16 child of a rewired node,
+                                 // 32 rewired with a candidate among its children, 64 rewired twice over (see decide)
       int cand[GROW_THREADS];    // slots of the rewire candidates
       int rewn[GROW_THREADS];    // rewired nodes, in the order they become children of the new node
+      int rslot[GROW_THREADS];   // their candidate slots
       double rctc[GROW_THREADS]; // their new cost-to-come / arrival time (apply)
       double rtim[GROW_THREADS];
-      int hash[GROW_HASH];       // open addressing over the near set's node indices
+      int hash[GROW_HASH];       // open addressing over the rewire candidates' node indices ...
+      int hslot[GROW_HASH];      // ... and their candidate slots
       int wl[GROW_QCAP];         // strict descendants of the rewired nodes, level by level ...
       int wl_head[GROW_QCAP];    // ... their first child (read together with the sibling link) ...
       int wl_par[GROW_QCAP];     // ... and their parent: index in wl, or -(q + 1) for rewired node q
@@ -167,6 +173,7 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
   double rho[GROW_THREADS];  // squared near radius at tree sizes nsub .. nsub + nb
   double par_cf;             // c*(parent -> sample)
   int ncand, nrew, tail, tries, K, flags, intra;
+  int ndead, xprop, tries_adj, xflag;  // candidates among the children of rewired nodes (decide)
   long long fin[20];  // last CTA: counters of the call, flushed to the control block when the kernel ends
 };
 __host__ __device__ inline size_t grow_shared_bytes() { return (sizeof(GrowShared) + 15) / 16 * 16; }
@@ -622,7 +629,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       const size_t base = (size_t)b * cap;
       const unsigned key = mark_key(round, cta);
       // what this CTA carries from decide to validate and apply
-      int outcome = OUT_REJECT, n_b = 0, K = 0, par = -1, park = -1, nrew = 0, nwl = 0, nlvl = 0;
+      int outcome = OUT_REJECT, n_b = 0, K = 0, par = -1, park = -1, nrew = 0, nwl = 0, nlvl = 0, nprop = 0;
       long long collide_calls = 0;
       double ctc_new = 0.0, tim_new = 0.0, rho2n = 0.0;
       int my_node = -1, my_q = -1;
@@ -667,6 +674,10 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.K = 0;
           sm.flags = 0;
           sm.intra = 0;
+          sm.ndead = 0;
+          sm.xprop = 0;
+          sm.tries_adj = 0;
+          sm.xflag = 0;
         }
         if (rejected) break;  // OUT_REJECT
         DBG_STAMP(1);
@@ -727,6 +738,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.u.d.tim[t] = my_tim;
           sm.u.d.tf[t] = my_tf;
           sm.u.d.tb[t] = my_tb;
+          sm.u.d.cb[t] = my_cb;
         }
         sm.u.d.flag[t] = my_near ? 1 : 0;
         __syncthreads();
@@ -830,6 +842,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           // look for those below the rewired nodes.
           unsigned hsl = near_hash(my_node);
           while (atomicCAS(&sm.u.d.hash[hsl], -1, my_node) != -1) hsl = (hsl + 1) & (GROW_HASH - 1);
+          sm.u.d.hslot[hsl] = t;
         }
         __syncthreads();
         const int ncand = sm.ncand;
@@ -850,6 +863,9 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         if (cand && !(sm.u.d.flag[t] & 8)) {  // candidate and free: rewired.  Its children seed the write list
           my_q = atomicAdd(&sm.nrew, 1);
           sm.u.d.rewn[my_q] = my_node;
+          sm.u.d.rslot[my_q] = t;
+          sm.u.d.rctc[my_q] = ctc_new + my_cb;
+          sm.u.d.rtim[my_q] = tim_new + sm.u.d.tb[t];
           atomicMax(&W.wmin[my_node], key);
           atomicMax(&W.rmin[my_node], ((unsigned long long)key << 32) | (unsigned)t);
           push_children(T, sm, my_head, -(my_q + 1));
@@ -877,17 +893,73 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           for (int q = level0 + t; q < level1; q += GROW_THREADS) {
             const int d = sm.u.d.wl[q];
             atomicMax(&W.wmin[d], key);
+            bool dead = false;
             for (unsigned hsl = near_hash(d);; hsl = (hsl + 1) & (GROW_HASH - 1)) {
               const int hv = sm.u.d.hash[hsl];
-              if (hv == d) sm.intra = 1;
+              if (hv == d) {
+                // d is a rewire candidate below a node this sample rewires.  A CHILD of rewired node r is settled here
+                // (rewires go in ascending index, each sees the costs the previous one left):
+                //  d < r: d is tested first, at its old cost — as decided above; if it is rewired it leaves r's subtree
+                //  d > r: r goes first and d's cost drops to r's new cost + d's edge; d is tested again at that cost
+                // If d is rewired it is a child of the new node in its own right: its entry below r is dead.
+                // Anything deeper, chains (r itself a candidate child of a rewired node) and a rewired d that fails
+                // the second test take the in-order path.
+                const int pr = sm.u.d.wl_par[q];
+                if (!cfg.intra_fix || pr >= 0) {
+                  sm.intra = 1;
+                } else {
+                  const int ks = sm.u.d.hslot[hsl];
+                  const int rq = -pr - 1;
+                  const bool kfree = !(sm.u.d.flag[ks] & 8);
+                  atomicOr(&sm.u.d.flag[sm.u.d.rslot[rq]], 32);
+                  atomicOr(&sm.u.d.flag[ks], 16);
+                  if (d > sm.u.d.rewn[rq]) {
+                    const double ck = sm.u.d.rctc[rq] + __ldcg(&T.ecost[d]);
+                    if (ctc_new + sm.u.d.cb[ks] < ck) {
+                      if (kfree) {  // r's propagation reaches d and its subtree, then d's own does: counted twice
+                        atomicOr(&sm.u.d.flag[ks], 64);
+                        sm.xflag = 1;
+                      }
+                    } else if (kfree) {
+                      sm.intra = 1;
+                    } else {
+                      atomicAdd(&sm.tries_adj, 1);  // no longer a candidate: its (colliding) edge is never tested
+                    }
+                  }
+                  if (kfree) {
+                    dead = true;
+                    sm.u.d.wl_par[q] = WL_DEAD;
+                    atomicAdd(&sm.ndead, 1);
+                  }
+                }
+              }
               if (hv == d || hv < 0) break;
             }
-            push_children(T, sm, sm.u.d.wl_head[q], q);
+            if (!dead) push_children(T, sm, sm.u.d.wl_head[q], q);
           }
           level0 = level1;
           __syncthreads();
         }
         nwl = overflow ? 0 : level0;
+        nprop = nwl;  // what a sequential planner counts as propagated
+        if (!overflow && sm.ndead > 0) {
+          if (my_q >= 0 && (sm.u.d.flag[t] & 48) == 48) sm.intra = 1;  // chain: the in-order path
+          if (sm.xflag) {
+            int cnt = (my_q >= 0 && (sm.u.d.flag[t] & 64)) ? 1 : 0;
+            for (int q = t; q < nwl; q += GROW_THREADS) {
+              int p = sm.u.d.wl_par[q];
+              if (p == WL_DEAD) continue;
+              while (p >= 0) p = sm.u.d.wl_par[p];  // (a dead entry has no children)
+              if (sm.u.d.flag[sm.u.d.rslot[-p - 1]] & 64) ++cnt;
+            }
+            if (cnt) atomicAdd(&sm.xprop, cnt);
+          }
+          __syncthreads();
+          nprop = nwl - sm.ndead + sm.xprop;
+          collide_calls -= sm.tries_adj;
+        } else if (!overflow && sm.tries_adj > 0) {
+          collide_calls -= sm.tries_adj;
+        }
         DBG_STAMP(8);
         const int intra = sm.intra;
         outcome = (overflow || intra) ? OUT_COMPLEX : OUT_INSERT;
@@ -907,7 +979,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 #else
         r.pad = 0;
 #endif
-        r.outcome = outcome; r.n_b = n_b; r.par = par; r.park = park; r.K = K; r.nrew = nrew; r.nwl = nwl;
+        r.outcome = outcome; r.n_b = n_b; r.par = par; r.park = park; r.K = K; r.nrew = nrew; r.nwl = nprop;
         r.ctc_new = ctc_new; r.tim_new = tim_new; r.collide_calls = collide_calls; r.d2_in_max = 0.0; r.d2_out_min = 0.0;
         W.rec[b] = r;
       }
@@ -1083,10 +1155,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             et[i] = __ldcg(&T.etime[d]);
           }
         }
-        if (my_q >= 0) {
-          sm.u.d.rctc[my_q] = ctc_new + my_cb;
-          sm.u.d.rtim[my_q] = tim_new + sm.u.d.tb[t];
-        }
         if (t == 0) {
           T.pos[nw] = make_double2(s.x, s.y);
           T.vel[nw] = make_double2(s.vx, s.vy);
@@ -1131,7 +1199,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 #pragma unroll
             for (int i = 0; i < GROW_QCAP / GROW_THREADS; ++i) {
               const int q = t + i * GROW_THREADS;
-              if (q >= q0 && q < q1) {
+              if (q >= q0 && q < q1 && sm.u.d.wl_par[q] != WL_DEAD) {
                 const int d = sm.u.d.wl[q];
                 const int pr = sm.u.d.wl_par[q];
                 const double c = (pr >= 0 ? sm.u.d.wl_ctc[pr] : sm.u.d.rctc[-pr - 1]) + ec[i];

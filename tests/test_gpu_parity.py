@@ -491,3 +491,39 @@ def test_prefix_relaxations_can_be_switched_off(gpu_required, monkeypatch, pend,
     assert G2.wave_stats()["rounds_parallel"] < off
     for a, b in zip(G.tree(), G2.tree()):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dynamic,p_direct,n_iter", [(1, 0.1, 20000), (0, 0.0, 60000)])
+def test_candidates_below_rewired_nodes(gpu_required, monkeypatch, dynamic, p_direct, n_iter):
+    """A sample that rewires a node AND a candidate child of that node: settled inside decide (KRRT_INTRA_FIX, the child is
+    re-tested at the cost the first rewire leaves it), else committed in order right behind the prefix (KRRT_TAIL_SEQ), else
+    in a sub-round of its own.  Tree AND counters (collision tests, propagated nodes) equal the oracle's in all three modes;
+    the switches only change the number of sub-rounds."""
+    goal = scenes.GOAL if dynamic else None
+    rounds = []
+    for fix, tail in (("1", "1"), ("0", "1"), ("0", "0")):
+        monkeypatch.setenv("KRRT_INTRA_FIX", fix)
+        monkeypatch.setenv("KRRT_TAIL_SEQ", tail)
+        G, O = make_pair(gpu_required, dynamic=dynamic, p_direct=p_direct, capacity=n_iter + 2)
+        assert G.grow(goal, n_iter) == O.grow(goal, n_iter)
+        assert_same_tree(G, O)
+        w = G.wave_stats()
+        rounds.append((w["rounds_parallel"] + w["rounds_sequential"] - G.tail_commits(), w["rounds_sequential"], G.tail_commits()))
+        G.close()
+    (r_fix, seq_fix, _), (r_tail, seq_tail, t_tail), (r_off, seq_off, t_off) = rounds
+    assert t_off == 0 and t_tail > 0
+    assert seq_fix < seq_tail // 2       # most of these samples are the simple parent-and-child case
+    assert r_fix < r_tail < r_off
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
+def test_grow_headline_size_other_seeds(gpu_required, seed):
+    """The headline plan (C2: 9 moving opponents, 20 000 iterations) on other sample streams: tree and counters equal the
+    oracle's (the rare branches of the parallel commit — second cost test of a candidate child, chains, colliding candidates
+    that stop being candidates — are hit by different streams)."""
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, capacity=20002, seed=seed)
+    assert G.grow(scenes.GOAL, 20000) == O.grow(scenes.GOAL, 20000)
+    assert_same_tree(G, O)
+    G.close()
