@@ -154,6 +154,7 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
       int cand[GROW_THREADS];    // slots of the rewire candidates
       int rewn[GROW_THREADS];    // rewired nodes, in the order they become children of the new node
       int rslot[GROW_THREADS];   // their candidate slots
+      int rpar[GROW_THREADS];    // their parents so far
       double rctc[GROW_THREADS]; // their new cost-to-come / arrival time (apply)
       double rtim[GROW_THREADS];
       int hash[GROW_HASH];       // open addressing over the rewire candidates' node indices ...
@@ -707,12 +708,13 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
         State4 x = {0, 0, 0, 0};
         double my_tim = 0.0;
-        int my_head = -1;
+        int my_head = -1, my_par0 = -1;
         if (my_node >= 0) {
           x = load_state_cg(T, my_node);
           my_ctc = __ldcg(&T.ctc[my_node]);
           my_tim = __ldcg(&T.tim[my_node]);
           my_head = __ldcg(&T.link[my_node].x);  // only needed if the node gets rewired; it rides along for free
+          my_par0 = __ldcg(&T.parent[my_node]);  // (likewise: apply detaches the node from this parent's list)
         }
         sm.u.d.hash[t] = -1;
         sm.u.d.hash[t + GROW_THREADS] = -1;
@@ -864,6 +866,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           my_q = atomicAdd(&sm.nrew, 1);
           sm.u.d.rewn[my_q] = my_node;
           sm.u.d.rslot[my_q] = t;
+          sm.u.d.rpar[my_q] = my_par0;
           sm.u.d.rctc[my_q] = ctc_new + my_cb;
           sm.u.d.rtim[my_q] = tim_new + sm.u.d.tb[t];
           atomicMax(&W.wmin[my_node], key);
@@ -1007,21 +1010,43 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         if (outcome == OUT_NOFREE || outcome == OUT_INSERT) {
           // the node index / tree size this sample really gets: earlier samples that found no free parent did not insert.
           // The decision was taken at the radius of n_b; it stands if no candidate changes sides between the two radii.
-          const int ins = __syncthreads_count(t < cta && __ldcg(&W.rec[F0 + t].outcome) == OUT_INSERT);
-          n_true = nsub + ins;
-          bool conf = false;
-          if (n_true != n_b && my_node >= 0) {
-            const double rt = P.rho2[n_true];
-            conf = (my_d <= rho2n) != (my_d <= rt);
+          // one round trip for everything that is addressed by what decide left behind: the earlier samples' outcomes, the
+          // marks on this thread's near node, the record of its same-sub-round neighbour, the marks on the nodes it writes
+          const int o_t = t < cta ? __ldcg(&W.rec[F0 + t].outcome) : -1;
+          unsigned mw = 0, mk_w = 0xffffffffu, mk_a = 0xffffffffu, ml_w = 0xffffffffu, ml_a = 0xffffffffu;
+          unsigned long long mr = 0;
+          if (my_near) {
+            mw = __ldcg(&W.wmin[my_node]);
+            mr = __ldcg(&W.rmin[my_node]);
           }
+          int oe = -1;
+          double ce_p = 0.0;
+          if (pend_e >= 0) {
+            oe = __ldcg(&W.rec[pend_e].outcome);
+            ce_p = __ldcg(&W.rec[pend_e].ctc_new);
+          }
+          const bool chk_r = outcome == OUT_INSERT && t < nrew, chk_l = outcome == OUT_INSERT && t < nwl;
+          if (chk_r) {
+            const int j = sm.u.d.rewn[t];
+            mk_w = __ldcg(&W.wmin[j]);
+            mk_a = __ldcg(&W.amin[j]);
+          }
+          if (chk_l) {
+            const int j = sm.u.d.wl[t];
+            ml_w = __ldcg(&W.wmin[j]);
+            ml_a = __ldcg(&W.amin[j]);
+          }
+          const int ins = __syncthreads_count(o_t == OUT_INSERT);
+          n_true = nsub + ins;
+          const double rt = sm.rho[ins];  // == P.rho2[n_true]: n_true < capacity, or n_b would have been too
+          bool conf = false;
+          if (n_true != n_b && my_node >= 0) conf = (my_d <= rho2n) != (my_d <= rt);
           WHY(conf, 1);
           // A near node whose cost an earlier sample of the sub-round changes.  If that sample REWIRED it, the new cost is
           // that sample's cost + c*(sample -> node), both on record (the rewire mark carries the node's slot in the writer's
           // candidate list); it only went down, so this decision stands unless the node is the parent, was tried as parent, is a rewire candidate, or
           // would now be tried before the chosen parent.  A cost changed by propagation ends the prefix as before.
           if (my_near) {
-            const unsigned mw = __ldcg(&W.wmin[my_node]);
-            const unsigned long long mr = __ldcg(&W.rmin[my_node]);  // (one round trip for both)
             const int w = mark_sample(mw, round);
             if (w < cta) {
               bool c = true;
@@ -1044,10 +1069,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           // a later sample that rewires it fails here, one that rewires an ancestor fails on the read marks of its parent.
           bool joins = false;
           if (pend_e >= 0) {
-            const WaveRec* re = &W.rec[pend_e];
-            const int oe = __ldcg(&re->outcome);
-            const double ce = __ldcg(&re->ctc_new);
-            if (oe == OUT_INSERT && my_d <= P.rho2[n_true]) {
+            const double ce = ce_p;
+            if (oe == OUT_INSERT && my_d <= rt) {
               joins = true;
               conf |= outcome == OUT_NOFREE || my_d == 0.0 || ce + my_cf < ctc_new || ctc_new + my_cb < ce;
               WHY(outcome == OUT_NOFREE, 4); WHY(my_d == 0.0, 8); WHY(ce + my_cf < ctc_new, 16); WHY(ctc_new + my_cb < ce, 32);
@@ -1057,13 +1080,17 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           if (n_join > 0 && t == 0) W.rec[b].K = K + n_join;
           if (outcome == OUT_INSERT) {
             // nodes this sample writes: none may have been written, or chosen as parent, by an earlier sample
-            if (t < nrew) {
-              const int j = sm.u.d.rewn[t];
-              const bool c = min(mark_sample(__ldcg(&W.wmin[j]), round), mark_sample(__ldcg(&W.amin[j]), round)) < cta;
+            if (chk_r) {
+              const bool c = min(mark_sample(mk_w, round), mark_sample(mk_a, round)) < cta;
               conf |= c;
               WHY(c, 64);
             }
-            for (int q = t; q < nwl; q += GROW_THREADS) {
+            if (chk_l) {
+              const bool c = min(mark_sample(ml_w, round), mark_sample(ml_a, round)) < cta;
+              conf |= c;
+              WHY(c, 128);
+            }
+            for (int q = t + GROW_THREADS; q < nwl; q += GROW_THREADS) {
               const int j = sm.u.d.wl[q];
               const bool c = min(mark_sample(__ldcg(&W.wmin[j]), round), mark_sample(__ldcg(&W.amin[j]), round)) < cta;
               conf |= c;
@@ -1176,7 +1203,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           if ((t & 31) == 0 && t > 0) {
             for (int q = (t >> 5) - 1; q < nrew; q += GROW_THREADS / 32 - 1) {
               const int j = sm.u.d.rewn[q];
-              const int old = __ldcg(&T.parent[j]);
+              const int old = sm.u.d.rpar[q];  // (nobody else of the prefix has rewired j: that would be a conflict)
               list_lock(W.lock, old);
               unlink_child_cg(T, old, j);
               list_unlock(W.lock, old);
