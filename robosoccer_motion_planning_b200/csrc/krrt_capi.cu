@@ -44,7 +44,7 @@ struct krrt_ctx {
   Wave W{};
   Params P{};
   int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the in-order commit (debugging / A-B timing)
-  int wave_min_n = 64;        // trees smaller than this commit in order (conflicts everywhere; profiles/r1_param_sweep.txt)
+  int wave_min_n = 32;        // trees smaller than this commit in order (conflicts everywhere; profiles/r1_param_sweep.txt)
   int small_max_n = 256;      // few-expansion calls on trees below this: one CTA, plain launch, in-order commit
   int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
   GridBar* d_bar = nullptr;    // its two grid barriers
