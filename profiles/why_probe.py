@@ -27,3 +27,4 @@ for mode, n_iter in (("c2", 20000), ("c3", 100000)):
     for k, nm in enumerate(NAMES):
         if d[k]:
             print(f"  {nm:50s} {int(d[k])}")
+    print(f"  {'(of the reads: cost changed by propagation)':50s} {int(d[15])}")

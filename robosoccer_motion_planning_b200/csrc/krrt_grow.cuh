@@ -62,6 +62,7 @@ struct GrowCfg {
   GridIndex gi;                // spatial index of the neighbour scan
   int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
+  int prop_forward;            // a near node whose cost an earlier sample's PROPAGATION changes: re-check with the new cost
   int intra_fix;               // a rewire candidate that is a CHILD of a node the same sample rewires is settled in decide (0: in-order path)
   int tail_seq;                // a sample that needs the in-order path right behind the prefix is committed in the same sub-round
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
@@ -155,14 +156,14 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
       int rewn[GROW_THREADS];    // rewired nodes, in the order they become children of the new node
       int rslot[GROW_THREADS];   // their candidate slots
       int rpar[GROW_THREADS];    // their parents so far
-      double rctc[GROW_THREADS]; // their new cost-to-come / arrival time (apply)
+      double rctc[GROW_THREADS]; // their new cost-to-come / arrival time (decide)
       double rtim[GROW_THREADS];
       int hash[GROW_HASH];       // open addressing over the rewire candidates' node indices ...
       int hslot[GROW_HASH];      // ... and their candidate slots
       int wl[GROW_QCAP];         // strict descendants of the rewired nodes, level by level ...
       int wl_head[GROW_QCAP];    // ... their first child (read together with the sibling link) ...
       int wl_par[GROW_QCAP];     // ... and their parent: index in wl, or -(q + 1) for rewired node q
-      double wl_ctc[GROW_QCAP];  // new cost-to-come / arrival time (apply)
+      double wl_ctc[GROW_QCAP];  // new cost-to-come / arrival time (decide, on the way down)
       double wl_tim[GROW_QCAP];
       int lvl[GROW_LEVELS + 2];  // level boundaries in wl
     } d;
@@ -182,15 +183,20 @@ __host__ __device__ inline size_t grow_shared_bytes() { return (sizeof(GrowShare
 __device__ __forceinline__ unsigned near_hash(int node) { return ((unsigned)node * 2654435761u) >> 23; }  // 9 bits
 
 // children of `first`'s list go to the write list: one 8-byte load per sibling gives its own first child too
-__device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm, int first, int parent_ref) {
+// (the child's edge cost / duration ride along: its new cost-to-come / arrival time = the parent's new ones + the edge's)
+__device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm, int first, int parent_ref, double pc,
+                                              double pt) {
   int c = first;
   for (int guard = 0; c >= 0 && guard < T.cap; ++guard) {
     const int2 lk = __ldcg(&T.link[c]);
+    const double ec = __ldcg(&T.ecost[c]), et = __ldcg(&T.etime[c]);
     const int pos = atomicAdd(&sm.tail, 1);
     if (pos < GROW_QCAP) {
       sm.u.d.wl[pos] = c;
       sm.u.d.wl_head[pos] = lk.x;
       sm.u.d.wl_par[pos] = parent_ref;
+      sm.u.d.wl_ctc[pos] = pc + ec;
+      sm.u.d.wl_tim[pos] = pt + et;
     }
     c = lk.y;
   }
@@ -871,7 +877,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.u.d.rtim[my_q] = tim_new + sm.u.d.tb[t];
           atomicMax(&W.wmin[my_node], key);
           atomicMax(&W.rmin[my_node], ((unsigned long long)key << 32) | (unsigned)t);
-          push_children(T, sm, my_head, -(my_q + 1));
+          push_children(T, sm, my_head, -(my_q + 1), ctc_new + my_cb, tim_new + sm.u.d.tb[t]);
         }
         __syncthreads();
         nrew = sm.nrew;
@@ -917,7 +923,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
                   atomicOr(&sm.u.d.flag[sm.u.d.rslot[rq]], 32);
                   atomicOr(&sm.u.d.flag[ks], 16);
                   if (d > sm.u.d.rewn[rq]) {
-                    const double ck = sm.u.d.rctc[rq] + __ldcg(&T.ecost[d]);
+                    const double ck = sm.u.d.wl_ctc[q];  // == r's new cost + d's edge
                     if (ctc_new + sm.u.d.cb[ks] < ck) {
                       if (kfree) {  // r's propagation reaches d and its subtree, then d's own does: counted twice
                         atomicOr(&sm.u.d.flag[ks], 64);
@@ -938,7 +944,12 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
               }
               if (hv == d || hv < 0) break;
             }
-            if (!dead) push_children(T, sm, sm.u.d.wl_head[q], q);
+            if (!dead) {
+              // the new cost goes on record for later samples of the sub-round that have d in their near set
+              atomicMax(&W.rmin[d], ((unsigned long long)key << 32) | (unsigned)(256 + q));
+              __stcg(&W.wlc[(size_t)cta * GROW_QCAP + q], sm.u.d.wl_ctc[q]);
+              push_children(T, sm, sm.u.d.wl_head[q], q, sm.u.d.wl_ctc[q], sm.u.d.wl_tim[q]);
+            }
           }
           level0 = level1;
           __syncthreads();
@@ -1052,14 +1063,22 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
               bool c = true;
               if (cfg.raw_forward && outcome == OUT_INSERT && mark_sample((unsigned)(mr >> 32), round) == w &&
                   t != park && !my_tried && !my_cand) {
-                // new cost of the node = the rewiring sample's cost + its c*(sample -> node), both on record
-                const double ce = __ldcg(&W.rec[F0 + w].ctc_new);
-                const double c_e = __ldcg(&Bt.cb[(size_t)(F0 + w) * cap + (unsigned)mr]);
-                const double cn = (ce + c_e) + my_cf;
-                c = cn < ctc_new || (cn == ctc_new && my_node < par);
+                const unsigned where = (unsigned)mr;
+                if (where < 256u) {
+                  // rewired: new cost of the node = the rewiring sample's cost + its c*(sample -> node), both on record
+                  const double ce = __ldcg(&W.rec[F0 + w].ctc_new);
+                  const double c_e = __ldcg(&Bt.cb[(size_t)(F0 + w) * cap + where]);
+                  const double cn = (ce + c_e) + my_cf;
+                  c = cn < ctc_new || (cn == ctc_new && my_node < par);
+                } else if (cfg.prop_forward) {
+                  // below a rewired node: the writer left the propagated cost in its row
+                  const double cn = __ldcg(&W.wlc[(size_t)w * GROW_QCAP + (where - 256u)]) + my_cf;
+                  c = cn < ctc_new || (cn == ctc_new && my_node < par);
+                }
               }
               conf |= c;
               WHY(c, 2);
+              WHY(c && mark_sample((unsigned)(mr >> 32), round) != w, 256);  // ... by propagation, not by a rewire
             }
           }
           // A candidate that is an earlier sample of this very sub-round: its decision is on record now.  If it inserts
@@ -1169,18 +1188,12 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       DBG_START();
       if (active && cta < F && outcome == OUT_INSERT) {
         const int nw = n_true;
-        // edge cost / duration of this thread's share of the descendants: in flight while the lists are edited
-        double ec[GROW_QCAP / GROW_THREADS], et[GROW_QCAP / GROW_THREADS];
-#pragma unroll
-        for (int i = 0; i < GROW_QCAP / GROW_THREADS; ++i) {
-          const int q = t + i * GROW_THREADS;
-          ec[i] = 0.0;
-          et[i] = 0.0;
-          if (q < nwl) {
-            const int d = sm.u.d.wl[q];
-            ec[i] = __ldcg(&T.ecost[d]);
-            et[i] = __ldcg(&T.etime[d]);
-          }
+        // the descendants' new cost-to-come / arrival time were worked out on the way down (decide)
+        for (int q = t; q < nwl; q += GROW_THREADS) {
+          if (sm.u.d.wl_par[q] == WL_DEAD) continue;
+          const int d = sm.u.d.wl[q];
+          __stcg(&T.ctc[d], sm.u.d.wl_ctc[q]);
+          __stcg(&T.tim[d], sm.u.d.wl_tim[q]);
         }
         if (t == 0) {
           T.pos[nw] = make_double2(s.x, s.y);
@@ -1219,25 +1232,6 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             T.etime[j] = sm.u.d.tb[t];
             T.ctc[j] = sm.u.d.rctc[my_q];
             T.tim[j] = sm.u.d.rtim[my_q];
-          }
-          // level order: a node is updated one level after its parent; the new values travel through shared memory
-          for (int l = 0; l < nlvl; ++l) {
-            const int q0 = sm.u.d.lvl[l], q1 = sm.u.d.lvl[l + 1];
-#pragma unroll
-            for (int i = 0; i < GROW_QCAP / GROW_THREADS; ++i) {
-              const int q = t + i * GROW_THREADS;
-              if (q >= q0 && q < q1 && sm.u.d.wl_par[q] != WL_DEAD) {
-                const int d = sm.u.d.wl[q];
-                const int pr = sm.u.d.wl_par[q];
-                const double c = (pr >= 0 ? sm.u.d.wl_ctc[pr] : sm.u.d.rctc[-pr - 1]) + ec[i];
-                const double tt = (pr >= 0 ? sm.u.d.wl_tim[pr] : sm.u.d.rtim[-pr - 1]) + et[i];
-                sm.u.d.wl_ctc[q] = c;
-                sm.u.d.wl_tim[q] = tt;
-                __stcg(&T.ctc[d], c);
-                __stcg(&T.tim[d], tt);
-              }
-            }
-            __syncthreads();
           }
           DBG_STAMP(11);
         }

@@ -111,8 +111,10 @@ struct Wave {
   WaveRec* rec;     // [B]
   unsigned* wmin;   // [capacity] mark: lowest sample of this sub-round that WRITES the node's cost/time
   unsigned* amin;   // [capacity] mark: lowest sample of this sub-round that chose the node as PARENT (derived its cost from it)
-  unsigned long long* rmin;  // [capacity] (mark << 32 | slot): lowest sample of this sub-round that REWIRES the node, and the
-                             // node's slot in that sample's candidate list (where c*(sample -> node) is)
+  unsigned long long* rmin;  // [capacity] (mark << 32 | where): lowest sample of this sub-round that changes the node's cost, and
+                             // where the new cost is on record: where < 256: the node is REWIRED, its slot in that sample's
+                             // candidate list (c*(sample -> node)); else 256 + its place in that sample's row of wlc
+  double* wlc;      // [gridDim][GROW_QCAP] new cost-to-come of the nodes below the nodes CTA c's sample rewires
   int* lock;        // [capacity] child-list lock of a parent
   double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...
   int* nn_idx;      // ... (squared distance, node index)

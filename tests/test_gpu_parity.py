@@ -518,6 +518,24 @@ def test_candidates_below_rewired_nodes(gpu_required, monkeypatch, dynamic, p_di
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dynamic,p_direct,n_iter", [(1, 0.1, 20000), (0, 0.0, 60000)])
+def test_propagated_costs_are_forwarded(gpu_required, monkeypatch, dynamic, p_direct, n_iter):
+    """A near node whose cost an earlier sample of the sub-round lowers by PROPAGATION (it lies below a node that sample
+    rewires): the writer leaves the new cost on record and the reader re-checks its decision with it (KRRT_PROP_FORWARD)
+    instead of ending the prefix.  Same tree and counters either way, fewer sub-rounds with it."""
+    goal = scenes.GOAL if dynamic else None
+    rounds = []
+    for fwd in ("0", "1"):
+        monkeypatch.setenv("KRRT_PROP_FORWARD", fwd)
+        G, O = make_pair(gpu_required, dynamic=dynamic, p_direct=p_direct, capacity=n_iter + 2)
+        assert G.grow(goal, n_iter) == O.grow(goal, n_iter)
+        assert_same_tree(G, O)
+        rounds.append(G.wave_stats()["rounds_parallel"])
+        G.close()
+    assert rounds[1] < rounds[0]
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
 def test_grow_headline_size_other_seeds(gpu_required, seed):
     """The headline plan (C2: 9 moving opponents, 20 000 iterations) on other sample streams: tree and counters equal the
