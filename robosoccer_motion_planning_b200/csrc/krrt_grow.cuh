@@ -173,6 +173,7 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
   int red_i[GROW_THREADS / 32], red_k[GROW_THREADS / 32];
   double hS[GROW_SMAX];      // h = p / (S - 1) of the edge sample points
   double rho[GROW_THREADS];  // squared near radius at tree sizes nsub .. nsub + nb
+  int woff[GROW_WMAX + 1];   // steer: exclusive scan of the window's candidate counts
   double par_cf;             // c*(parent -> sample)
   int ncand, nrew, tail, tries, K, flags, intra;
   int ndead, xprop, tries_adj, xflag;  // candidates among the children of rewired nodes (decide)
@@ -571,14 +572,43 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     }
     grid_barrier(cfg.bar, bs_all, G, false);
     phase_done(0);
-    // ---- steer: tau*, c* of candidate -> sample and sample -> candidate, one thread per (candidate, direction)
-    for (int b = cta; b < Wn; b += G) {
-      const int cnt = min(__ldcg(&Bt.count[b]), cap);
-      const State4 s = sm.u.ss[b];
-      const size_t base = (size_t)b * cap;
-      for (int w = t; w < 2 * cnt; w += GROW_THREADS) {
-        const int e = w >> 1;
-        const bool fwd = (w & 1) == 0;
+    // ---- steer: tau*, c* of candidate -> sample and sample -> candidate, one thread per (candidate, direction).  The
+    // window's (sample, candidate, direction) items are spread evenly over the whole grid: every CTA scans the candidate
+    // counts for itself (one L2 round trip) and finds its items' samples by bisection.
+    {
+      static_assert(GROW_WMAX <= 2 * GROW_THREADS, "two counts per thread");
+      const int b0 = 2 * t, b1 = 2 * t + 1;
+      const int c0 = b0 < Wn ? min(__ldcg(&Bt.count[b0]), cap) : 0;
+      const int c1 = b1 < Wn ? min(__ldcg(&Bt.count[b1]), cap) : 0;
+      int incl = c0 + c1;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(FULL, incl, off);
+        if ((t & 31) >= off) incl += v;
+      }
+      if ((t & 31) == 31) sm.red_i[t >> 5] = incl;
+      __syncthreads();
+      int wbase = 0;
+#pragma unroll
+      for (int w = 0; w < GROW_THREADS / 32; ++w)
+        if (w < (t >> 5)) wbase += sm.red_i[w];
+      const int excl = wbase + incl - (c0 + c1);
+      if (b0 <= Wn) sm.woff[b0] = excl;
+      if (b1 <= Wn) sm.woff[b1] = excl + c0;
+      if (t == GROW_THREADS - 1 && 2 * GROW_THREADS <= Wn) sm.woff[2 * GROW_THREADS] = excl + c0 + c1;
+      __syncthreads();
+      const int items = 2 * sm.woff[Wn];
+      for (int g = cta * GROW_THREADS + t; g < items; g += G * GROW_THREADS) {
+        const int pair = g >> 1;
+        const bool fwd = (g & 1) == 0;
+        int lo = 0, hi = Wn;  // the last sample whose offset is <= pair (samples without candidates share an offset)
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (sm.woff[mid] <= pair) lo = mid; else hi = mid;
+        }
+        const int b = lo, e = pair - sm.woff[lo];
+        const size_t base = (size_t)b * cap;
+        const State4 s = sm.u.ss[b];
         const int ref = __ldcg(&Bt.ref[base + e]);
         const State4 x = (ref & IN_BATCH) ? sm.u.ss[ref & ~IN_BATCH] : load_state_cg(T, ref);
         double tau, c;
