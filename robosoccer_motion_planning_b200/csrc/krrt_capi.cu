@@ -183,7 +183,7 @@ static int create_impl(krrt_ctx* ctx) {
   const krrt_config& c = ctx->cfg;
   REQUIRE(c.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED, "only KRRT_F64 is implemented");
   REQUIRE(c.capacity >= 2 && c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad capacity / S / r / R");
-  REQUIRE(c.batch >= 1 && c.batch <= GROW_WMAX, KRRT_ERR_INVALID, "batch must be in [1,512]");
+  REQUIRE(c.batch >= 1 && c.batch <= GROW_WMAX, KRRT_ERR_INVALID, "batch must be in [1,1024]");
   REQUIRE(c.near_cap >= 32 && c.near_cap <= 4096, KRRT_ERR_INVALID, "near_cap must be in [32,4096]");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -324,7 +324,7 @@ int krrt_create(const krrt_config* c, krrt_ctx** out) {
   *out = nullptr;
   krrt_ctx* ctx = new krrt_ctx();
   ctx->cfg = *c;
-  if (ctx->cfg.batch == 0) ctx->cfg.batch = 512;   // profiles/r1_param_sweep.txt
+  if (ctx->cfg.batch == 0) ctx->cfg.batch = 1024;   // profiles/r1_param_sweep.txt
   if (const char* e = std::getenv("KRRT_WINDOW")) ctx->cfg.batch = std::max(1, std::min(GROW_WMAX, std::atoi(e)));
   if (ctx->cfg.near_cap == 0) ctx->cfg.near_cap = 1024;
   int rc = create_impl(ctx);

@@ -32,7 +32,7 @@
 namespace krrt {
 
 constexpr int GROW_THREADS = 256;
-constexpr int GROW_WMAX = 512;    // window cap
+constexpr int GROW_WMAX = 1024;   // window cap
 constexpr int GROW_LEVELS = 62;   // BFS depth below the rewired nodes that the parallel path handles
 constexpr int GROW_SEQ_WINDOW = 64;
 constexpr int GROW_SMAX = 64;     // edge sample counts up to this use a shared table of h = p / (S - 1)
@@ -576,11 +576,16 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     // window's (sample, candidate, direction) items are spread evenly over the whole grid: every CTA scans the candidate
     // counts for itself (one L2 round trip) and finds its items' samples by bisection.
     {
-      static_assert(GROW_WMAX <= 2 * GROW_THREADS, "two counts per thread");
-      const int b0 = 2 * t, b1 = 2 * t + 1;
-      const int c0 = b0 < Wn ? min(__ldcg(&Bt.count[b0]), cap) : 0;
-      const int c1 = b1 < Wn ? min(__ldcg(&Bt.count[b1]), cap) : 0;
-      int incl = c0 + c1;
+      constexpr int CPT = GROW_WMAX / GROW_THREADS;  // consecutive counts per thread
+      static_assert(CPT * GROW_THREADS == GROW_WMAX, "window cap is a multiple of the CTA size");
+      int c[CPT], mine = 0;
+#pragma unroll
+      for (int k = 0; k < CPT; ++k) {
+        const int b = CPT * t + k;
+        c[k] = b < Wn ? min(__ldcg(&Bt.count[b]), cap) : 0;
+        mine += c[k];
+      }
+      int incl = mine;
 #pragma unroll
       for (int off = 1; off < 32; off <<= 1) {
         const int v = __shfl_up_sync(FULL, incl, off);
@@ -588,14 +593,17 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       }
       if ((t & 31) == 31) sm.red_i[t >> 5] = incl;
       __syncthreads();
-      int wbase = 0;
+      int run = incl - mine;
 #pragma unroll
       for (int w = 0; w < GROW_THREADS / 32; ++w)
-        if (w < (t >> 5)) wbase += sm.red_i[w];
-      const int excl = wbase + incl - (c0 + c1);
-      if (b0 <= Wn) sm.woff[b0] = excl;
-      if (b1 <= Wn) sm.woff[b1] = excl + c0;
-      if (t == GROW_THREADS - 1 && 2 * GROW_THREADS <= Wn) sm.woff[2 * GROW_THREADS] = excl + c0 + c1;
+        if (w < (t >> 5)) run += sm.red_i[w];
+#pragma unroll
+      for (int k = 0; k < CPT; ++k) {
+        const int b = CPT * t + k;
+        if (b <= Wn) sm.woff[b] = run;
+        run += c[k];
+      }
+      if (t == GROW_THREADS - 1 && Wn == GROW_WMAX) sm.woff[GROW_WMAX] = run;
       __syncthreads();
       const int items = 2 * sm.woff[Wn];
       for (int g = cta * GROW_THREADS + t; g < items; g += G * GROW_THREADS) {
