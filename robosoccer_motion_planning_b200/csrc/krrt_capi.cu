@@ -207,7 +207,7 @@ static int create_impl(krrt_ctx* ctx) {
   {
     const size_t bcn = (size_t)c.batch * c.near_cap;
     size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + cap * 8 + (GRID_CELLS_MAX + 1) * 4 +
-                  (cap + 1) * 8 + bcn * (4 + 8 * 5) + (size_t)1024 * GROW_QCAP * 8 +
+                  (cap + 1) * 8 + bcn * (4 + 8 * 5) + (size_t)1024 * GROW_QCAP * 8 + 2 * 1024 * 4 + 512 +
                   (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
 #ifdef KRRT_DEBUG_CLK
     need += (size_t)32 * ((1 << 20) + 1) + 4096;
@@ -262,6 +262,10 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &W.rmin, cap));
   CK(dev_alloc(ctx, &W.lock, cap));
   CK(dev_alloc(ctx, &W.wlc, (size_t)1024 * GROW_QCAP));
+  CK(dev_alloc(ctx, &W.done, (size_t)1024));
+  CK(dev_alloc(ctx, &W.ok, (size_t)1024));
+  CK(cudaMemsetAsync(W.done, 0, sizeof(unsigned) * 1024, ctx->stream));
+  CK(cudaMemsetAsync(W.ok, 0, sizeof(unsigned) * 1024, ctx->stream));
   CK(dev_alloc(ctx, &ctx->gi.pos, cap));
   CK(dev_alloc(ctx, &ctx->gi.vel, cap));
   CK(dev_alloc(ctx, &ctx->gi.id, cap));
@@ -478,6 +482,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     gcfg.tail_seq = envi("KRRT_TAIL_SEQ", 1);
     gcfg.intra_fix = envi("KRRT_INTRA_FIX", 1);
     gcfg.prop_forward = envi("KRRT_PROP_FORWARD", 1);
+    gcfg.flow = envi("KRRT_FLOW", 0);  // measured: no gain
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
   }
@@ -492,6 +497,8 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       CK(cudaMemsetAsync(ctx->W.wmin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.amin, 0, sizeof(unsigned) * cap, st));
       CK(cudaMemsetAsync(ctx->W.rmin, 0, sizeof(unsigned long long) * cap, st));
+      CK(cudaMemsetAsync(ctx->W.done, 0, sizeof(unsigned) * 1024, st));
+      CK(cudaMemsetAsync(ctx->W.ok, 0, sizeof(unsigned) * 1024, st));
     }
     ctx->ctl_valid = false;
     k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);

@@ -43,6 +43,27 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
   return v;
 }
 
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// watchdog of the flag waits below (see grid_barrier)
+__device__ __forceinline__ void flag_watchdog(unsigned& spins, unsigned long long& t_first, const char* what) {
+  if ((++spins & 0x3fffu) == 0) {
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+    if (t_first == 0) t_first = now;
+    else if (now - t_first > 5000000000ull) {
+      printf("krrt k_grow: %s wedged (cta %d, thread %d)\n", what, (int)blockIdx.x, (int)threadIdx.x);
+      __trap();
+    }
+  }
+}
+
 // Grid barrier over n co-resident CTAs (cooperative launch, one CTA per SM): one counter, red.release to arrive
 // (MEMBAR.ALL.GPU + REDG), ld.acquire to poll (LDG.STRONG.GPU + CCTL.IVALL, so later plain loads miss L1).  Measured on
 // B200 (tests/native/barrier_bench.cu): 2200 cycles with 64 CTAs, against 3000 for fence + atomicAdd + spin + fence
@@ -62,6 +83,7 @@ struct GrowCfg {
   GridIndex gi;                // spatial index of the neighbour scan
   int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
+  int flow;                    // sub-rounds as a dataflow: a sample waits for the samples BEFORE it only (0: two grid barriers)
   int prop_forward;            // a near node whose cost an earlier sample's PROPAGATION changes: re-check with the new cost
   int intra_fix;               // a rewire candidate that is a CHILD of a node the same sample rewires is settled in decide (0: in-order path)
   int tail_seq;                // a sample that needs the in-order path right behind the prefix is committed in the same sub-round
@@ -176,6 +198,7 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
   int woff[GROW_WMAX + 1];   // steer: exclusive scan of the window's candidate counts
   double par_cf;             // c*(parent -> sample)
   int ncand, nrew, tail, tries, K, flags, intra;
+  int tmpF;                  // flow: first sample of the sub-round that has not passed validation (<< 1 | not known yet)
   int ndead, xprop, tries_adj, xflag;  // candidates among the children of rewired nodes (decide)
   long long fin[20];  // last CTA: counters of the call, flushed to the control block when the kernel ends
 };
@@ -1039,7 +1062,27 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       if (active || last) cta_dec += clock64() - cta_t;
 #endif
       DBG_START();
-      grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      const unsigned tag = round + 1u;
+      if (cfg.flow) {
+        // Validation of sample c looks at what the samples BEFORE it decided (records, marks of lower samples): it waits
+        // for those only, not for the whole sub-round — a straggler (a sample with a deep subtree to walk) holds up the
+        // samples behind it, and those are the ones least likely to make it into the prefix anyway
+        if (active) {
+          __syncthreads();  // every mark of this CTA is issued, the record is written
+          if (t == 0) {
+            __threadfence();
+            st_release_u32(&W.done[cta], tag);
+          }
+          if (t < cta) {
+            unsigned spins = 0;
+            unsigned long long t_first = 0;
+            while (ld_acquire_u32(&W.done[t]) != tag) flag_watchdog(spins, t_first, "wait for earlier decisions");
+          }
+          __syncthreads();
+        }
+      } else {
+        grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      }
       DBG_STAMP(12);
       phase_done(2);
 #ifdef KRRT_DEBUG_CLK
@@ -1156,12 +1199,48 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           }
           fail = __syncthreads_or(conf) != 0;
         }
-        if (fail && t == 0) atomicMin(&ctl->wave_Fs[slot], cta);
+        if (t == 0) {
+          if (cfg.flow) {
+            __threadfence();
+            st_release_u32(&W.ok[cta], (tag << 1) | (fail ? 1u : 0u));
+          } else if (fail) {
+            atomicMin(&ctl->wave_Fs[slot], cta);
+          }
+        }
       }
 #ifdef KRRT_DEBUG_CLK
       if (active || last) cta_val += clock64() - cta_t;
 #endif
-      grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      int F_flow = nb;
+      if (cfg.flow) {
+        // the prefix: the first sample that failed validation, known as soon as every sample before it has passed —
+        // every CTA of the sub-round works it out for itself from the same flags
+        unsigned spins = 0, okv = 0;
+        unsigned long long t_first = 0;
+        bool have = false;
+        for (;;) {
+          if (t == 0) sm.tmpF = nb << 1;
+          __syncthreads();
+          if (t < nb) {
+            if (!have) {  // (a flag that has been seen is not fetched again: 148 CTAs poll the same five lines)
+              okv = ld_acquire_u32(&W.ok[t]);
+              have = (okv >> 1) == tag;
+            }
+            if (!have) atomicMin(&sm.tmpF, (t << 1) | 1);       // not validated yet
+            else if (okv & 1u) atomicMin(&sm.tmpF, t << 1);     // failed
+          }
+          __syncthreads();
+          const int key = sm.tmpF;
+          __syncthreads();
+          if (!(key & 1)) {
+            F_flow = key >> 1;
+            break;
+          }
+          flag_watchdog(spins, t_first, "wait for the prefix");
+        }
+      } else {
+        grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      }
       DBG_STAMP(12);
       phase_done(3);
 #ifdef KRRT_DEBUG_CLK
@@ -1169,7 +1248,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
 #endif
 
       // -------------------------------------------------------------- apply
-      const int F = min(nb, __ldcg(&ctl->wave_Fs[slot]));
+      const int F = cfg.flow ? F_flow : min(nb, __ldcg(&ctl->wave_Fs[slot]));
 #ifdef KRRT_WHY
       if (active && cta == F) {
         if (why_bits) atomicOr(&sm.flags, why_bits << 8);  // (sm.flags is re-initialised by the next decide)

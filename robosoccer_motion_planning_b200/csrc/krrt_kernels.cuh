@@ -114,6 +114,8 @@ struct Wave {
   unsigned long long* rmin;  // [capacity] (mark << 32 | where): lowest sample of this sub-round that changes the node's cost, and
                              // where the new cost is on record: where < 256: the node is REWIRED, its slot in that sample's
                              // candidate list (c*(sample -> node)); else 256 + its place in that sample's row of wlc
+  unsigned* done;   // [1024] sub-round tag of the last decision CTA c finished (flow)
+  unsigned* ok;     // [1024] (tag << 1 | failed) of the last validation CTA c finished (flow)
   double* wlc;      // [gridDim][GROW_QCAP] new cost-to-come of the nodes below the nodes CTA c's sample rewires
   int* lock;        // [capacity] child-list lock of a parent
   double* nn_d2;    // [gridDim] per-CTA partial of a grid-wide nearest-node scan ...

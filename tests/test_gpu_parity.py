@@ -536,6 +536,22 @@ def test_propagated_costs_are_forwarded(gpu_required, monkeypatch, dynamic, p_di
 
 
 @pytest.mark.gpu
+def test_dataflow_sub_rounds_same_tree(gpu_required, monkeypatch):
+    """KRRT_FLOW=1 (experimental, off by default: measured no faster): inside a sub-round a sample waits for the samples
+    before it only (per-sample flags with release/acquire) instead of two of the three grid barriers.  Same tree, same
+    counters, same sub-rounds."""
+    rounds = []
+    for flow in ("0", "1"):
+        monkeypatch.setenv("KRRT_FLOW", flow)
+        G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, capacity=20002)
+        assert G.grow(scenes.GOAL, 20000) == O.grow(scenes.GOAL, 20000)
+        assert_same_tree(G, O)
+        rounds.append(G.wave_stats())
+        G.close()
+    assert rounds[0] == rounds[1]
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
 def test_grow_headline_size_other_seeds(gpu_required, seed):
     """The headline plan (C2: 9 moving opponents, 20 000 iterations) on other sample streams: tree and counters equal the
