@@ -159,7 +159,10 @@ __device__ __forceinline__ void unlink_child_cg(const TreeView& T, int par, int 
   if (nx >= 0) __stcg(&T.prev[nx], pv);
 }
 
-constexpr int GROW_QCAP = 1024;   // strict descendants of one sample's rewired nodes that the parallel path handles
+#ifndef KRRT_QCAP
+#define KRRT_QCAP 1024
+#endif
+constexpr int GROW_QCAP = KRRT_QCAP;   // strict descendants of one sample's rewired nodes that the parallel path handles
 constexpr int WL_DEAD = (int)0x80000000;  // wl_par of a write-list entry that is rewired in its own right
 constexpr int GROW_HASH = 512;    // near-set membership table (>= 2 x GROW_THREADS)
 
@@ -1265,13 +1268,17 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       // the sample that ended the prefix needs the in-order path anyway (it rewires a node below another node it
       // rewires): the last CTA commits it right behind the prefix, one barrier later, instead of spending a whole
       // sub-round on it
-      const bool tail_seq = cfg.tail_seq && F > 0 && F < nb && __ldcg(&W.rec[F0 + F].outcome) == OUT_COMPLEX;
-      if (need_nn) {
-        const State4 s0 = Bt.samples[F0];
+      // — or has an empty near set: the grid-wide nearest-node scan runs behind the prefix as well
+      const int o_tail = (cfg.tail_seq && F > 0 && F < nb) ? __ldcg(&W.rec[F0 + F].outcome) : OUT_INSERT;
+      const bool tail_seq = o_tail == OUT_COMPLEX || o_tail == OUT_NEAREST;
+      const bool tail_nn = o_tail == OUT_NEAREST;
+      // this CTA's share of a nearest-node scan over nodes [0, n_scan) for window sample b_scan
+      auto nn_scan = [&](int b_scan, int n_scan) {
+        const State4 s0 = Bt.samples[b_scan];
         const int pidx = last ? Pn : cta;
         double bd = INFINITY;
         int bi = 0x7fffffff;
-        for (int i = pidx * GROW_THREADS + t; i < nsub; i += (Pn + 1) * GROW_THREADS) {
+        for (int i = pidx * GROW_THREADS + t; i < n_scan; i += (Pn + 1) * GROW_THREADS) {
           const double d = dist2(load_state_cg(T, i), s0);
           if (d < bd) {
             bd = d;
@@ -1300,6 +1307,31 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           W.nn_d2[pidx] = c;
           W.nn_idx[pidx] = ci;
         }
+      };
+      // the last CTA's first warp folds the partials
+      auto nn_fold = [&](int& ni, double& nd2) {
+        const int lane = t;
+        nd2 = INFINITY;
+        ni = 0x7fffffff;
+        for (int k = lane; k <= Pn; k += 32) {
+          const double c = __ldcg(&W.nn_d2[k]);
+          const int ci = __ldcg(&W.nn_idx[k]);
+          if (c < nd2 || (c == nd2 && ci < ni)) {
+            nd2 = c;
+            ni = ci;
+          }
+        }
+        for (int off = 16; off > 0; off >>= 1) {
+          const double c = __shfl_xor_sync(FULL, nd2, off);
+          const int ci = __shfl_xor_sync(FULL, ni, off);
+          if (c < nd2 || (c == nd2 && ci < ni)) {
+            nd2 = c;
+            ni = ci;
+          }
+        }
+      };
+      if (need_nn) {
+        nn_scan(F0, nsub);
         grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
       }
       DBG_START();
@@ -1405,26 +1437,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         } else {  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
           int ni = -1;
           double nd2 = 0.0;
-          if (need_nn) {
-            nd2 = INFINITY;
-            ni = 0x7fffffff;
-            for (int k = lane; k <= Pn; k += 32) {
-              const double c = __ldcg(&W.nn_d2[k]);
-              const int ci = __ldcg(&W.nn_idx[k]);
-              if (c < nd2 || (c == nd2 && ci < ni)) {
-                nd2 = c;
-                ni = ci;
-              }
-            }
-            for (int off = 16; off > 0; off >>= 1) {
-              const double c = __shfl_xor_sync(FULL, nd2, off);
-              const int ci = __shfl_xor_sync(FULL, ni, off);
-              if (c < nd2 || (c == nd2 && ci < ni)) {
-                nd2 = c;
-                ni = ci;
-              }
-            }
-          }
+          if (need_nn) nn_fold(ni, nd2);
           seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2);
           if (lane == 0) {
             ctl->ema16 = (3 * ema_sub + 16) / 4;
@@ -1433,9 +1446,16 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
         }
       }
       if (tail_seq) grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);  // the prefix is in the tree, ctl is up to date
+      if (tail_nn) {
+        nn_scan(F0 + F, __ldcg(&ctl->n));
+        grid_barrier(cfg.bar + 1, bs_sub, Pn + 1, false);
+      }
       if (last && t < 32) {
         if (tail_seq) {
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, -1, 0.0);
+          int ni = -1;
+          double nd2 = 0.0;
+          if (tail_nn) nn_fold(ni, nd2);
+          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2);
           if (t == 0) sm.fin[18] += 1;  // tail commits
         }
         __syncwarp();
