@@ -482,6 +482,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     gcfg.tail_seq = envi("KRRT_TAIL_SEQ", 1);
     gcfg.intra_fix = envi("KRRT_INTRA_FIX", 1);
     gcfg.prop_forward = envi("KRRT_PROP_FORWARD", 1);
+    gcfg.join_test = envi("KRRT_JOIN_TEST", 1);
     gcfg.flow = envi("KRRT_FLOW", 0);  // measured: no gain
     gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
     gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);

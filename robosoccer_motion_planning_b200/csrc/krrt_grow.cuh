@@ -83,6 +83,7 @@ struct GrowCfg {
   GridIndex gi;                // spatial index of the neighbour scan
   int raw_forward;             // a near node rewired by an earlier sample of the sub-round: re-check with its new cost
   int pend_resolve;            // resolve neighbours decided in the same sub-round at validation (0: they end the prefix)
+  int join_test;               // a newcomer that would be tried as parent / is a rewire candidate: test its edge at validation (0: ends the prefix)
   int flow;                    // sub-rounds as a dataflow: a sample waits for the samples BEFORE it only (0: two grid barriers)
   int prop_forward;            // a near node whose cost an earlier sample's PROPAGATION changes: re-check with the new cost
   int intra_fix;               // a rewire candidate that is a CHILD of a node the same sample rewires is settled in decide (0: in-order path)
@@ -159,6 +160,7 @@ __device__ __forceinline__ void unlink_child_cg(const TreeView& T, int par, int 
   if (nx >= 0) __stcg(&T.prev[nx], pv);
 }
 
+constexpr int GROW_XE = 8;  // newcomer edges one sample can settle at validation
 #ifndef KRRT_QCAP
 #define KRRT_QCAP 1024
 #endif
@@ -201,6 +203,10 @@ struct GrowShared {  // lives in dynamic shared memory, in front of the in-order
   int woff[GROW_WMAX + 1];   // steer: exclusive scan of the window's candidate counts
   double par_cf;             // c*(parent -> sample)
   int ncand, nrew, tail, tries, K, flags, intra;
+  // validate: edges to / from newcomers (earlier samples of the sub-round) that have to be collision-tested
+  State4 xe_a[GROW_XE], xe_b[GROW_XE];
+  double xe_tau[GROW_XE], xe_t0[GROW_XE];
+  int xe_hit[GROW_XE], nxe, xcalls;
   int tmpF;                  // flow: first sample of the sub-round that has not passed validation (<< 1 | not known yet)
   int ndead, xprop, tries_adj, xflag;  // candidates among the children of rewired nodes (decide)
   long long fin[20];  // last CTA: counters of the call, flushed to the control block when the kernel ends
@@ -706,6 +712,7 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
       int my_node = -1, my_q = -1;
       bool my_tried = false, my_cand = false;  // this thread's near node was tried as parent / is a rewire candidate
       int pend_e = -1;  // this thread's candidate is an earlier sample of the SAME sub-round (window index): see validate
+      double pend_tf = 0.0, pend_tb = 0.0;  // tau* of that candidate -> sample / sample -> candidate
       double my_d = 0.0, my_cf = 0.0, my_cb = 0.0, my_ctc = 0.0;
       bool my_near = false;
       State4 s = {0, 0, 0, 0};
@@ -749,6 +756,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           sm.xprop = 0;
           sm.tries_adj = 0;
           sm.xflag = 0;
+          sm.nxe = 0;
+          sm.xcalls = 0;
         }
         if (rejected) break;  // OUT_REJECT
         DBG_STAMP(1);
@@ -770,7 +779,11 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             const int mapped = __ldcg(&Bt.map[e]);            // (all three loads leave together)
             const bool e_ins = sample_insertable(Bt, P, e);
             if (e < F0) my_node = mapped;  // committed in an earlier sub-round (-1: it did not insert)
-            else if (cfg.pend_resolve) pend_e = e_ins ? e : -1;  // decided in this sub-round: settled at validation
+            else if (cfg.pend_resolve) {  // decided in this sub-round: settled at validation
+              pend_e = e_ins ? e : -1;
+              pend_tf = my_tf;
+              pend_tb = my_tb;
+            }
             else pend = e_ins;             // may land inside the radius: wait for the next sub-round
           } else {
             my_node = ref;
@@ -1115,10 +1128,13 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
             mr = __ldcg(&W.rmin[my_node]);
           }
           int oe = -1;
-          double ce_p = 0.0;
+          double ce_p = 0.0, te_p = 0.0;
+          State4 xe_p = {0, 0, 0, 0};
           if (pend_e >= 0) {
             oe = __ldcg(&W.rec[pend_e].outcome);
             ce_p = __ldcg(&W.rec[pend_e].ctc_new);
+            te_p = __ldcg(&W.rec[pend_e].tim_new);
+            xe_p = Bt.samples[pend_e];
           }
           const bool chk_r = outcome == OUT_INSERT && t < nrew, chk_l = outcome == OUT_INSERT && t < nwl;
           if (chk_r) {
@@ -1170,17 +1186,58 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
           // long as the newcomer would be neither the parent (it is tried before the chosen one only if strictly cheaper:
           // it has the highest index) nor a rewire candidate, and is not a duplicate.  Nobody changes its cost in between:
           // a later sample that rewires it fails here, one that rewires an ancestor fails on the read marks of its parent.
-          bool joins = false;
+          bool joins = false, need_a = false, need_b = false;
           if (pend_e >= 0) {
             const double ce = ce_p;
             if (oe == OUT_INSERT && my_d <= rt) {
               joins = true;
-              conf |= outcome == OUT_NOFREE || my_d == 0.0 || ce + my_cf < ctc_new || ctc_new + my_cb < ce;
+              conf |= my_d == 0.0;
+              // the newcomer would be tried as parent (all candidates are if none is free) / is a rewire candidate
+              need_a = outcome == OUT_NOFREE || ce + my_cf < ctc_new;
+              need_b = outcome == OUT_INSERT && ctc_new + my_cb < ce;
+              if (!cfg.join_test) {
+                conf |= need_a || need_b;
+                need_a = need_b = false;
+              }
               WHY(outcome == OUT_NOFREE, 4); WHY(my_d == 0.0, 8); WHY(ce + my_cf < ctc_new, 16); WHY(ctc_new + my_cb < ce, 32);
             }
           }
           const int n_join = __syncthreads_count(joins);
-          if (n_join > 0 && t == 0) W.rec[b].K = K + n_join;
+          // If that edge COLLIDES the decision stands — a sequential planner tests it (one more collision test) and moves on;
+          // if it is free the sample has another parent, or rewires the newcomer: redone in the next sub-round.
+          if (__syncthreads_or(need_a || need_b)) {
+            int my_x = -1;
+            if (need_a || need_b) {
+              my_x = atomicAdd(&sm.nxe, 1);
+              if (my_x < GROW_XE) {
+                sm.xe_a[my_x] = need_a ? xe_p : s;
+                sm.xe_b[my_x] = need_a ? s : xe_p;
+                sm.xe_tau[my_x] = need_a ? pend_tf : pend_tb;
+                sm.xe_t0[my_x] = need_a ? te_p : tim_new;
+                sm.xe_hit[my_x] = 0;
+              } else {
+                conf = true;
+              }
+            }
+            __syncthreads();
+            const int ne = min(sm.nxe, GROW_XE);
+            for (int w = t; w < ne * S; w += GROW_THREADS) {
+              const int q = w / S, p = w - q * S;
+              const Edge ed = make_edge(sm.xe_a[q], sm.xe_b[q], sm.xe_tau[q], sm.xe_t0[q]);
+              const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+              if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) sm.xe_hit[q] = 1;
+            }
+            __syncthreads();
+            if (my_x >= 0 && my_x < GROW_XE) {
+              if (sm.xe_hit[my_x]) atomicAdd(&sm.xcalls, 1);
+              else conf = true;
+            }
+            __syncthreads();
+          }
+          if (t == 0 && (n_join > 0 || sm.xcalls > 0)) {
+            W.rec[b].K = K + n_join;
+            W.rec[b].collide_calls = collide_calls + sm.xcalls;
+          }
           if (outcome == OUT_INSERT) {
             // nodes this sample writes: none may have been written, or chosen as parent, by an earlier sample
             if (chk_r) {

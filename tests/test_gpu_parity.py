@@ -536,6 +536,24 @@ def test_propagated_costs_are_forwarded(gpu_required, monkeypatch, dynamic, p_di
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dynamic,p_direct,n_iter", [(1, 0.1, 20000), (0, 0.0, 60000)])
+def test_newcomer_edges_tested_at_validation(gpu_required, monkeypatch, dynamic, p_direct, n_iter):
+    """A near neighbour inserted by an earlier sample of the same sub-round that would be tried as parent, or is a rewire
+    candidate: its edge is collision-tested at validation (KRRT_JOIN_TEST); if it collides the decision stands and the
+    test is counted, as a sequential planner counts it.  Same tree and counters either way, fewer sub-rounds with it."""
+    goal = scenes.GOAL if dynamic else None
+    rounds = []
+    for on in ("0", "1"):
+        monkeypatch.setenv("KRRT_JOIN_TEST", on)
+        G, O = make_pair(gpu_required, dynamic=dynamic, p_direct=p_direct, capacity=n_iter + 2)
+        assert G.grow(goal, n_iter) == O.grow(goal, n_iter)
+        assert_same_tree(G, O)
+        rounds.append(G.wave_stats()["rounds_parallel"])
+        G.close()
+    assert rounds[1] < rounds[0]
+
+
+@pytest.mark.gpu
 def test_dataflow_sub_rounds_same_tree(gpu_required, monkeypatch):
     """KRRT_FLOW=1 (experimental, off by default: measured no faster): inside a sub-round a sample waits for the samples
     before it only (per-sample flags with release/acquire) instead of two of the three grid barriers.  Same tree, same
