@@ -13,19 +13,28 @@
 //             descendants of the rewired nodes) + conflict marks on what it reads / would write
 //   validate  same CTA: is that decision what a sequential planner would take, given everything earlier samples of
 //             the sub-round do?  -> longest valid prefix F
-//   apply     same CTA, for the prefix: insert, rewire, level-order cost/time propagation (lists kept in shared
-//             memory since decide); the last CTA folds the counters / runs the sequential fall-back
+//   apply     same CTA, for the prefix: insert, rewire, store the propagated costs/times decide worked out (lists kept
+//             in shared memory since decide); the last CTA folds the counters and, if the sample right behind the prefix
+//             needs the in-order path, commits it in the same sub-round
 //
 // Why the prefix is exact.  RRT* is sequential: expansion k+1 sees the tree after k.  But an expansion only READS
 // the cost/time of its near set and only WRITES the cost/time of the nodes it rewires and of their descendants.
-// Each decision marks both sets; sample b stays in the prefix iff no earlier sample writes anything b reads or
-// writes, no earlier sample reads anything b writes, no earlier uncommitted sample's new node can fall inside b's
-// near radius, and b's near set is unchanged at the radius of the tree size it really sees (earlier samples that
-// found no collision-free parent did not insert).  For such a prefix the sequential outcome IS the speculated one.
-// A sample that cannot be decided this way (empty near set -> global nearest, a rewired subtree larger than
-// GROW_QCAP, a near node inside one of its own rewired subtrees) is committed alone by one warp; while the tree is
-// small (conflicts everywhere) whole windows are.  Trees are bit-identical to the in-order commit whatever the
-// prefix lengths are.
+// Each decision leaves marks: on the nodes it writes (with where the NEW cost is on record), on the node it chose as
+// parent.  Sample b stays in the prefix iff, for every earlier sample of the sub-round,
+//   - a near node of b that the earlier sample writes keeps b's decision unchanged at its new (lower) cost: it is not
+//     b's parent, was not tried, is no rewire candidate, and is not cheaper than the chosen parent now;
+//   - nothing b writes was written, or chosen as parent, by the earlier sample (a node b merely read and a later sample
+//     writes is a write-after-read: harmless, b's decision is already taken);
+//   - the earlier sample's new node, if it lands inside b's radius, would not be a duplicate, and where it would be
+//     tried as parent or is a rewire candidate its edge collides (tested at validation, counted);
+//   - b's near set is unchanged at the radius of the tree size it really sees (earlier samples that found no
+//     collision-free parent did not insert).
+// For such a prefix the sequential outcome IS the speculated one, counters included.  A rewire candidate that is a CHILD
+// of a node the same sample rewires is settled inside decide (ascending-index order, second test at the lowered cost).
+// A sample that cannot be decided this way (empty near set -> global nearest, more than GROW_QCAP descendants or
+// GROW_LEVELS levels below its rewired nodes, a candidate deeper below a rewired node) is committed in order by one warp;
+// while the tree is small (conflicts everywhere) whole windows are.  Trees and counters are bit-identical to the
+// in-order commit whatever the prefix lengths are (DESIGN.md 5.1 lists each rule with its measured effect).
 #pragma once
 #include "krrt_kernels.cuh"
 
