@@ -448,8 +448,8 @@ def run_ours(args, rank, world, local_rank):
         line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
                                                else "MISMATCH")
         # config 0 (rrtstar_benchmark, C1): static obstacles, fixed seed, 10k iterations — GPU and the CPU port, same plan
-        G1 = capi.Planner(device=local_rank, capacity=10002, batch=args.batch, goal_tol=0.5)
-        O1 = ob.OraclePlanner(capacity=10002, query_id=0, goal_tol=0.5)
+        G1 = capi.Planner(device=local_rank, capacity=10002, batch=args.batch)
+        O1 = ob.OraclePlanner(capacity=10002, query_id=0)
         for P_ in (G1, O1):
             P_.set_obstacles(scenes.static_obstacles(), 0)
             P_.set_start(start)
@@ -463,7 +463,7 @@ def run_ours(args, rank, world, local_rank):
         dt1 = time.perf_counter() - t0
         same1 = r1 == ro1 and all(np.array_equal(a, b) for a, b in zip(G1.tree(), O1.tree()))
         line["c1_rrtstar_benchmark"] = {
-            "workload": "C1: 9 static obstacles, fixed seed, 10000 iterations, p_direct = 0, goal region 0.5",
+            "workload": "C1: 9 static obstacles, fixed seed, 10000 iterations, p_direct = 0, goal connected (O8)",
             "cost": float(G1.result(*r1)["cost"]) if r1[0] else None,
             "expansions_per_sec": 10000 / (ms1 * 1e-3), "ms": ms1, "nodes": G1.size, "solved": bool(r1[0]),
             "cpu_baseline": {"value": 10000 / dt1, "unit": UNIT, "cores": 1, "kind": "port", "sample": "the full plan, once"},
@@ -478,14 +478,14 @@ def run_ours(args, rank, world, local_rank):
         c_g = np.tile(goal, (qn, 1))
         c_o = np.tile(scenes.static_obstacles(), (qn, 1, 1))
         for p_dir in (0.0, 0.1):
-            Gc = capi.Planner(device=local_rank, p_direct=p_dir, goal_tol=0.5)
+            Gc = capi.Planner(device=local_rank, p_direct=p_dir)
             for nodes in (10, 25, 50, 75, 100, 150, 200):
                 Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
                 Gc.timer_begin()
                 oc = Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
                 msb = Gc.timer_end()
                 tcp = time.perf_counter()
-                rc_ = ob.plan_batch(ob.default_config(p_direct=p_dir, goal_tol=0.5), c_s[:4 * allc], c_g[:4 * allc], c_o[:4 * allc], 0,
+                rc_ = ob.plan_batch(ob.default_config(p_direct=p_dir), c_s[:4 * allc], c_g[:4 * allc], c_o[:4 * allc], 0,
                                     nodes, nthreads=allc)
                 tcp = time.perf_counter() - tcp
                 sv = oc["solved"] != 0
@@ -495,7 +495,7 @@ def run_ours(args, rank, world, local_rank):
                               "mean_cost": float(oc["cost"][sv].mean()) if sv.any() else None,
                               "parity": bool(np.array_equal(oc[:4 * allc].view(np.uint8), rc_.view(np.uint8)))})
             Gc.close()
-        line["readme_curve"] = {"scene": "C1 start/goal, 9 static obstacles, goal region 0.5 (state-space distance), 1024 seeds per point (query_id = seed)",
+        line["readme_curve"] = {"scene": "C1 start/goal, 9 static obstacles, goal connected to the cheapest collision-free node (O8), 1024 seeds per point (query_id = seed)",
                                 "points": curve}
         # config 3: single large tree, 100k iterations, static obstacles (+ the 1M-iteration tree with --c3-1m)
         if not args.skip_c3:

@@ -4,7 +4,8 @@
 // The reference's header of this name is part of the absent submodule src/motion_planning; what is mirrored
 // here is the surface its in-tree callers use (file:line under /root/reference/src/robosoccer_motion_planning/):
 //   Kinodynamic::TreeInt2D::State xs; xs(0)=…            src/robosoccer_motion_planning_node.cpp:131-133
-//   tree.tree.size()                                      …node.cpp:175,179
+//   tree.tree.size()                                      …node.cpp:175,179   (tree nodes; the connected goal node is
+//                                                         entry size() of the mirrors below while rrt.goalIndex() == size())
 //   tree.tree.cloud.states, tree.trajectories, tree.parent include/robosoccer_visual.hpp:18
 //   tree(i), tree.get_trajectory(idx) -> edges with .path() and (x,y,vx,vy,t) samples  robosoccer_visual.hpp:20-22,37-45
 //   tree.states(idx)                                      …node.cpp:237
@@ -191,8 +192,10 @@ class TreeInt2D {
     if (seen_ == session_->version() || !session_->started) return;
     auto* self = const_cast<TreeInt2D*>(this);
     krrt_ctx* c = session_->ctx();
-    int n = 0;
+    int n = 0, gi = -1;
     session_->check(krrt_tree_size(c, &n));
+    session_->check(krrt_goal_index(c, &gi));
+    if (gi == n) ++n;  // the goal node connected behind the tree: tree(goalIndex()), get_trajectory(goalIndex()), parent[goalIndex()]
     auto& st = self->tree.cloud.states.raw();
     auto& pa = self->parent.raw();
     st.resize(n);
@@ -201,7 +204,7 @@ class TreeInt2D {
     self->time_.resize(n);
     const int S = edge_samples;
     std::vector<double> rows((size_t)n * S * 5);
-    session_->check(krrt_tree_download(c, st[0].data(), pa.data(), self->cost_.data(), self->time_.data()));
+    session_->check(krrt_tree_read(c, 0, n, st[0].data(), pa.data(), self->cost_.data(), self->time_.data()));
     session_->check(krrt_tree_edges(c, S, rows.data(), n));
     auto& tr = self->trajectories.raw();
     tr.assign(n, Edge());
@@ -384,8 +387,14 @@ class GoalCheckerInt2D {
   static constexpr bool device_backed = true;
   using State = State4;
   GoalCheckerInt2D(Env* env, SamplerInt2D* sampler) : env_(env), sampler_(sampler), rng_(12345u) {}
-  double goal_tol = 0.0;  // a node is a goal node iff it lies within goal_tol of the goal (4-D Euclidean)
-  void configure(krrt_config& c) const { c.goal_tol = goal_tol; }
+  // KRRT_GOAL_CONNECT (default): the goal is connected to the cheapest collision-free node -> goal edge the tree offers
+  // when grow() returns; KRRT_GOAL_TOLERANCE: a node is a goal node iff it lies within goal_tol of the goal (krrt.h)
+  int goal_mode = KRRT_GOAL_CONNECT;
+  double goal_tol = 0.0;
+  void configure(krrt_config& c) const {
+    c.goal_mode = goal_mode;
+    c.goal_tol = goal_tol;
+  }
   // a resting goal on the field, outside every disc at t = 0 (…node.cpp:221; host-side, called once at start-up)
   State randomGoal() {
     State g{};

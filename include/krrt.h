@@ -51,6 +51,15 @@ enum {
 };
 
 enum { KRRT_F64 = 0, KRRT_F32 = 1 };
+/* Goal rule (GoalChecker slot; `solved` of rrt.grow(xg) …node.cpp:177, rrt.goalIndex() robosoccer_visual.hpp:19,40-45).
+ * KRRT_GOAL_CONNECT (default): when a grow call returns, every node the planner inserted (index >= 1) offers the edge
+ *   node -> goal (optimal steering, cost-to-come + c*, collision-tested like any other edge from the node's arrival
+ *   time); the goal's parent is the cheapest collision-free offer on the tree as it stands, lowest index among equal
+ *   costs.  The goal node is stored right behind the tree: goal_index == krrt_tree_size (> 0), valid for krrt_path /
+ *   krrt_trajectory / krrt_result_of / krrt_tree_edges until the next call that changes the tree; a tree node that
+ *   coincides with the goal (a direct sample) IS the goal node when it is the cheapest offer.
+ * KRRT_GOAL_TOLERANCE: the goal node is the cheapest tree node within goal_tol of the goal (4-D Euclidean).       */
+enum { KRRT_GOAL_CONNECT = 0, KRRT_GOAL_TOLERANCE = 1 };
 
 typedef struct krrt_config {
   int32_t device;     /* CUDA device ordinal                                                 */
@@ -64,12 +73,13 @@ typedef struct krrt_config {
   double gamma;       /* near radius rho(n) = min(rho_max, gamma (ln n / n)^(1/4))           */
   double rho_max;
   double p_direct;    /* sampler.set_direct_sample(true, p) (…node.cpp:225-226)              */
-  double goal_tol;    /* node is a goal node iff |x - goal| <= goal_tol (4-D Euclidean)      */
+  double goal_tol;    /* KRRT_GOAL_TOLERANCE: node is a goal node iff |x - goal| <= goal_tol */
   uint64_t seed;      /* Philox4x32-10 key                                                   */
   uint32_t query_id;  /* Philox counter word 1                                               */
   int32_t batch;      /* speculative batch: samples evaluated against a frozen tree per round, then
                          committed in order (results do not depend on it). 0 -> default      */
   int32_t near_cap;   /* per-sample candidate capacity. 0 -> default                         */
+  int32_t goal_mode;  /* KRRT_GOAL_CONNECT (default) / KRRT_GOAL_TOLERANCE                    */
 } krrt_config;
 
 typedef struct krrt_result {
@@ -111,8 +121,14 @@ int krrt_last_sample(krrt_ctx* ctx, double out[4]);
 int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out);
 /* any of the output pointers may be NULL.  states: n x 4, parent: n, cost/time: n              */
 int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time);
+/* rows [first, first + count) of the same arrays; the range may end with the goal node of KRRT_GOAL_CONNECT (index ==
+ * krrt_tree_size while krrt_goal_index says so): tree(rrt.goalIndex()) of robosoccer_visual.hpp:45                */
+int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t* parent, double* cost, double* time);
+/* rrt.goalIndex() (robosoccer_visual.hpp:19): the goal node found by the last krrt_grow, -1 when there is none    */
+int krrt_goal_index(krrt_ctx* ctx, int* goal_index);
 /* tree.trajectories (robosoccer_visual.hpp:18): for every node i the stored edge parent[i] -> i as S rows
- * (x,y,vx,vy,t), h = k/(S-1); node 0 gives S copies of the root.  rows: cap_nodes x S x 5 doubles         */
+ * (x,y,vx,vy,t), h = k/(S-1); node 0 gives S copies of the root.  rows: cap_nodes x S x 5 doubles; with cap_nodes >
+ * tree size the connected goal node's edge follows the tree's                                                  */
 int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes);
 /* root -> idx chain; states cap x 4, times cap; *len = true chain length                        */
 int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len);

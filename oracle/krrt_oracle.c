@@ -302,7 +302,7 @@ void ko_default_config(ko_config* c) {
   c->lo[0] = -9.0; c->hi[0] = 9.0; c->lo[1] = -6.0; c->hi[1] = 6.0;
   c->lo[2] = -2.0; c->hi[2] = 2.0; c->lo[3] = -2.0; c->hi[3] = 2.0;
   c->gamma = 7.0; c->rho_max = 4.0; c->p_direct = 0.0; c->goal_tol = 0.0;
-  c->seed = 0; c->query_id = 0; c->use_kdtree = 1;
+  c->seed = 0; c->query_id = 0; c->use_kdtree = 1; c->goal_mode = KO_GOAL_CONNECT;
 }
 
 /* ------------------------------------------------------------------ */
@@ -332,7 +332,10 @@ struct ko_planner {
   double* stack_d;
   double last_sample[4];
   ko_stats st;
+  void* gsort; /* connect_goal: (cost through node, node) pairs */
 };
+
+typedef struct { double c; int32_t i; } ko_gcand;
 
 static inline double d2_4(const double* a, const double* b) {
   double d0 = a[0] - b[0], d1 = a[1] - b[1], d2 = a[2] - b[2], d3 = a[3] - b[3];
@@ -342,7 +345,7 @@ static inline double d2_4(const double* a, const double* b) {
 ko_planner* ko_create(const ko_config* c) {
   ko_planner* p = (ko_planner*)calloc(1, sizeof(ko_planner));
   p->cfg = *c;
-  int cap = c->capacity;
+  int cap = c->capacity + 1; /* + the goal node's slot right behind the last tree node (connect_goal) */
   p->state = (double*)malloc(sizeof(double) * 4 * cap);
   p->parent = (int32_t*)malloc(sizeof(int32_t) * cap);
   p->ctc = (double*)malloc(sizeof(double) * cap);
@@ -357,6 +360,7 @@ ko_planner* ko_create(const ko_config* c) {
   p->kdim = (uint8_t*)malloc(cap);
   p->rho2 = (double*)malloc(sizeof(double) * (cap + 1));
   for (int n = 0; n <= cap; ++n) p->rho2[n] = ko_rho2(c, n);
+  p->gsort = malloc(sizeof(ko_gcand) * cap);
   p->near_cap = cap;
   p->near = (int32_t*)malloc(sizeof(int32_t) * cap);
   p->cf = (double*)malloc(sizeof(double) * cap);
@@ -371,7 +375,7 @@ void ko_destroy(ko_planner* p) {
   if (!p) return;
   free(p->state); free(p->parent); free(p->ctc); free(p->time); free(p->ecost); free(p->etime);
   free(p->head); free(p->next); free(p->prev); free(p->kl); free(p->kr); free(p->kdim); free(p->rho2);
-  free(p->near); free(p->cf); free(p->tf); free(p->tried); free(p->stack); free(p->stack_d);
+  free(p->gsort); free(p->near); free(p->cf); free(p->tf); free(p->tried); free(p->stack); free(p->stack_d);
   free(p);
 }
 
@@ -579,6 +583,7 @@ static int grow_once(ko_planner* p, const double* xs) {
   return 1;
 }
 
+/* O8, goal_mode KO_GOAL_TOLERANCE: the goal node is the cheapest tree node within goal_tol of the goal (4-D) */
 static int find_goal(const ko_planner* p, const double* goal) {
   if (!goal) return -1;
   double tol2 = p->cfg.goal_tol * p->cfg.goal_tol;
@@ -590,6 +595,51 @@ static int find_goal(const ko_planner* p, const double* goal) {
   return best;
 }
 
+static int cmp_gcand(const void* a, const void* b) {
+  const ko_gcand *x = (const ko_gcand*)a, *y = (const ko_gcand*)b;
+  if (x->c != y->c) return x->c < y->c ? -1 : 1;
+  return (x->i > y->i) - (x->i < y->i);
+}
+
+/* O8, goal_mode KO_GOAL_CONNECT (default): the goal is CONNECTED to the tree.  Every node the planner inserted
+ * (i >= 1; the start itself is not a candidate: a direct start -> goal edge is what direct sampling is for,
+ * ...node.cpp:225-229) offers the edge i -> goal: optimal steering, cost ctc[i] + c*(i -> goal), collision-tested as
+ * any other edge, departing at the node's arrival time.  The goal's parent is the cheapest collision-free offer on the
+ * tree AS IT STANDS when grow() returns (lowest index among equal costs), so rewires that make a node cheaper make the
+ * goal cheaper, and the answer does not depend on how the iterations were split over grow() calls.  The goal node is
+ * stored right behind the last tree node (index n = ko_size): rrt.goalIndex() > 0 (robosoccer_visual.hpp:19,40-45),
+ * tree(goalIndex) is the goal state and tree.states(goalIndex) the chain root -> ... -> goal; it is not part of the
+ * tree the next grow() call searches (no near query finds it, it has no children) and is rebuilt at the end of that
+ * call.  A node that coincides with the goal (a direct sample) offers a zero-length edge and, if it wins, IS the goal
+ * node.  Returns the goal index or -1. */
+static int connect_goal(ko_planner* p, const double* goal) {
+  if (!goal) return -1;
+  const ko_config* c = &p->cfg;
+  ko_gcand* g = (ko_gcand*)p->gsort;
+  int n = p->n, k = 0;
+  for (int i = 1; i < n; ++i) {
+    const double* x = p->state + 4 * i;
+    double tg = 0.0, cg = 0.0;
+    if (d2_4(x, goal) != 0.0) ko_steer(x, goal, c->r, &tg, &cg);
+    p->tf[i] = tg; p->cf[i] = cg;
+    g[k].c = p->ctc[i] + cg; g[k].i = i; ++k;
+  }
+  qsort(g, k, sizeof(ko_gcand), cmp_gcand);
+  for (int j = 0; j < k; ++j) {
+    int i = g[j].i;
+    const double* x = p->state + 4 * i;
+    if (d2_4(x, goal) == 0.0) return i;
+    if (ko_edge_collide(x, goal, p->tf[i], p->time[i], p->obs, p->m, p->dynamic, c->R, c->S)) continue;
+    memcpy(p->state + 4 * n, goal, sizeof(double) * 4);
+    p->parent[n] = i;
+    p->ecost[n] = p->cf[i]; p->etime[n] = p->tf[i];
+    p->ctc[n] = g[j].c;
+    p->time[n] = p->time[i] + p->tf[i];
+    return n;
+  }
+  return -1;
+}
+
 int ko_grow(ko_planner* p, const double* goal, int n_iter, const double* samples, int* goal_index) {
   for (int it = 0; it < n_iter; ++it) {
     double xs[4];
@@ -598,7 +648,7 @@ int ko_grow(ko_planner* p, const double* goal, int n_iter, const double* samples
     else ko_sample(&p->cfg, (uint64_t)gi, goal, xs);
     if (grow_once(p, xs) < 0) break;
   }
-  int g = find_goal(p, goal);
+  int g = p->cfg.goal_mode == KO_GOAL_TOLERANCE ? find_goal(p, goal) : connect_goal(p, goal);
   if (goal_index) *goal_index = g;
   return g >= 0;
 }

@@ -35,6 +35,7 @@ extern "C" {
 
 #define KO_MAX_OBS 64
 #define KO_MAX_WAYPOINTS 32
+enum { KO_GOAL_CONNECT = 0, KO_GOAL_TOLERANCE = 1 };
 
 typedef struct ko_config {
   double r;            /* input weight of J = int (1 + r|u|^2) dt  (config.yaml:1 -> 0.5) */
@@ -46,10 +47,11 @@ typedef struct ko_config {
   double gamma;        /* near radius rho(n) = min(rho_max, gamma (ln n / n)^(1/4)) (O3)   */
   double rho_max;
   double p_direct;     /* probability of sampling the goal itself (O2, config.yaml:7)      */
-  double goal_tol;     /* node is a goal node iff d2(x, goal) <= goal_tol^2 (O8)           */
+  double goal_tol;     /* KO_GOAL_TOLERANCE: node is a goal node iff d2(x, goal) <= goal_tol^2 */
   uint64_t seed;       /* Philox key                                                       */
   uint32_t query_id;   /* Philox counter word 1                                            */
   int32_t use_kdtree;  /* 1: incremental kd-tree near/nearest, 0: brute force              */
+  int32_t goal_mode;   /* O8: KO_GOAL_CONNECT (default) or KO_GOAL_TOLERANCE, see connect_goal / find_goal */
 } ko_config;
 
 typedef struct ko_result {
@@ -94,7 +96,9 @@ void ko_set_obstacles(ko_planner* p, const double* xyvxvy, int m, int dynamic);
 void ko_set_start(ko_planner* p, const double x0[4]);
 void ko_set_near_radius(ko_planner* p, double gamma, double rho_max);
 /* n_iter expansions. samples: NULL or n_iter x 4 (a row whose first entry is NaN
- * means "draw internally").  returns 1 when a goal node exists at the end.      */
+ * means "draw internally").  returns 1 when a goal node exists at the end; *goal_index is its index: a tree node, or
+ * (KO_GOAL_CONNECT) ko_size(p), the goal node stored right behind the tree — ko_states / ko_parents / ko_ctc /
+ * ko_times / ko_path / ko_fill_result all accept it.                                                          */
 int ko_grow(ko_planner* p, const double* goal, int n_iter, const double* samples, int* goal_index);
 int ko_size(const ko_planner* p);
 int64_t ko_iteration(const ko_planner* p);

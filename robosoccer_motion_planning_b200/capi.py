@@ -31,7 +31,7 @@ EXPORTS = (
     "krrt_batch_stats", "krrt_launch_count", "krrt_set_profile", "krrt_last_timing", "krrt_timer_begin",
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_tail_commits", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
-    "krrt_solve_inputs", "krrt_scan_stats",
+    "krrt_solve_inputs", "krrt_scan_stats", "krrt_tree_read", "krrt_goal_index",
 )
 
 
@@ -43,7 +43,11 @@ class KrrtConfig(ctypes.Structure):
         ("gamma", ctypes.c_double), ("rho_max", ctypes.c_double), ("p_direct", ctypes.c_double),
         ("goal_tol", ctypes.c_double), ("seed", ctypes.c_uint64), ("query_id", ctypes.c_uint32),
         ("batch", ctypes.c_int32), ("near_cap", ctypes.c_int32),
+        ("goal_mode", ctypes.c_int32),
     ]
+
+
+KRRT_GOAL_CONNECT, KRRT_GOAL_TOLERANCE = 0, 1
 
 
 class KrrtStats(ctypes.Structure):
@@ -104,6 +108,8 @@ def lib():
     L.krrt_get_stats.argtypes = [P, ctypes.POINTER(KrrtStats)]
     L.krrt_batch_stats.argtypes = [P, ctypes.POINTER(KrrtStats)]
     L.krrt_tree_download.argtypes = [P, D, I, D, D]
+    L.krrt_tree_read.argtypes = [P, ctypes.c_int, ctypes.c_int, D, I, D, D]
+    L.krrt_goal_index.argtypes = [P, I]
     L.krrt_path.argtypes = [P, ctypes.c_int, D, D, ctypes.c_int, I]
     L.krrt_result_of.argtypes = [P, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
     L.krrt_trajectory.argtypes = [P, ctypes.c_int, ctypes.c_double, D, ctypes.c_int, I]
@@ -253,6 +259,23 @@ class Planner:
         tim = np.empty(n)
         self._ck(lib().krrt_tree_download(self.h, _d(states), parent.ctypes.data_as(I), _d(ctc), _d(tim)))
         return states, parent, ctc, tim
+
+    def tree_read(self, first, count):
+        """rows [first, first + count); may end with the connected goal node (index == size)"""
+        states = np.empty((count, 4))
+        parent = np.empty(count, dtype=np.int32)
+        ctc = np.empty(count)
+        tim = np.empty(count)
+        self._ck(lib().krrt_tree_read(self.h, int(first), int(count), _d(states), parent.ctypes.data_as(I), _d(ctc),
+                                      _d(tim)))
+        return states, parent, ctc, tim
+
+    # rrt.goalIndex() (robosoccer_visual.hpp:19)
+    @property
+    def goal_index(self):
+        g = ctypes.c_int32(-1)
+        self._ck(lib().krrt_goal_index(self.h, ctypes.byref(g)))
+        return g.value
 
     # tree.states(idx) (…node.cpp:237)
     def path(self, idx, cap=4096):

@@ -24,14 +24,71 @@ struct BatchJob {
   const int* list_count;
   long long* stats;         // [10] accumulated over queries
   const double* rho2;       // [cap + 1]
-  int q, m, dynamic, n_iter, cap;
+  int q, m, dynamic, n_iter, cap;  // cap: most nodes a tree can hold; the arrays have cap + 1 slots (goal node)
   uint32_t query_base;
   double r, R2, goal_tol2;
   int S;
+  int goal_mode;  // KRRT_GOAL_CONNECT / KRRT_GOAL_TOLERANCE (include/krrt.h)
   SamplerParams sp;
 };
 
+constexpr int GOAL_MODE_TOLERANCE = 1;  // == KRRT_GOAL_TOLERANCE
+
+// Goal connection at the end of a query (k_goal_connect of krrt_kernels.cuh for one warp; T in shared memory): every
+// inserted node offers node -> goal, the cheapest collision-free offer wins (lowest index among equal costs), the goal
+// node is written to slot n (all but its parent link, whose type is the caller's: goal_parent) unless a node that
+// coincides with the goal wins.  Returns the goal index or -1.
+template <typename Tree, typename LoadState>
+__device__ __noinline__ int warp_goal_connect(const Tree& T, LoadState load, int n, const State4& goal, double r,
+                                                 const EnvView& E, int& goal_parent) {
+  const int lane = threadIdx.x & 31;
+  double bc = INFINITY, btg = 0.0, bcg = 0.0;
+  int bi = -1, bsame = 0;
+  for (int b0 = 1; b0 < n; b0 += 32) {
+    const int i = b0 + lane;
+    if (i >= n) continue;
+    const State4 x = load(i);
+    const bool same = dist2(x, goal) == 0.0;
+    double tg = 0.0, cg = 0.0;
+    if (!same) steer(x, goal, r, tg, cg);
+    const double cand = T.ctc[i] + cg;
+    if (bi >= 0 && cand >= bc) continue;  // (i only grows: an equal offer loses on the index)
+    bool hit = false;
+    if (!same && E.m > 0) {
+      const Edge e = make_edge(x, goal, tg, T.tim[i]);
+      for (int k = 0; k < E.S && !hit; ++k) {
+        const double h = (E.S > 1) ? (double)k / (double)(E.S - 1) : 0.0;
+        hit = edge_point_hits_any(e, h, E.obs, E.m, E.dynamic, E.R2);
+      }
+    }
+    if (!hit) {
+      bc = cand; bi = i; btg = tg; bcg = cg; bsame = same ? 1 : 0;
+    }
+  }
+  __syncwarp();
+  // (cost, index) arg-min over the lanes; the winner's lane hands out its edge
+  double kc = bc;
+  int ki = bi, kl = lane;
+  warp_argmin(kc, ki, kl);
+  goal_parent = ki;
+  if (ki < 0) return -1;
+  const double tg = __shfl_sync(FULL, btg, kl), cg = __shfl_sync(FULL, bcg, kl);
+  const int same = __shfl_sync(FULL, bsame, kl);
+  if (same) return ki;
+  if (lane == 0) {
+    T.pos[n] = make_double2(goal.x, goal.y);
+    T.vel[n] = make_double2(goal.vx, goal.vy);
+    T.ecost[n] = cg;
+    T.etime[n] = tg;
+    T.ctc[n] = kc;
+    T.tim[n] = T.tim[ki] + tg;
+  }
+  __syncwarp();
+  return n;
+}
+
 __host__ __device__ inline size_t batch_warp_smem_bytes(int cap, int m) {
+  cap += 1;  // the goal node's slot
   size_t b = 0;
   b += (size_t)cap * 16 * 2;                        // pos, vel
   b += (size_t)(m > 0 ? m : 1) * 32;                // obstacles
@@ -45,8 +102,8 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = lane_id();
   const int warp = threadIdx.x >> 5;
-  const int cap = J.cap;
-  unsigned char* base = smem + (size_t)warp * batch_warp_smem_bytes(cap, J.m);
+  const int cap = J.cap + 1;  // array stride: the tree's cap nodes + the goal node's slot
+  unsigned char* base = smem + (size_t)warp * batch_warp_smem_bytes(J.cap, J.m);
   TreeView T;
   NearView N;
   T.pos = reinterpret_cast<double2*>(base);
@@ -66,7 +123,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
   T.queue = T.prev + cap;
   N.idx = T.queue + cap;
   N.tried = reinterpret_cast<unsigned char*>(N.idx + cap);
-  T.cap = cap;
+  T.cap = J.cap;
   EnvView E = {s_obs, J.m, J.dynamic, J.R2, J.S};
   Stats st = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 
@@ -101,7 +158,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
         st.fail_reject++;
         continue;
       }
-      if (n >= cap) break;
+      if (n >= J.cap) break;
       const double rho2n = J.rho2[n];
       // near set (ascending by construction) + nearest + duplicate detection
       int K = 0;
@@ -157,7 +214,15 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       __syncwarp();
     }
     // result record
-    const int gi = warp_find_goal(T, n, goal, J.goal_tol2);
+    int gi;
+    if (J.goal_mode == GOAL_MODE_TOLERANCE) {
+      gi = warp_find_goal(T, n, goal, J.goal_tol2);
+    } else {
+      int gpar = -1;
+      gi = warp_goal_connect(T, [&](int i) { return load_state(T, i); }, n, goal, J.r, E, gpar);
+      if (gi == n && lane == 0) T.parent[n] = gpar;
+      __syncwarp();
+    }
     ResultRec* R = J.out + qi;
     double* wp = &R->waypoints[0][0];
     for (int k = lane; k < 32 * 5; k += 32) wp[k] = 0.0;
@@ -167,7 +232,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       R->goal_index = gi;
       R->n_nodes = n;
       int len = 0;
-      for (int i = gi; i >= 0 && len < n; i = T.parent[i]) ++len;
+      for (int i = gi; i >= 0 && len <= n; i = T.parent[i]) ++len;
       R->path_len = len;
       R->cost = gi >= 0 ? T.ctc[gi] : 0.0;
       R->time = gi >= 0 ? T.tim[gi] : 0.0;

@@ -48,6 +48,7 @@ struct B2Tree {
 };
 
 __host__ __device__ inline size_t batch2_warp_smem_bytes(int cap, int m) {
+  cap += 1;  // the goal node's slot
   size_t b = 0;
   b += (size_t)cap * 16 * 2;                            // pos, vel
   b += (size_t)cap * 8 * 4;                             // ctc, tim, ecost, etime
@@ -187,9 +188,9 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const int cap = J.cap;
+  const int cap = J.cap + 1;  // array stride: the tree's J.cap nodes + the goal node's slot
   const size_t cap8 = ((size_t)cap + 7) / 8 * 8;
-  unsigned char* base = smem + (size_t)warp * batch2_warp_smem_bytes(cap, J.m);
+  unsigned char* base = smem + (size_t)warp * batch2_warp_smem_bytes(J.cap, J.m);
   B2Tree T;
   T.pos = reinterpret_cast<double2*>(base);
   T.vel = T.pos + cap;
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
   T.parent = T.sib + cap8;
   T.prev = T.parent + cap8;
   T.scr = T.prev + cap8;
-  T.cap = cap;
+  T.cap = J.cap;
   const EnvView E = {s_obs, J.m, J.dynamic, J.R2, J.S};
   const B2Lanes L = b2_lanes(J.S, J.m);
   const unsigned lt_mask = (1u << lane) - 1;
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
           c_rej++;
           continue;
         }
-        if (n >= cap) {
+        if (n >= J.cap) {
           full = true;
           break;
         }
@@ -422,25 +423,33 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       __syncwarp();
       continue;
     }
-    // goal node = cheapest node within goal_tol of the goal, lowest index on ties (warp_find_goal)
+    // goal node: connected to the cheapest collision-free offer of the tree (default), or the cheapest node within
+    // goal_tol of the goal (warp_find_goal); lowest index on ties
     int gi;
     {
       const double* gs = J.goals + 4 * (size_t)qi;
       const State4 goal = {gs[0], gs[1], gs[2], gs[3]};
-      double bc = INFINITY;
-      int bn = -1;
-      for (int i = lane; i < n; i += 32) {
-        if (dist2(b2_state(T, i), goal) <= J.goal_tol2) {
-          const double c = T.ctc[i];
-          if (c < bc) {
-            bc = c;
-            bn = i;
+      if (J.goal_mode == GOAL_MODE_TOLERANCE) {
+        double bc = INFINITY;
+        int bn = -1;
+        for (int i = lane; i < n; i += 32) {
+          if (dist2(b2_state(T, i), goal) <= J.goal_tol2) {
+            const double c = T.ctc[i];
+            if (c < bc) {
+              bc = c;
+              bn = i;
+            }
           }
         }
+        int owner;
+        const unsigned w = b2_argmin(bn >= 0, bc, (unsigned)bn, owner);
+        gi = w == 0xffffffffu ? -1 : (int)w;
+      } else {
+        int gpar = -1;
+        gi = warp_goal_connect(T, [&](int i) { return b2_state(T, i); }, n, goal, J.r, E, gpar);
+        if (gi == n && lane == 0) T.parent[n] = (unsigned short)gpar;
+        __syncwarp();
       }
-      int owner;
-      const unsigned w = b2_argmin(bn >= 0, bc, (unsigned)bn, owner);
-      gi = w == 0xffffffffu ? -1 : (int)w;
     }
     ResultRec* R = J.out + qi;
     double* wp = &R->waypoints[0][0];
@@ -451,7 +460,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       R->goal_index = gi;
       R->n_nodes = n;
       int len = 0;
-      for (int i = gi; i >= 0 && len < n; i = (T.parent[i] == B2_NIL ? -1 : (int)T.parent[i])) ++len;
+      for (int i = gi; i >= 0 && len <= n; i = (T.parent[i] == B2_NIL ? -1 : (int)T.parent[i])) ++len;
       R->path_len = len;
       R->cost = gi >= 0 ? T.ctc[gi] : 0.0;
       R->time = gi >= 0 ? T.tim[gi] : 0.0;

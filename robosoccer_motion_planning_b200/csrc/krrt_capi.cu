@@ -49,6 +49,7 @@ struct krrt_ctx {
   int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
   GridBar* d_bar = nullptr;    // its two grid barriers
   GridIndex gi{};              // spatial index of its neighbour scan
+  GoalScratch goal_scr{};      // partials of k_goal_connect
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
@@ -65,7 +66,8 @@ struct krrt_ctx {
   Ctl* h_ctl = nullptr;       // pinned host copy of the control block ...
   bool ctl_valid = false;     // ... current until the next call that changes the tree (krrt_set_start, krrt_grow)
   int batch_v1 = 0;           // KRRT_BATCH_V1=1 in the environment: the shared-memory-list kernel only (A-B timing)
-  int rho2_batch_cap = -1;
+  int rho2_batch_cap = -1, rho2_batch_alloc = 0;
+  std::vector<double> h_rho2_batch;
   int* d_counter = nullptr;
   long long* d_batch_stats = nullptr;
 
@@ -148,6 +150,7 @@ void krrt_default_config(krrt_config* c) {
   c->query_id = 0;
   c->batch = 0;
   c->near_cap = 0;
+  c->goal_mode = KRRT_GOAL_CONNECT;
 }
 
 int krrt_device_count(void) {
@@ -185,6 +188,7 @@ static int create_impl(krrt_ctx* ctx) {
   REQUIRE(c.capacity >= 2 && c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad capacity / S / r / R");
   REQUIRE(c.batch >= 1 && c.batch <= GROW_WMAX, KRRT_ERR_INVALID, "batch must be in [1,1024]");
   REQUIRE(c.near_cap >= 32 && c.near_cap <= 4096, KRRT_ERR_INVALID, "near_cap must be in [32,4096]");
+  REQUIRE(c.goal_mode == KRRT_GOAL_CONNECT || c.goal_mode == KRRT_GOAL_TOLERANCE, KRRT_ERR_INVALID, "bad goal_mode");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0 || c.device < 0 || c.device >= ndev) {
@@ -208,7 +212,7 @@ static int create_impl(krrt_ctx* ctx) {
     const size_t bcn = (size_t)c.batch * c.near_cap;
     size_t need = cap * (16 * 2 + 8 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (16 * 2 + 4 * 2) + cap * 8 + (GRID_CELLS_MAX + 1) * 4 +
                   (cap + 1) * 8 + bcn * (4 + 8 * 5) + (size_t)1024 * GROW_QCAP * 8 + 2 * 1024 * 4 + 512 +
-                  (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + (64 << 10);
+                  (size_t)c.batch * (32 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + GOAL_MAX_CTAS * 12 + (64 << 10);
 #ifdef KRRT_DEBUG_CLK
     need += (size_t)32 * ((1 << 20) + 1) + 4096;
 #endif
@@ -216,13 +220,13 @@ static int create_impl(krrt_ctx* ctx) {
     ctx->arena_bytes = need;
     ctx->arena_used = 0;
   }
-  CK(dev_alloc(ctx, &ctx->T.pos, cap));
-  CK(dev_alloc(ctx, &ctx->T.vel, cap));
-  CK(dev_alloc(ctx, &ctx->T.ctc, cap));
-  CK(dev_alloc(ctx, &ctx->T.tim, cap));
-  CK(dev_alloc(ctx, &ctx->T.ecost, cap));
-  CK(dev_alloc(ctx, &ctx->T.etime, cap));
-  CK(dev_alloc(ctx, &ctx->T.parent, cap));
+  CK(dev_alloc(ctx, &ctx->T.pos, cap + 1));  // + the goal node's slot (k_goal_connect)
+  CK(dev_alloc(ctx, &ctx->T.vel, cap + 1));
+  CK(dev_alloc(ctx, &ctx->T.ctc, cap + 1));
+  CK(dev_alloc(ctx, &ctx->T.tim, cap + 1));
+  CK(dev_alloc(ctx, &ctx->T.ecost, cap + 1));
+  CK(dev_alloc(ctx, &ctx->T.etime, cap + 1));
+  CK(dev_alloc(ctx, &ctx->T.parent, cap + 1));
   CK(dev_alloc(ctx, &ctx->T.link, cap));
   CK(dev_alloc(ctx, &ctx->T.prev, cap));
   CK(dev_alloc(ctx, &ctx->T.queue, cap));
@@ -232,6 +236,10 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &ctx->d_ctl, (size_t)1));
   CK(dev_alloc(ctx, &ctx->d_counter, (size_t)1));
   CK(dev_alloc(ctx, &ctx->d_batch_stats, (size_t)10));
+  CK(dev_alloc(ctx, &ctx->goal_scr.part_c, (size_t)GOAL_MAX_CTAS));
+  CK(dev_alloc(ctx, &ctx->goal_scr.part_i, (size_t)GOAL_MAX_CTAS));
+  CK(dev_alloc(ctx, &ctx->goal_scr.ticket, (size_t)1));
+  CK(cudaMemsetAsync(ctx->goal_scr.ticket, 0, sizeof(unsigned), ctx->stream));
   CK(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
   CK(cudaMemsetAsync(ctx->d_obs, 0, sizeof(double4) * KRRT_MAX_OBS, ctx->stream));
   {
@@ -315,6 +323,7 @@ static int create_impl(krrt_ctx* ctx) {
   P.m = 0;
   P.dynamic = 0;
   P.goal_tol2 = c.goal_tol * c.goal_tol;
+  P.goal_mode = c.goal_mode;
   P.rho2 = ctx->d_rho2;
   P.obs = ctx->d_obs;
   return KRRT_OK;
@@ -518,7 +527,14 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
     }
     // the goal lookup and the end-of-call event follow at once: ONE read-back per launch (when the kernel came back early
     // to have its conflict marks cleared, the lookup and the event are simply repeated after the next launch)
-    k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
+    if (ctx->P.goal_mode == KRRT_GOAL_TOLERANCE) {
+      k_find_goal<<<1, 1024, 0, st>>>(ctx->d_ctl, ctx->T, ctx->P.goal_tol2);
+    } else {
+      const long long n_max = (long long)ctx->n_upper + n_iter;
+      const int ctas = (int)std::max<long long>(1, std::min<long long>(std::min(GOAL_MAX_CTAS, 4 * ctx->prop.multiProcessorCount),
+                                                                       (n_max + GOAL_THREADS - 1) / GOAL_THREADS));
+      k_goal_connect<<<ctas, GOAL_THREADS, 0, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->goal_scr);
+    }
     CK(cudaEventRecord(ctx->ev1, st));
     ctx->launches += 3;
     CK(cudaGetLastError());

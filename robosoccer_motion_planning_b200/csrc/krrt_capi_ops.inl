@@ -1,11 +1,13 @@
 // krrt_capi_ops.inl — tree read-back, stateless operators and the batched planner entry points of include/krrt.h.
 // Included at the end of krrt_capi.cu (same translation unit, same -fmad=false arithmetic contract).
 
-static int current_size(krrt_ctx* ctx, int* n) {
+static int current_size(krrt_ctx* ctx, int* n, int* n_with_goal = nullptr) {
   Ctl h;
   int rc = fetch_ctl(ctx, &h);
   if (rc != KRRT_OK) return rc;
   *n = h.n;
+  // the goal node of KRRT_GOAL_CONNECT sits right behind the tree (slot n): the index-taking getters accept it
+  if (n_with_goal) *n_with_goal = h.n + (h.goal_index == h.n ? 1 : 0);
   return KRRT_OK;
 }
 
@@ -31,15 +33,48 @@ int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* c
   return KRRT_OK;
 }
 
+int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t* parent, double* cost, double* time) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  int n = 0, ng = 0;
+  int rc = current_size(ctx, &n, &ng);
+  if (rc != KRRT_OK) return rc;
+  REQUIRE(first >= 0 && count >= 0 && first + count <= ng, KRRT_ERR_INVALID, "node range out of bounds");
+  if (count == 0) return KRRT_OK;
+  cudaStream_t st = ctx->stream;
+  if (states) {
+    CK(cudaMemcpy2DAsync(states, 32, ctx->T.pos + first, 16, 16, count, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(states + 2, 32, ctx->T.vel + first, 16, 16, count, cudaMemcpyDeviceToHost, st));
+  }
+  if (parent) CK(cudaMemcpyAsync(parent, ctx->T.parent + first, sizeof(int) * count, cudaMemcpyDeviceToHost, st));
+  if (cost) CK(cudaMemcpyAsync(cost, ctx->T.ctc + first, sizeof(double) * count, cudaMemcpyDeviceToHost, st));
+  if (time) CK(cudaMemcpyAsync(time, ctx->T.tim + first, sizeof(double) * count, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return KRRT_OK;
+}
+
+int krrt_goal_index(krrt_ctx* ctx, int* goal_index) {
+  if (!ctx || !goal_index) return KRRT_ERR_INVALID;
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  CK(cudaSetDevice(ctx->cfg.device));
+  Ctl h;
+  int rc = fetch_ctl(ctx, &h);
+  if (rc != KRRT_OK) return rc;
+  *goal_index = h.goal_index;
+  return KRRT_OK;
+}
+
 int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len) {
   if (!ctx || !len) return KRRT_ERR_INVALID;
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(cap >= 0, KRRT_ERR_INVALID, "cap < 0");
   CK(cudaSetDevice(ctx->cfg.device));
-  int n = 0;
-  int rc = current_size(ctx, &n);
+  int n = 0, ng = 0;
+  int rc = current_size(ctx, &n, &ng);
   if (rc != KRRT_OK) return rc;
-  REQUIRE(idx >= 0 && idx < n, KRRT_ERR_INVALID, "node index out of range");
+  REQUIRE(idx >= 0 && idx < ng, KRRT_ERR_INVALID, "node index out of range");
+  n = ng;
   cudaStream_t st = ctx->stream;
   const size_t c = (size_t)std::max(cap, 1);
   if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 4 * c)) != KRRT_OK) return rc;
@@ -131,10 +166,11 @@ int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_row
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   CK(cudaSetDevice(ctx->cfg.device));
-  int n = 0;
-  int rc = current_size(ctx, &n);
+  int n = 0, ng = 0;
+  int rc = current_size(ctx, &n, &ng);
   if (rc != KRRT_OK) return rc;
-  REQUIRE(idx >= 0 && idx < n, KRRT_ERR_INVALID, "node index out of range");
+  REQUIRE(idx >= 0 && idx < ng, KRRT_ERR_INVALID, "node index out of range");
+  n = ng;
   cudaStream_t st = ctx->stream;
   if ((rc = ensure_scratch(ctx, 0, sizeof(double) * 4 * (size_t)n)) != KRRT_OK) return rc;
   if ((rc = ensure_scratch(ctx, 1, sizeof(double) * (size_t)n)) != KRRT_OK) return rc;
@@ -270,20 +306,42 @@ int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, in
 }
 
 // ---- batched independent queries ---------------------------------------------------------------------
+// One batched plan may be in flight per context (work counter, counters and redo list are per-context scratch); the
+// near-radius table and the redo list are (re)built on the caller's stream, so the call stays asynchronous once the
+// buffers have reached their size (they only grow: the first call of a given q / n_iter allocates).
 static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double* d_goals, const double* d_obs, int q,
                              int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* d_out,
-                             cudaStream_t st) {
+                             cudaStream_t st, bool* redo_unserved = nullptr) {
   const krrt_config& c = ctx->cfg;
-  const int cap = std::min(c.capacity, n_iter + 2);
+  const int cap = std::min(c.capacity, n_iter + 1);  // root + one node per iteration at most (+ the goal node's slot)
   REQUIRE(cap >= 2, KRRT_ERR_INVALID, "n_iter / capacity too small");
+  const size_t smem_max = ctx->prop.sharedMemPerBlockOptin;            // 227 KB on sm_100
+  const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
+  // what fits: k_plan_batch2 (near lists in registers, 16-bit links) and its redo pass k_plan_batch (everything in shared
+  // memory, 121 B per node against 74).  Decided BEFORE anything is launched.
+  const size_t pw2 = batch2_warp_smem_bytes(cap, m);
+  const int w2 = (int)std::min<size_t>(B2_MAX_WARPS, (smem_max - 1024) / pw2);
+  const bool use_v2 = !ctx->batch_v1 && cap <= 65533 && w2 >= 1;
+  const size_t pw = batch_warp_smem_bytes(cap, m);
+  const bool v1_fits = pw <= smem_max;
+  REQUIRE(use_v2 || v1_fits, KRRT_ERR_UNSUPPORTED,
+          "n_iter too large for the shared-memory batched planner; use krrt_grow per query");
+  // trees too big for the redo pass: k_plan_batch2 alone, and the caller has to look at the redo count afterwards
+  REQUIRE(v1_fits || redo_unserved, KRRT_ERR_UNSUPPORTED,
+          "n_iter too large for the redo pass of the batched planner on a caller-owned stream; use krrt_plan_batch");
+  if (redo_unserved) *redo_unserved = !v1_fits;
   if (ctx->rho2_batch_cap != cap) {
-    if (ctx->d_rho2_batch) CK(cudaFree(ctx->d_rho2_batch));
-    ctx->d_rho2_batch = nullptr;
-    ctx->rho2_batch_cap = -1;
-    CK(cudaMalloc((void**)&ctx->d_rho2_batch, sizeof(double) * (cap + 1)));
-    std::vector<double> rho2(cap + 1);
-    for (int n = 0; n <= cap; ++n) rho2[n] = near_radius2(c, n);
-    CK(cudaMemcpy(ctx->d_rho2_batch, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice));
+    if (ctx->rho2_batch_alloc < cap + 1) {
+      if (ctx->d_rho2_batch) CK(cudaFree(ctx->d_rho2_batch));
+      ctx->d_rho2_batch = nullptr;
+      ctx->rho2_batch_alloc = 0;
+      ctx->rho2_batch_cap = -1;
+      CK(cudaMalloc((void**)&ctx->d_rho2_batch, sizeof(double) * (cap + 1)));
+      ctx->rho2_batch_alloc = cap + 1;
+    }
+    ctx->h_rho2_batch.resize(cap + 1);  // (owned by the context: the copy below is asynchronous)
+    for (int n = 0; n <= cap; ++n) ctx->h_rho2_batch[n] = near_radius2(c, n);
+    CK(cudaMemcpyAsync(ctx->d_rho2_batch, ctx->h_rho2_batch.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice, st));
     ctx->rho2_batch_cap = cap;
   }
   BatchJob J;
@@ -296,18 +354,14 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
   J.q = q; J.m = m; J.dynamic = dynamic ? 1 : 0; J.n_iter = n_iter; J.cap = cap;
   J.query_base = query_base;
   J.r = c.r; J.R2 = c.R * c.R; J.goal_tol2 = c.goal_tol * c.goal_tol; J.S = c.S;
+  J.goal_mode = c.goal_mode;
   for (int k = 0; k < 4; ++k) { J.sp.lo[k] = c.lo[k]; J.sp.hi[k] = c.hi[k]; }
   J.sp.p_direct = c.p_direct;
   J.sp.seed = c.seed;
-  const size_t smem_max = ctx->prop.sharedMemPerBlockOptin;            // 227 KB on sm_100
-  const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
   CK(cudaMemsetAsync(ctx->d_counter, 0, sizeof(int), st));
   CK(cudaMemsetAsync(ctx->d_batch_stats, 0, sizeof(long long) * 10, st));
 
   // ---- k_plan_batch2: near lists in registers, 16-bit links, one CTA of up to 16 warps per SM
-  const size_t pw2 = batch2_warp_smem_bytes(cap, m);
-  const int w2 = (int)std::min<size_t>(B2_MAX_WARPS, (smem_max - 1024) / pw2);
-  const bool use_v2 = !ctx->batch_v1 && cap <= 65534 && w2 >= 1;
   if (use_v2) {
     if (ctx->redo_cap < (size_t)q + 2) {
       if (ctx->d_redo) CK(cudaFree(ctx->d_redo));
@@ -332,12 +386,10 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
     J.next_query = ctx->d_redo;
     J.list = ctx->d_redo + 2;
     J.list_count = ctx->d_redo + 1;
+    if (!v1_fits) return KRRT_OK;
   }
 
   // ---- k_plan_batch: every list in shared memory (the whole batch, or k_plan_batch2's redo list)
-  const size_t pw = batch_warp_smem_bytes(cap, m);
-  REQUIRE(pw <= smem_max, KRRT_ERR_UNSUPPORTED,
-          "n_iter too large for the shared-memory batched planner; use krrt_grow per query");
   int best_w = 1, best_total = 0, best_ctas = 1;
   for (int w = 1; w <= 8; ++w) {
     size_t per_cta = (size_t)w * pw;
@@ -393,13 +445,20 @@ int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, co
   CK(cudaMemcpyAsync(ctx->d_scratch[0], starts, sb, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(ctx->d_scratch[1], goals, sb, cudaMemcpyHostToDevice, st));
   if (m > 0) CK(cudaMemcpyAsync(ctx->d_scratch[6], obstacles, sizeof(double) * 4 * (size_t)q * m, cudaMemcpyHostToDevice, st));
+  bool redo_unserved = false;
   rc = launch_plan_batch(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1],
                          (const double*)ctx->d_scratch[6], q, m, dynamic, n_iter, query_base,
-                         (krrt_result*)ctx->d_scratch[7], st);
+                         (krrt_result*)ctx->d_scratch[7], st, &redo_unserved);
   if (rc != KRRT_OK) return rc;
   CK(cudaMemcpyAsync(out, ctx->d_scratch[7], rb, cudaMemcpyDeviceToHost, st));
   CK(cudaEventRecord(ctx->ev1, st));
   CK(cudaStreamSynchronize(st));
+  if (redo_unserved) {  // trees too big for the redo pass: fine as long as no query needed it
+    int redo = 0;
+    CK(cudaMemcpy(&redo, ctx->d_redo + 1, sizeof(int), cudaMemcpyDeviceToHost));
+    REQUIRE(redo == 0, KRRT_ERR_NEAR_OVERFLOW,
+            "a near set outgrew k_plan_batch2's 64 candidates and n_iter is too large for its redo pass; use krrt_grow per query");
+  }
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->last_total_ms = ms;
@@ -423,6 +482,7 @@ int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
               c.batch == ctx->cfg.batch && c.near_cap == ctx->cfg.near_cap,
           KRRT_ERR_INVALID, "device / precision / capacity / batch / near_cap are create-time fields");
   REQUIRE(c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad S / r / R");
+  REQUIRE(c.goal_mode == KRRT_GOAL_CONNECT || c.goal_mode == KRRT_GOAL_TOLERANCE, KRRT_ERR_INVALID, "bad goal_mode");
   CK(cudaSetDevice(c.device));
   if (c.gamma != ctx->cfg.gamma || c.rho_max != ctx->cfg.rho_max) {
     const size_t cap = (size_t)c.capacity;
@@ -445,6 +505,7 @@ int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
   P.sp.seed = c.seed;
   P.query_id = c.query_id;
   P.goal_tol2 = c.goal_tol * c.goal_tol;
+  P.goal_mode = c.goal_mode;
   return KRRT_OK;
 }
 
@@ -481,10 +542,10 @@ int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes) {
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(S >= 1 && cap_nodes >= 0, KRRT_ERR_INVALID, "S < 1 / cap_nodes < 0");
   CK(cudaSetDevice(ctx->cfg.device));
-  int n = 0;
-  int rc = current_size(ctx, &n);
+  int n = 0, ng = 0;
+  int rc = current_size(ctx, &n, &ng);
   if (rc != KRRT_OK) return rc;
-  n = std::min(n, cap_nodes);
+  n = std::min(ng, cap_nodes);  // (cap_nodes > tree size: the goal node's edge follows the tree's)
   if (n == 0) return KRRT_OK;
   cudaStream_t st = ctx->stream;
   const size_t rb = sizeof(double) * 5 * (size_t)n * S;

@@ -67,6 +67,7 @@ struct Params {
   int m;
   int dynamic;
   double goal_tol2;
+  int goal_mode;       // KRRT_GOAL_CONNECT / KRRT_GOAL_TOLERANCE (include/krrt.h)
   const double* rho2;  // [capacity + 1], host-computed table of squared near radii
   const double4* obs;
 };
@@ -148,7 +149,8 @@ __host__ __device__ inline size_t commit_smem_bytes(int near_cap) {
   return sizeof(double4) * KRRT_MAX_OBS_DEV + (size_t)near_cap * (4 * 8 + 4 + 1) + 16;
 }
 
-// goal lookup after a grow call: cheapest node within goal_tol of the goal (rrt.goalIndex(), robosoccer_visual.hpp:19)
+// goal lookup after a grow call, goal_mode KRRT_GOAL_TOLERANCE: cheapest node within goal_tol of the goal
+// (rrt.goalIndex(), robosoccer_visual.hpp:19)
 __global__ void __launch_bounds__(1024) k_find_goal(Ctl* ctl, TreeView T, double tol2) {
   __shared__ double s_c[32];
   __shared__ int s_i[32];
@@ -180,6 +182,114 @@ __global__ void __launch_bounds__(1024) k_find_goal(Ctl* ctl, TreeView T, double
     bi = s_i[threadIdx.x];
     warp_argmin(bc, bi, aux);
     if (threadIdx.x == 0) ctl->goal_index = bi;
+  }
+}
+
+// Goal connection after a grow call, goal_mode KRRT_GOAL_CONNECT (default; the `solved` of rrt.grow(xg),
+// robosoccer_motion_planning_node.cpp:177, and rrt.goalIndex(), robosoccer_visual.hpp:19,40-45).  Every node the planner
+// inserted (i >= 1) offers the edge i -> goal: optimal steering, cost ctc[i] + c*(i -> goal), collision-tested as any
+// other edge, departing at the node's arrival time.  The goal's parent is the cheapest collision-free offer on the tree
+// as it stands (lowest index among equal costs); a node that coincides with the goal offers a zero-length edge and, if it
+// wins, IS the goal node.  Otherwise the goal node is written right behind the last tree node (slot n: the arrays hold
+// capacity + 1 entries): path / edge / trajectory extraction take its index like any other, the next grow call does not
+// see it (no scan reaches slot n, it is in no child list) and overwrites it.
+// One thread per node; a thread skips the collision test of an offer that cannot beat the best free one it has seen.
+constexpr int GOAL_THREADS = 256;
+constexpr int GOAL_MAX_CTAS = 1024;
+struct GoalScratch {
+  double* part_c;    // [GOAL_MAX_CTAS] per-CTA best offer ...
+  int* part_i;       // ... and the node that makes it (-1: none)
+  unsigned* ticket;  // CTAs done (the last one folds the partials; re-armed for the next launch)
+};
+
+__global__ void __launch_bounds__(GOAL_THREADS) k_goal_connect(Ctl* ctl, Params P, TreeView T, GoalScratch Gs) {
+  __shared__ double4 s_obs[KRRT_MAX_OBS_DEV];
+  __shared__ double s_c[GOAL_THREADS / 32];
+  __shared__ int s_i[GOAL_THREADS / 32];
+  __shared__ int s_last;
+  const int t = threadIdx.x;
+  if (!ctl->has_goal) {
+    if (t == 0 && blockIdx.x == 0) ctl->goal_index = -1;
+    return;
+  }
+  const int n = ctl->n;
+  const State4 g = {ctl->goal[0], ctl->goal[1], ctl->goal[2], ctl->goal[3]};
+  for (int j = t; j < P.m; j += GOAL_THREADS) s_obs[j] = P.obs[j];
+  __syncthreads();
+  double bc = INFINITY;
+  int bi = -1, aux = 0;
+  for (int i = 1 + blockIdx.x * GOAL_THREADS + t; i < n; i += gridDim.x * GOAL_THREADS) {
+    const State4 x = load_state(T, i);
+    const bool same = dist2(x, g) == 0.0;
+    double tg = 0.0, cg = 0.0;
+    if (!same) steer(x, g, P.r, tg, cg);
+    const double cand = T.ctc[i] + cg;
+    if (bi >= 0 && cand >= bc) continue;  // (i only grows: an equal offer loses on the index)
+    bool hit = false;
+    if (!same && P.m > 0) {
+      const Edge e = make_edge(x, g, tg, T.tim[i]);
+      for (int k = 0; k < P.S && !hit; ++k) {
+        const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : 0.0;
+        hit = edge_point_hits_any(e, h, s_obs, P.m, P.dynamic, P.R2);
+      }
+    }
+    if (!hit) {
+      bc = cand;
+      bi = i;
+    }
+  }
+  warp_argmin(bc, bi, aux);
+  if ((t & 31) == 0) {
+    s_c[t >> 5] = bc;
+    s_i[t >> 5] = bi;
+  }
+  __syncthreads();
+  if (t < 32) {
+    bc = t < GOAL_THREADS / 32 ? s_c[t] : INFINITY;
+    bi = t < GOAL_THREADS / 32 ? s_i[t] : -1;
+    warp_argmin(bc, bi, aux);
+    if (t == 0) {
+      Gs.part_c[blockIdx.x] = bc;
+      Gs.part_i[blockIdx.x] = bi;
+      __threadfence();
+      s_last = atomicAdd(Gs.ticket, 1u) == gridDim.x - 1;
+    }
+  }
+  __syncthreads();
+  if (!s_last || t >= 32) return;
+  __threadfence();
+  bc = INFINITY;
+  bi = -1;
+  for (int k = t; k < (int)gridDim.x; k += 32) {
+    const double c = __ldcg(&Gs.part_c[k]);
+    const int ci = __ldcg(&Gs.part_i[k]);
+    if (ci >= 0 && (bi < 0 || c < bc || (c == bc && ci < bi))) {
+      bc = c;
+      bi = ci;
+    }
+  }
+  warp_argmin(bc, bi, aux);
+  if (t == 0) {
+    *Gs.ticket = 0u;
+    int gi = -1;
+    if (bi >= 0) {
+      const State4 x = load_state(T, bi);
+      if (dist2(x, g) == 0.0) {
+        gi = bi;
+      } else {
+        double tg, cg;
+        steer(x, g, P.r, tg, cg);
+        gi = n;
+        T.pos[n] = make_double2(g.x, g.y);
+        T.vel[n] = make_double2(g.vx, g.vy);
+        T.parent[n] = bi;
+        T.ecost[n] = cg;
+        T.etime[n] = tg;
+        T.ctc[n] = T.ctc[bi] + cg;
+        T.tim[n] = T.tim[bi] + tg;
+      }
+    }
+    ctl->goal_index = gi;
   }
 }
 

@@ -107,7 +107,7 @@ __global__ void k_path_extract(TreeView T, int n, int idx, double* states, doubl
     return;
   }
   int len = 0;
-  for (int i = idx; i >= 0 && len < n; i = T.parent[i]) ++len;
+  for (int i = idx; i >= 0 && len < n; i = T.parent[i]) ++len;  // (n counts the goal node's slot when idx is the goal)
   int p = len - 1;
   for (int i = idx; i >= 0 && p >= 0; i = T.parent[i], --p) {
     if (p < cap) {

@@ -39,7 +39,6 @@ int main(int argc, char** argv) {
     env.collision_radius = 1.35;   // config/config.yaml:5
     solver.set_weight(0.5);        // config/config.yaml:1
     tree.capacity = 256;
-    goal.goal_tol = 0.5;
     const double sp[9][2] = {{-2, 1}, {-2, -1}, {-5, 2}, {-5, -2}, {8.5, 0}, {2, 1}, {2, -1}, {5, 2}, {5, -2}};
     std::vector<ObState> obstacles(9);
     for (int j = 0; j < 9; ++j) obstacles[j] = ObState{{sp[j][0], sp[j][1], 0.0, 0.0}};
@@ -51,7 +50,7 @@ int main(int argc, char** argv) {
 
     const int sizes[] = {10, 25, 50, 75, 100, 150, 200};
     const double probs[] = {0.0, 0.1, 0.25, 0.5};
-    std::printf("# rrtstar_custom_benchmark: %d trials per point, scene C1 (9 static robots), goal region 0.5\n", trials);
+    std::printf("# rrtstar_custom_benchmark: %d trials per point, scene C1 (9 static robots), goal connected (O8)\n", trials);
     std::printf("# %-10s %-9s %10s %10s %10s %8s %10s %10s %10s\n", "p_direct", "node_size", "t_min_ms", "t_mean_ms",
                 "t_max_ms", "solved", "cost_min", "cost_mean", "cost_max");
     for (double p : probs) {

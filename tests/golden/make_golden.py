@@ -34,10 +34,12 @@ solved, gi = P.grow(scenes.GOAL, 1500)
 st, par, ctc, tim = P.tree()
 np.savez_compressed(os.path.join(HERE, "tree_c2_small.npz"), capacity=2048, p_direct=0.1, obs=obs, start=scenes.START,
                     goal=scenes.GOAL, n_iter=1500, states=st, parent=par, ctc=ctc, time=tim, solved=solved,
-                    goal_index=gi)
+                    goal_index=gi, result=np.frombuffer(P.result(solved, gi).tobytes(), dtype=np.uint8))
 
 starts, goals, bobs = scenes.batch_queries(24, 9, seed=7)
 out = ob.plan_batch(ob.default_config(p_direct=0.1, seed=5), starts, goals, bobs, 1, 120, query_base=500, nthreads=2)
+tol = ob.plan_batch(ob.default_config(p_direct=0.1, seed=5, goal_mode=1), starts, goals, bobs, 1, 120, query_base=500,
+                    nthreads=2)
 np.savez_compressed(os.path.join(HERE, "batch_small.npz"), starts=starts, goals=goals, obs=bobs, n_iter=120,
-                    query_base=500, results=out.view(np.uint8))
+                    query_base=500, results=out.view(np.uint8), results_tolerance=tol.view(np.uint8))
 print("golden vectors written")

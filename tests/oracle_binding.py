@@ -33,6 +33,7 @@ class KoConfig(ctypes.Structure):
         ("seed", ctypes.c_uint64),
         ("query_id", ctypes.c_uint32),
         ("use_kdtree", ctypes.c_int32),
+        ("goal_mode", ctypes.c_int32),
     ]
 
 

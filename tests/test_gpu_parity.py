@@ -4,6 +4,8 @@ Bar: bit-exact — states, parents, costs, arrival times, indices, counters (fp6
 IEEE operations in the same order as the oracle, so `==` is the tolerance).  north_star would allow 1e-6
 relative on costs/times and ties within 1e-9; we do not need the allowance.
 """
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -579,3 +581,87 @@ def test_grow_headline_size_other_seeds(gpu_required, seed):
     assert G.grow(scenes.GOAL, 20000) == O.grow(scenes.GOAL, 20000)
     assert_same_tree(G, O)
     G.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dynamic,p_direct", [(0, 0.0), (1, 0.0), (1, 0.1)])
+def test_goal_connection_rule(gpu_required, dynamic, p_direct):
+    """O8 (KRRT_GOAL_CONNECT, the default): the goal node behind the tree, its parent, cost and arrival time, the chain
+    and the fine trajectory through it — bit-identical with the oracle, at every call of a growing tree."""
+    G, O = make_pair(gpu_required, dynamic=dynamic, p_direct=p_direct, capacity=4096)
+    seen_solved = False
+    for n_iter in (0, 1, 9, 15, 25, 50, 400, 3000):
+        rg = G.grow(scenes.GOAL, n_iter)
+        ro = O.grow(scenes.GOAL, n_iter)
+        assert rg == ro
+        assert_same_tree(G, O)
+        if not ro[0]:
+            assert rg[1] == -1
+            continue
+        seen_solved = True
+        assert ro[1] > 0
+        a, b = G.result(*rg), O.result(*ro)
+        assert a.tobytes() == b.tobytes()
+        ps, pt = G.path(rg[1])
+        qs, qt = O.path(ro[1])
+        assert np.array_equal(ps, qs) and np.array_equal(pt, qt) and np.array_equal(ps[-1], scenes.GOAL)
+        ref = np.concatenate([ob.solve(qs[k], qs[k + 1], 0.5, 0.1, qt[k]) for k in range(len(qs) - 1)])
+        assert np.array_equal(G.trajectory(rg[1], 0.1), ref)
+        if ro[1] == O.size:   # the goal node's stored edge follows the tree's in tree.trajectories
+            rows = np.empty((O.size + 1, 10, 5))
+            G._ck(capi.lib().krrt_tree_edges(G.h, 10, capi._d(rows), O.size + 1))
+            tau, _ = ob.steer(qs[-2], qs[-1])
+            want = np.array([np.append(ob.edge_state(qs[-2], qs[-1], tau[0], k / 9.0), qt[-2] + tau[0] * (k / 9.0))
+                             for k in range(10)])
+            assert np.array_equal(rows[-1], want)
+    assert seen_solved
+    # without a goal nothing is solved and the goal node's index is no longer accepted
+    assert G.grow(None, 5) == O.grow(None, 5) == (False, -1)
+    with pytest.raises(capi.KrrtError):
+        G.path(G.size)
+
+
+@pytest.mark.gpu
+def test_goal_tolerance_mode_and_full_tree(gpu_required):
+    """KRRT_GOAL_TOLERANCE keeps the tolerance-ball rule; a FULL tree still has room for the connected goal node."""
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.1, capacity=4096, goal_mode=1, goal_tol=0.5)
+    rg, ro = G.grow(scenes.GOAL, 3000), O.grow(scenes.GOAL, 3000)
+    assert rg == ro and ro[0] and ro[1] < O.size
+    assert G.result(*rg).tobytes() == O.result(*ro).tobytes()
+    G, O = make_pair(gpu_required, dynamic=1, p_direct=0.0, capacity=300)
+    rg, ro = G.grow(scenes.GOAL, 600), O.grow(scenes.GOAL, 600)
+    assert rg == ro and ro[0] and ro[1] == 300 == O.size
+    assert G.result(*rg).tobytes() == O.result(*ro).tobytes()
+    # set_params switches the rule on a live context
+    cfg = G.cfg
+    cfg.goal_mode = 1
+    G._ck(capi.lib().krrt_set_params(G.h, ctypes.byref(cfg)))
+    assert G.grow(scenes.GOAL, 0) == (False, -1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("goal_mode,dynamic,p_direct", [(0, 1, 0.0), (0, 0, 0.1), (1, 1, 0.1)])
+def test_plan_batch_goal_rule(gpu_required, goal_mode, dynamic, p_direct):
+    starts, goals, obs = scenes.batch_queries(400, 9, seed=23)
+    goals[::7] = starts[::7]                      # start == goal
+    goals[3, :2] = obs[3, 0, :2]                  # goal inside an obstacle: every offer collides at its end point
+    kw = dict(p_direct=p_direct, seed=9, goal_mode=goal_mode, goal_tol=0.7)
+    G = capi.Planner(capacity=1 << 12, **kw)
+    for n_iter in (200, 30):
+        out = G.plan_batch(starts, goals, obs, dynamic, n_iter, query_base=77)
+        ref = ob.plan_batch(ob.default_config(capacity=1 << 12, **kw), starts, goals, obs, dynamic, n_iter, query_base=77,
+                            nthreads=8)
+        assert out.tobytes() == ref.tobytes()
+        if goal_mode == 0:
+            assert not out["solved"][3] and out["solved"].mean() > (0.9 if n_iter == 200 else 0.5)
+            conn = out["goal_index"] == out["n_nodes"]
+            assert conn.sum() > 0 and np.all(out["goal_index"][out["solved"] == 1] > 0)
+    # the v1 kernel (every list in shared memory) applies the same rule
+    import os
+    os.environ["KRRT_BATCH_V1"] = "1"
+    try:
+        G1 = capi.Planner(capacity=1 << 12, **kw)
+        out1 = G1.plan_batch(starts, goals, obs, dynamic, 30, query_base=77)
+    finally:
+        del os.environ["KRRT_BATCH_V1"]
+    assert out1.tobytes() == ref.tobytes()
