@@ -158,10 +158,21 @@ int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, in
 int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, const double* obstacles, int q,
                     int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* out);
 /* same with device-resident inputs/outputs (pointers from the caller's CUDA allocator, e.g. for
- * timing with inputs already in HBM, or to feed an NCCL gather without a host round trip)      */
+ * timing with inputs already in HBM, or to feed an NCCL gather without a host round trip).  Asynchronous on
+ * cuda_stream (the ctx stream when NULL) once the per-context buffers have reached their size (the first call of a
+ * given q / n_iter allocates).  ONE batched plan may be in flight per context: work counter, counters and the redo
+ * list are per-context scratch — use one context per concurrent stream.                                          */
 int krrt_plan_batch_device(krrt_ctx* ctx, const double* d_starts, const double* d_goals,
                            const double* d_obstacles, int q, int m, int dynamic, int n_iter,
                            uint32_t query_base, krrt_result* d_out, void* cuda_stream);
+/* same, and the kernels count finished queries per chunk: d_chunk_done[i / chunk_queries] (zeroed by the caller) is
+ * incremented once query i's record is visible device-wide, so a consumer on ANOTHER stream can wait for a chunk to reach
+ * its size (cuStreamWaitValue32 GEQ) and ship it while the rest of the batch is still being planned — what
+ * libkrrt_mgpu's sweep does to overlap the NCCL gather with the planning (include/krrt_mgpu.h)                    */
+int krrt_plan_batch_device_chunks(krrt_ctx* ctx, const double* d_starts, const double* d_goals,
+                                  const double* d_obstacles, int q, int m, int dynamic, int n_iter,
+                                  uint32_t query_base, krrt_result* d_out, int chunk_queries,
+                                  uint32_t* d_chunk_done, void* cuda_stream);
 /* Yaw (heading) profiles for q independent queries: (w, dw) = current heading / rate, yaw = target heading, limits
  * v_max / a_max (Controller::setLimit), n sample rows over [0, final_time] as getAngleTrajectory(ctrl, offset, 0, t, n,
  * &inputs) returns them.  states: q x max(n,1) x 2 (w wrapped to [-pi, pi], dw), times / inputs: q x max(n,1),

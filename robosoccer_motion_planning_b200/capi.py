@@ -32,6 +32,7 @@ EXPORTS = (
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_tail_commits", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
     "krrt_solve_inputs", "krrt_scan_stats", "krrt_tree_read", "krrt_goal_index",
+    "krrt_plan_batch_device_chunks",
 )
 
 
@@ -123,6 +124,9 @@ def lib():
     L.krrt_plan_batch_device.argtypes = [P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
                                          ctypes.c_void_p, ctypes.c_void_p]
+    L.krrt_plan_batch_device_chunks.argtypes = [P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
+                                                ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
     L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
     L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
     L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]

@@ -29,6 +29,10 @@ struct BatchJob {
   double r, R2, goal_tol2;
   int S;
   int goal_mode;  // KRRT_GOAL_CONNECT / KRRT_GOAL_TOLERANCE (include/krrt.h)
+  // completion counters for a consumer on another stream (krrt_plan_batch_device_chunks): chunk_done[i / chunk_queries]
+  // is incremented once query i's record is visible device-wide (nullptr: none)
+  unsigned* chunk_done;
+  int chunk_queries;
   SamplerParams sp;
 };
 
@@ -38,16 +42,86 @@ constexpr int GOAL_MODE_TOLERANCE = 1;  // == KRRT_GOAL_TOLERANCE
 // inserted node offers node -> goal, the cheapest collision-free offer wins (lowest index among equal costs), the goal
 // node is written to slot n (all but its parent link, whose type is the caller's: goal_parent) unless a node that
 // coincides with the goal wins.  Returns the goal index or -1.
-template <typename Tree, typename LoadState>
-__device__ __noinline__ int warp_goal_connect(const Tree& T, LoadState load, int n, const State4& goal, double r,
-                                                 const EnvView& E, int& goal_parent) {
+// (not inlined, and handed COPIES of the views: the planner's own tree view stays in registers — taking its address
+// would move it to local memory for the whole kernel)
+__device__ __forceinline__ State4 goal_load_state(const TreeView& T, int i) { return load_state(T, i); }
+
+constexpr int GOAL_NC = 8;  // offers a lane keeps in registers: trees of up to 32 x GOAL_NC + 1 nodes take the fast path
+
+template <typename Tree>
+__device__ __noinline__ int warp_goal_connect(const Tree T, int n, const State4 goal, double r, const EnvView E,
+                                              int* goal_parent) {
   const int lane = threadIdx.x & 31;
+  *goal_parent = -1;
+  if (n - 1 <= 32 * GOAL_NC) {
+    // Fast path.  Every lane steers its nodes once and keeps (cost through the node, arrival time of the edge); then the
+    // warp walks the offers in (cost, index) order — the order the sequential planner sorts them in — and tests one
+    // edge at a time with all 32 lanes (S x m disc tests spread over the lanes) until one is free.
+    double cand[GOAL_NC], tgv[GOAL_NC];
+#pragma unroll
+    for (int p = 0; p < GOAL_NC; ++p) {
+      cand[p] = INFINITY;
+      tgv[p] = 0.0;
+      if (1 + 32 * p < n) {  // (warp-uniform)
+        const int i = 1 + 32 * p + lane;
+        if (i < n) {
+          const State4 x = goal_load_state(T, i);
+          double tg = 0.0, cg = 0.0;
+          if (dist2(x, goal) != 0.0) steer(x, goal, r, tg, cg);
+          cand[p] = T.ctc[i] + cg;
+          tgv[p] = tg;
+        }
+      }
+    }
+    for (;;) {
+      double bc = INFINITY, btg = 0.0;
+      int bp = -1;
+#pragma unroll
+      for (int p = 0; p < GOAL_NC; ++p)
+        if (cand[p] < bc) {  // (strict: an equal cost keeps the lower index)
+          bc = cand[p];
+          btg = tgv[p];
+          bp = p;
+        }
+      double kc = bc;
+      int ki = bp >= 0 ? 1 + 32 * bp + lane : -1, kl = lane;
+      warp_argmin(kc, ki, kl);
+      if (ki < 0) return -1;
+      const State4 x = goal_load_state(T, ki);
+      if (dist2(x, goal) == 0.0) {  // a node that coincides with the goal IS the goal node
+        *goal_parent = ki;
+        return ki;
+      }
+      const double tg = __shfl_sync(FULL, btg, kl);
+      if (!warp_edge_collide(x, goal, tg, T.tim[ki], E)) {
+        double t2, cg;
+        steer(x, goal, r, t2, cg);  // (the winner's edge cost once more: it was not kept)
+        if (lane == 0) {
+          T.pos[n] = make_double2(goal.x, goal.y);
+          T.vel[n] = make_double2(goal.vx, goal.vy);
+          T.ecost[n] = cg;
+          T.etime[n] = tg;
+          T.ctc[n] = kc;
+          T.tim[n] = T.tim[ki] + tg;
+        }
+        __syncwarp();
+        *goal_parent = ki;
+        return n;
+      }
+      if (lane == kl) {
+#pragma unroll
+        for (int p = 0; p < GOAL_NC; ++p)
+          if (p == bp) cand[p] = INFINITY;
+      }
+    }
+  }
+  // Big trees: every lane walks its nodes and tests the edges that can still win by itself.
   double bc = INFINITY, btg = 0.0, bcg = 0.0;
   int bi = -1, bsame = 0;
   for (int b0 = 1; b0 < n; b0 += 32) {
     const int i = b0 + lane;
     if (i >= n) continue;
-    const State4 x = load(i);
+    const State4 x = goal_load_state(T, i);
     const bool same = dist2(x, goal) == 0.0;
     double tg = 0.0, cg = 0.0;
     if (!same) steer(x, goal, r, tg, cg);
@@ -70,7 +144,7 @@ __device__ __noinline__ int warp_goal_connect(const Tree& T, LoadState load, int
   double kc = bc;
   int ki = bi, kl = lane;
   warp_argmin(kc, ki, kl);
-  goal_parent = ki;
+  *goal_parent = ki;
   if (ki < 0) return -1;
   const double tg = __shfl_sync(FULL, btg, kl), cg = __shfl_sync(FULL, bcg, kl);
   const int same = __shfl_sync(FULL, bsame, kl);
@@ -85,6 +159,14 @@ __device__ __noinline__ int warp_goal_connect(const Tree& T, LoadState load, int
   }
   __syncwarp();
   return n;
+}
+
+// every lane's stores of the record are ordered before the counter (fence by each writing lane, then one atomic)
+__device__ __forceinline__ void batch_query_done(const BatchJob& J, int qi) {
+  if (!J.chunk_done) return;
+  __threadfence();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) atomicAdd(&J.chunk_done[qi / J.chunk_queries], 1u);
 }
 
 __host__ __device__ inline size_t batch_warp_smem_bytes(int cap, int m) {
@@ -219,7 +301,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       gi = warp_find_goal(T, n, goal, J.goal_tol2);
     } else {
       int gpar = -1;
-      gi = warp_goal_connect(T, [&](int i) { return load_state(T, i); }, n, goal, J.r, E, gpar);
+      gi = warp_goal_connect(T, n, goal, J.r, E, &gpar);
       if (gi == n && lane == 0) T.parent[n] = gpar;
       __syncwarp();
     }
@@ -247,6 +329,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       }
     }
     __syncwarp();
+    batch_query_done(J, qi);
   }
   if (lane == 0 && J.stats) {
     const long long* sv = &st.iters;

@@ -63,6 +63,8 @@ __device__ __forceinline__ State4 b2_state(const B2Tree& T, int i) {
   return s;
 }
 
+__device__ __forceinline__ State4 goal_load_state(const B2Tree& T, int i) { return b2_state(T, i); }
+
 // order-preserving map of a double onto an unsigned 64-bit key (total order of the finite values and infinities)
 __device__ __forceinline__ unsigned long long b2_key(double x) {
   const unsigned long long u = (unsigned long long)__double_as_longlong(x);
@@ -167,7 +169,7 @@ __device__ __forceinline__ int b2_propagate(const B2Tree& T, int j) {
     qhead += cnt;
     for (;;) {
       const unsigned mk = __ballot_sync(FULL, c != B2_NIL);
-      if (mk == 0 || qtail + 32 > T.cap) break;
+      if (mk == 0 || qtail + __popc(mk) > T.cap) break;  // (exact bound: see warp_propagate)
       if (c != B2_NIL) {
         T.scr[qtail + __popc(mk & ((1u << lane) - 1))] = (unsigned short)c;
         c = T.sib[c];
@@ -446,7 +448,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
         gi = w == 0xffffffffu ? -1 : (int)w;
       } else {
         int gpar = -1;
-        gi = warp_goal_connect(T, [&](int i) { return b2_state(T, i); }, n, goal, J.r, E, gpar);
+        gi = warp_goal_connect(T, n, goal, J.r, E, &gpar);
         if (gi == n && lane == 0) T.parent[n] = (unsigned short)gpar;
         __syncwarp();
       }
@@ -481,6 +483,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       }
     }
     __syncwarp();
+    batch_query_done(J, qi);
   }
 }
 

@@ -311,9 +311,10 @@ int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, in
 // buffers have reached their size (they only grow: the first call of a given q / n_iter allocates).
 static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double* d_goals, const double* d_obs, int q,
                              int m, int dynamic, int n_iter, uint32_t query_base, krrt_result* d_out,
-                             cudaStream_t st, bool* redo_unserved = nullptr) {
+                             cudaStream_t st, bool* redo_unserved = nullptr, unsigned* d_chunk_done = nullptr,
+                             int chunk_queries = 0) {
   const krrt_config& c = ctx->cfg;
-  const int cap = std::min(c.capacity, n_iter + 1);  // root + one node per iteration at most (+ the goal node's slot)
+  const int cap = std::min(c.capacity, std::max(n_iter + 1, 2));  // root + one node per iteration at most (+ the goal node's slot)
   REQUIRE(cap >= 2, KRRT_ERR_INVALID, "n_iter / capacity too small");
   const size_t smem_max = ctx->prop.sharedMemPerBlockOptin;            // 227 KB on sm_100
   const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
@@ -355,6 +356,8 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
   J.query_base = query_base;
   J.r = c.r; J.R2 = c.R * c.R; J.goal_tol2 = c.goal_tol * c.goal_tol; J.S = c.S;
   J.goal_mode = c.goal_mode;
+  J.chunk_done = d_chunk_done;
+  J.chunk_queries = chunk_queries > 0 ? chunk_queries : 1;
   for (int k = 0; k < 4; ++k) { J.sp.lo[k] = c.lo[k]; J.sp.hi[k] = c.hi[k]; }
   J.sp.p_direct = c.p_direct;
   J.sp.seed = c.seed;
@@ -424,6 +427,20 @@ int krrt_plan_batch_device(krrt_ctx* ctx, const double* d_starts, const double* 
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
   return launch_plan_batch(ctx, d_starts, d_goals, d_obstacles, q, m, dynamic, n_iter, query_base, d_out, st);
+}
+
+int krrt_plan_batch_device_chunks(krrt_ctx* ctx, const double* d_starts, const double* d_goals,
+                                  const double* d_obstacles, int q, int m, int dynamic, int n_iter, uint32_t query_base,
+                                  krrt_result* d_out, int chunk_queries, uint32_t* d_chunk_done, void* cuda_stream) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  REQUIRE(q >= 0 && m >= 0 && m <= KRRT_MAX_OBS && n_iter >= 0, KRRT_ERR_INVALID, "bad q / m / n_iter");
+  REQUIRE(chunk_queries >= 1 && d_chunk_done, KRRT_ERR_INVALID, "chunk_queries >= 1 and a counter array are needed");
+  if (q == 0) return KRRT_OK;
+  REQUIRE(d_starts && d_goals && d_out && (m == 0 || d_obstacles), KRRT_ERR_INVALID, "null buffer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+  return launch_plan_batch(ctx, d_starts, d_goals, d_obstacles, q, m, dynamic, n_iter, query_base, d_out, st, nullptr,
+                           d_chunk_done, chunk_queries);
 }
 
 int krrt_plan_batch(krrt_ctx* ctx, const double* starts, const double* goals, const double* obstacles, int q, int m,

@@ -150,7 +150,9 @@ __device__ __forceinline__ long long warp_propagate(const TreeView& T, int j) {
     qhead += cnt;
     for (;;) {
       unsigned m = __ballot_sync(FULL, c >= 0);
-      if (m == 0 || qtail + 32 > T.cap) break;
+      // (a node is queued once, so a sound tree never fills the queue; the bound only stops a corrupted list.  It must be
+      //  the exact one: "qtail + 32" would drop the grandchildren of every rewired node in a tree of fewer than 64 slots)
+      if (m == 0 || qtail + __popc(m) > T.cap) break;
       if (c >= 0) {
         T.queue[qtail + __popc(m & ((1u << lane) - 1))] = c;
         c = T.link[c].y;

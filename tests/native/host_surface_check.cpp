@@ -134,8 +134,12 @@ int main(int argc, char** argv) {
     EXPECT((int)n == ko_size(oracle));
     const std::vector<Kinodynamic::State4>& cloud = tree.tree.cloud.states;
     const std::vector<int>& par = tree.parent;
-    EXPECT(cloud.size() == n && par.size() == n && tree.trajectories.size() == n);
-    for (size_t i = 0; i < n && i < cloud.size(); ++i) {
+    // the mirrors carry the connected goal node behind the tree while rrt.goalIndex() == tree.tree.size()
+    // (robosoccer_visual.hpp:45: tree(rrt.goalIndex()))
+    const size_t n_all = n + ((size_t)gi == n ? 1 : 0);
+    EXPECT(cloud.size() == n_all && par.size() == n_all && tree.trajectories.size() == n_all);
+    if (gi > 0) EXPECT(std::memcmp(tree((size_t)gi).data(), xg.data(), 32) == 0);
+    for (size_t i = 0; i < n_all && i < cloud.size(); ++i) {
       EXPECT(std::memcmp(cloud[i].data(), ko_states(oracle) + 4 * i, 32) == 0);
       EXPECT(par[i] == ko_parents(oracle)[i]);
       EXPECT(tree.cost()[i] == ko_ctc(oracle)[i] && tree.time()[i] == ko_times(oracle)[i]);

@@ -248,8 +248,11 @@ def test_trajectory_of_path(gpu_required):
     assert np.allclose(rows[-1, :4], st[-1], atol=1e-9)
 
 
-@pytest.mark.parametrize("dynamic,n_iter,q", [(1, 200, 300), (0, 75, 200), (1, 1, 40), (1, 0, 8)])
+@pytest.mark.parametrize("dynamic,n_iter,q", [(1, 200, 300), (0, 75, 200), (1, 1, 40), (1, 0, 8),
+                                              (1, 30, 800), (1, 50, 500), (0, 25, 400), (1, 62, 300)])
 def test_plan_batch(gpu_required, dynamic, n_iter, q):
+    """(trees of fewer than 64 slots once lost the grandchildren of rewired nodes in the propagation queue: the small
+    sizes of the live system — target_size 50 / 75, config.yaml:3, debug_core.launch:2 — are cases of their own)"""
     starts, goals, obs = scenes.batch_queries(q, 9, seed=11)
     cfg_kw = dict(p_direct=0.1, seed=5)
     G = capi.Planner(capacity=1 << 12, **cfg_kw)
@@ -653,7 +656,8 @@ def test_plan_batch_goal_rule(gpu_required, goal_mode, dynamic, p_direct):
                             nthreads=8)
         assert out.tobytes() == ref.tobytes()
         if goal_mode == 0:
-            assert not out["solved"][3] and out["solved"].mean() > (0.9 if n_iter == 200 else 0.5)
+            assert out["solved"].mean() > (0.9 if n_iter == 200 else 0.5)
+            assert dynamic or not out["solved"][3]    # (a moving disc leaves the goal free sooner or later)
             conn = out["goal_index"] == out["n_nodes"]
             assert conn.sum() > 0 and np.all(out["goal_index"][out["solved"] == 1] > 0)
     # the v1 kernel (every list in shared memory) applies the same rule
