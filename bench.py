@@ -10,7 +10,9 @@ N > 1: a single tree does not shard ("replicas only"): every rank
 Philox stream, so the per-GPU work is exactly the N = 1 work (with one stream per rank the plans differ in length by
 +-30 % and the max over ranks measures the unluckiest seed: 4.88 M expansions/s at N = 8, profiles/r1_bench_n8_s25.json);
 value = all ranks' expansions / max-over-ranks time.  The batched-query sweep, which
-DOES shard (contiguous blocks + one NCCL all-gather of results), is reported in the same line under "batched".
+DOES shard (contiguous blocks + NCCL gather of the result records inside libkrrt_mgpu.so), is reported in the same line
+under "batched" (C4, weak scaling) and "sweep_c5" (C5, strong scaling, with the sha256 of the gathered records).
+No torch anywhere on this path: processes are launched by torch.distributed.run, everything else goes through the C ABIs.
 
 --impl reference: the CPU oracle (oracle/krrt_oracle.c — the reference's own RRT* sources are an absent submodule,
 so nothing of it can be built: DESIGN.md §3) timed on the host cores on the same config.
@@ -177,37 +179,29 @@ def run_reference(args, rank, world):
 
 
 # ---------------------------------------------------------------------------------------------------- our arm
+def profile_json(name):
+    """a number taken from an ncu capture / microbenchmark committed under profiles/ (None when the file is absent)"""
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
 def run_ours(args, rank, world, local_rank):
-    import torch
-    import torch.distributed as dist
+    """No torch on this path: device memory, streams, NCCL and timing all live behind the C ABIs of libkrrt.so
+    (include/krrt.h) and libkrrt_mgpu.so (include/krrt_mgpu.h)."""
+    import hashlib
     from robosoccer_motion_planning_b200 import capi, scenes, sweep
-    assert torch.cuda.is_available(), "bench.py needs a GPU: libkrrt has no CPU fallback"
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-
-    def flush_l2():
-        flush_buf.zero_()
-        torch.cuda.synchronize()
+    assert capi.lib().krrt_device_count() > local_rank, "bench.py needs a GPU: libkrrt has no CPU fallback"
+    # the batched-query handle also carries the job's NCCL communicator (barrier / max over ranks of the headline)
+    S = sweep.Sweep.from_env(p_direct=P_DIRECT)
+    barrier = S.barrier
+    max_over_ranks = S.max_over_ranks
 
     obs, start, goal = c2_scene()
     G = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, query_id=0, batch=args.batch)
+    flush_l2 = G.flush_l2          # overwrites 2 x L2 on the context's stream and waits
 
     def plan_device_timed():
         G.set_obstacles(obs, 1)
@@ -269,12 +263,25 @@ def run_ours(args, rank, world, local_rank):
     scan_bytes = lt["scan_node_samples"] * 32.0
     achieved = scan_bytes / (lt["total_ms"] * 1e-3) / 1e9 if lt["total_ms"] > 0 else 0.0
     scan_only = scan_bytes / (lt["scan_ms"] * 1e-3) / 1e9 if lt["scan_ms"] > 0 else 0.0
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_k_grow_traffic.json")) as f:
-            tr = json.load(f)
-        traffic = float(tr["dram_bytes_read"] + tr["dram_bytes_write"])   # one ncu --set full capture of this kernel
-    except Exception:
-        traffic = None
+    ncu_k = profile_json("r2_k_grow_ncu.json") or profile_json("r1_k_grow_traffic.json") or {}
+    traffic = (float(ncu_k["dram_bytes_read"] + ncu_k["dram_bytes_write"])
+               if "dram_bytes_read" in ncu_k else None)   # one ncu --set full capture of this kernel
+    sst = G.scan_stats()
+    sub_rounds = wave["rounds_parallel"] + wave["rounds_sequential"]
+    lat = profile_json("r2_latency_model.json") or {}
+    # what really bounds the kernel: the chain of sub-rounds.  floor = sub-rounds x (grid barriers x their
+    # measured cost + the decide / validate / apply critical path of an undisturbed CTA) + windows x (scan + steer of one)
+    commit_ms = sum(kt[k]["ms"] for k in ("decide", "validate", "apply"))
+    latency = {"sub_rounds": int(sub_rounds), "windows": int(kt["scan"]["launches"]),
+               "us_per_sub_round": 1e3 * commit_ms / max(sub_rounds, 1),
+               "expansions_per_sub_round": N_ITER / max(sub_rounds, 1)}
+    if lat:
+        floor_us = lat["barriers_per_sub_round"] * lat["barrier_us"] + lat["cta0_critical_path_us"]
+        latency.update({"barrier_us": lat["barrier_us"], "barriers_per_sub_round": lat["barriers_per_sub_round"],
+                        "cta0_critical_path_us": lat["cta0_critical_path_us"],
+                        "latency_floor_ms": 1e-3 * floor_us * sub_rounds,
+                        "frac_of_latency_floor": (1e-3 * floor_us * sub_rounds) / commit_ms if commit_ms > 0 else None,
+                        "source": lat.get("source")})
     roofline = {"bound": "hbm", "kernel": "k_grow", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": scan_bytes,
@@ -282,124 +289,126 @@ def run_ours(args, rank, world, local_rank):
                 "share_of_step": 1.0,
                 "phase_shares": shares,
                 "scan_phase_GBps_algorithmic": scan_only,
-                "scan_index": dict(G.scan_stats(), visited_bytes=32.0 * G.scan_stats()["visited_pairs"]),
+                "scan_index": dict(sst, visited_bytes=32.0 * sst["visited_pairs"]),
+                "visited_bytes": 32.0 * sst["visited_pairs"],
+                "l2_bytes": ncu_k.get("lts_t_bytes"),
+                "scan_phase_GBps_visited": (32.0 * sst["visited_pairs"] / (lt["scan_ms"] * 1e-3) / 1e9
+                                            if lt["scan_ms"] > 0 else None),
+                "l2_peak_GBps": (profile_json("r2_l2_peak.json") or {}).get("l2_read_GBps"),
+                "fp64_pipe_pct": ncu_k.get("fp64_pipe_pct"),
+                "latency_model": latency,
                 "note": "one persistent kernel per grow call; algorithmic bytes = 32 B x tree nodes x samples scanned "
-                        "(brute-force equivalent; scan_index.visited_bytes is what the grid-indexed scan really read) "
-                        "(SURVEY 8d: N x 32 B per expansion) over the kernel's whole duration.  A <= 20k-node tree is "
-                        "640 KB and L2-resident: this config is bound by the latency chain of the commit sub-rounds "
-                        "(decide / validate / apply, three grid barriers each), not by HBM; scan_phase_GBps is the "
-                        "same byte count over the scan phase alone (see c3_100k / c3_1m for larger trees)"}
-    # ---- batched queries (configs 3/4): one warp per query, sharded over ranks, NCCL all-gather of the results
+                        "(brute-force equivalent, SURVEY 8d: N x 32 B per expansion) over the kernel's whole duration; "
+                        "visited_bytes is what the grid-indexed scan really read (L2-resident: `traffic` is the DRAM "
+                        "bytes of one ncu capture).  A <= 20k-node tree is 640 KB: this config is bound by the latency "
+                        "chain of the commit sub-rounds (latency_model), not by HBM"}
+
+    # ---- batched queries (config 3, C4): BATCH_Q queries per GPU (weak scaling), blocks + chunked NCCL gather inside
+    # libkrrt_mgpu (krrt_sweep_load / run: inputs resident in HBM, device time of plan + gather, max over ranks)
     q_total = BATCH_Q * world
-    lo, hi = sweep.shard_bounds(q_total, rank, world)
-    bs, bg, bo = scenes.batch_queries(hi - lo, 9, seed=0, first=lo)
-    Gb = capi.Planner(device=local_rank, p_direct=P_DIRECT)
-    d_s = torch.from_numpy(bs).to(dev)
-    d_g = torch.from_numpy(bg).to(dev)
-    d_o = torch.from_numpy(bo).to(dev)
-    item = capi.RESULT_DTYPE.itemsize
-    d_out = torch.zeros((hi - lo) * item, dtype=torch.uint8, device=dev)
-    d_all = torch.zeros(q_total * item, dtype=torch.uint8, device=dev)
-    # a dedicated torch stream (non-zero handle): the kernel, the NCCL gather and the timing events all go on it
-    tstream = torch.cuda.Stream(device=dev)
-    assert tstream.cuda_stream != 0
-
-    def batched_step():
-        Gb.plan_batch_device(d_s.data_ptr(), d_g.data_ptr(), d_o.data_ptr(), hi - lo, 9, 1, BATCH_ITERS, lo,
-                             d_out.data_ptr(), tstream.cuda_stream)
-        if world > 1:
-            dist.all_gather_into_tensor(d_all, d_out)
-
-    torch.cuda.synchronize()
-    with torch.cuda.stream(tstream):
-        for _ in range(3):
-            batched_step()
+    bs, bg, bo = scenes.batch_queries(q_total, 9, seed=0)
+    S.load(bs, bg, bo)
+    for _ in range(3):
+        S.run(1, BATCH_ITERS)
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     bsteps = max(3, args.steps)
+    l0b = S.launch_count
     b_ms = 0.0
     for _ in range(bsteps):
         flush_l2()
-        with torch.cuda.stream(tstream):
-            e0.record(tstream)
-            batched_step()
-            e1.record(tstream)
-        e1.synchronize()
-        b_ms += e0.elapsed_time(e1)
+        b_ms += S.run(1, BATCH_ITERS)
+    b_launches = S.launch_count - l0b
     barrier()
     b_ms = max_over_ranks(b_ms)
-    # e2e batched: pinned host buffers through krrt_plan_batch
-    p_s = torch.from_numpy(bs).pin_memory().numpy()
-    p_g = torch.from_numpy(bg).pin_memory().numpy()
-    p_o = torch.from_numpy(bo).pin_memory().numpy()
-    p_out = torch.zeros((hi - lo) * item, dtype=torch.uint8).pin_memory().numpy().view(capi.RESULT_DTYPE)
-    Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo, out=p_out)
+    bst = S.stats()                 # counters of the last C4 run, all ranks
+    # e2e batched: page-locked host buffers through krrt_sweep_multi_gpu (H2D of the block, plan, gather, D2H of all records)
+    p_s, p_g, p_o = capi.PinnedArray.like(bs), capi.PinnedArray.like(bg), capi.PinnedArray.like(bo)
+    p_out = capi.PinnedArray((q_total,), capi.RESULT_DTYPE)
+    S.sweep(p_s.array, p_g.array, p_o.array, 1, BATCH_ITERS, out=p_out.array)
+    barrier()
     be_ms = 0.0
     for _ in range(bsteps):
         flush_l2()
-        Gb.timer_begin()
-        out_h = Gb.plan_batch(p_s, p_g, p_o, 1, BATCH_ITERS, query_base=lo, out=p_out)
-        be_ms += Gb.timer_end()
+        out_h = S.sweep(p_s.array, p_g.array, p_o.array, 1, BATCH_ITERS, out=p_out.array)
+        be_ms += S.last_timing()["e2e_ms"]
     barrier()
     be_ms = max_over_ranks(be_ms)
-    bst = Gb.batch_stats()          # counters of the last C4 launch (one rank's shard)
+    out_h = out_h.copy()
+    lo, hi = sweep.shard_bounds(q_total, rank, world)
+
     # ---- config 4 (C5): ONE Monte-Carlo sweep of 65536 queries sharded over the ranks (strong scaling: the sweep is fixed,
-    # the shard shrinks with N) + NCCL all-gather of all 65536 result records.  Scenes: the 4096 C4 scenes, each planned
-    # with 16 different Philox streams (global query id = stream of the query)
+    # the block shrinks with N) + gather of all 65536 result records.  Scenes: the 4096 C4 scenes, each planned with 16
+    # different Philox streams (global query id = stream of the query)
     SWEEP_Q = 65536
-    slo, shi = sweep.shard_bounds(SWEEP_Q, rank, world)
     base_s, base_g, base_o = scenes.batch_queries(BATCH_Q, 9, seed=0)
-    sel = np.arange(slo, shi) % BATCH_Q
-    d_ss = torch.from_numpy(np.ascontiguousarray(base_s[sel])).to(dev)
-    d_sg = torch.from_numpy(np.ascontiguousarray(base_g[sel])).to(dev)
-    d_so = torch.from_numpy(np.ascontiguousarray(base_o[sel])).to(dev)
-    spad = sweep.max_shard(SWEEP_Q, world)
-    d_sout = torch.zeros(spad * item, dtype=torch.uint8, device=dev)
-    d_sall = torch.zeros(world * spad * item, dtype=torch.uint8, device=dev)
-
-    def sweep_step():
-        Gb.plan_batch_device(d_ss.data_ptr(), d_sg.data_ptr(), d_so.data_ptr(), shi - slo, 9, 1, BATCH_ITERS, slo,
-                             d_sout.data_ptr(), tstream.cuda_stream)
-        if world > 1:
-            dist.all_gather_into_tensor(d_sall, d_sout)
-
-    torch.cuda.synchronize()
-    with torch.cuda.stream(tstream):
-        sweep_step()
+    sel = np.arange(SWEEP_Q) % BATCH_Q
+    sw_s, sw_g, sw_o = (np.ascontiguousarray(x[sel]) for x in (base_s, base_g, base_o))
+    S.load(sw_s, sw_g, sw_o)
+    S.run(1, BATCH_ITERS)
     barrier()
     s_ms = 0.0
     for _ in range(3):
         flush_l2()
-        with torch.cuda.stream(tstream):
-            e0.record(tstream)
-            sweep_step()
-            e1.record(tstream)
-        e1.synchronize()
-        s_ms += e0.elapsed_time(e1)
+        s_ms += S.run(1, BATCH_ITERS)
     barrier()
     s_ms = max_over_ranks(s_ms)
+    ov = S.overlap()
+    info = S.info()
     sweep_line = {"workload": f"C5: one sweep of {SWEEP_Q} queries x {BATCH_ITERS} iterations sharded over {world} GPU(s) "
-                              "(strong scaling), results all-gathered" + (" over NCCL" if world > 1 else " (1 GPU: no gather)"),
+                              "(strong scaling), results gathered" + (" over NCCL, chunk by chunk while later chunks are planned"
+                                                                      if world > 1 else " (1 GPU: no gather)"),
                   "queries_per_sec": SWEEP_Q * 3 / (s_ms * 1e-3), "ms_per_sweep": s_ms / 3,
-                  "gather_bytes": int(SWEEP_Q * item) if world > 1 else 0,
-                  "solved_frac": float((d_sout.cpu().numpy()[: (shi - slo) * item].view(capi.RESULT_DTYPE)["solved"] != 0).mean())}
-    b_flop = 134.0 * bst["steer_calls"] + 1180.0 * bst["collide_calls"]      # SURVEY 8(d) accounting, one rank's shard
+                  "gather_bytes": int(SWEEP_Q * capi.RESULT_DTYPE.itemsize) if world > 1 else 0,
+                  "gather": {"nccl": bool(info["nccl"]), "nccl_version": info["nccl_version"], "ranks": info["world"],
+                             "overlapped": ov["overlapped"], "chunks_per_block": ov["chunks"]}}
+    if rank == 0:
+        recs = S.results()                     # all 65536 records, global order, from the gathered device array
+        sweep_line["records_sha256"] = hashlib.sha256(recs.tobytes()).hexdigest()
+        sweep_line["solved_frac"] = float((recs["solved"] != 0).mean())
+        import oracle_binding as ob
+        pick = np.arange(0, SWEEP_Q, SWEEP_Q // 512)          # 512 queries spread over every rank's block
+        cfgo = ob.default_config(p_direct=P_DIRECT)
+        okp = True
+        for i in pick:
+            ref1 = ob.plan_batch(cfgo, sw_s[i:i + 1], sw_g[i:i + 1], sw_o[i:i + 1], 1, BATCH_ITERS, query_base=int(i))
+            okp = okp and ref1.tobytes() == recs[i:i + 1].tobytes()
+        sweep_line["parity_vs_oracle"] = {"sample": "512 of the 65536 gathered records (every 128th query)",
+                                          "result": "bit-exact" if okp else "MISMATCH"}
+    if world > 1:
+        # the same sweep on ONE GPU, timed in the same run (rank 0; the others wait at the barrier): strong-scaling efficiency
+        t1 = 0.0
+        if rank == 0:
+            S1 = sweep.Sweep.single_process(1, devices=[local_rank], p_direct=P_DIRECT)
+            S1.load(sw_s, sw_g, sw_o)
+            S1.run(1, BATCH_ITERS)
+            for _ in range(2):
+                flush_l2()
+                t1 += S1.run(1, BATCH_ITERS) / 2
+            sweep_line["one_gpu_records_sha256"] = hashlib.sha256(S1.results().tobytes()).hexdigest()
+            S1.close()
+        barrier()
+        t1 = max_over_ranks(t1)
+        sweep_line["one_gpu_ms_per_sweep"] = t1
+        sweep_line["efficiency"] = t1 / (world * (s_ms / 3))
+    b_flop = 134.0 * bst["steer_calls"] + 1180.0 * bst["collide_calls"]      # SURVEY 8(d) accounting, all ranks
     f64_peak, f64_src = fp64_peak()
-    b_tflops = b_flop * bsteps / (b_ms * 1e-3) / 1e12
+    b_tflops = b_flop * bsteps / (b_ms * 1e-3) / 1e12 / world
     batched = {
         "roofline": {"bound": "fp64 pipe / latency", "kernel": "k_plan_batch2", "achieved": b_tflops, "peak": f64_peak,
                      "unit": "TFLOP/s", "frac": b_tflops / f64_peak, "peak_source": f64_src,
-                     "algorithmic_flop_per_launch": b_flop,
-                     "note": "134 flop per steering pair + 1180 flop per edge test (SURVEY 8d), counted from the "
+                     "algorithmic_flop_per_launch": b_flop / world,
+                     "note": "per GPU; 134 flop per steering pair + 1180 flop per edge test (SURVEY 8d), counted from the "
                              "kernel's own steer_calls / collide_calls; trees live in shared memory, HBM traffic is the "
-                             "inputs and the 1304-byte result records only"},
+                             "inputs and the 1312-byte result records only"},
         "workload": f"{BATCH_Q} queries/GPU x {BATCH_ITERS} iterations, 9 moving obstacles, p_direct=0.1 (C4; sharded sweep C5 for N>1)",
         "queries_per_sec": q_total * bsteps / (b_ms * 1e-3),
         "expansions_per_sec": q_total * BATCH_ITERS * bsteps / (b_ms * 1e-3),
         "ms_per_step": b_ms / bsteps,
         "e2e_queries_per_sec": q_total * bsteps / (be_ms * 1e-3),
-        "h2d_bytes_per_step": int(bs.nbytes + bg.nbytes + bo.nbytes), "d2h_bytes_per_step": int((hi - lo) * item),
-        "gather": "nccl all_gather_into_tensor of result records" if world > 1 else "none (1 GPU)",
+        "h2d_bytes_per_step": int((bs.nbytes + bg.nbytes + bo.nbytes) // world),
+        "d2h_bytes_per_step": int(q_total * capi.RESULT_DTYPE.itemsize),
+        "gpu_launches": int(b_launches),
+        "gather": "NCCL all-gather of result records inside libkrrt_mgpu, overlapped chunk by chunk" if world > 1 else "none (1 GPU)",
         "solved_frac": float(out_h["solved"].mean()),
     }
 
@@ -408,7 +417,7 @@ def run_ours(args, rank, world, local_rank):
         "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "replicas": world, "window": int(G.cfg.batch),
-                   "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only (single tree; every rank grows the same plan, same seed); "
+                   "l2": "flushed between timed steps (write of 2 x L2)", "parallelism": "replicas only (single tree; every rank grows the same plan, same seed); "
                    "batched queries shard by contiguous blocks"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / args.steps},
@@ -419,6 +428,8 @@ def run_ours(args, rank, world, local_rank):
         "sweep_c5": sweep_line,
         "tree_nodes": int(res["n_nodes"]), "solved": bool(res["solved"]), "cost": float(res["cost"]),
         "rounds": wave,
+        "cpu_flags": "oracle built with -O3 -mavx2 -mfma -ffp-contract=off (x86-64-v3, not -march=native: the .so built in the "
+                     "build container must run on the GPU box's host)",
     }
 
     if rank == 0 and world == 1:
@@ -435,16 +446,17 @@ def run_ours(args, rank, world, local_rank):
                                 "sample": f"{reps} full C2 plans ({N_ITER} iterations each), kd-tree near search, 1 thread "
                                           "(a single RRT* tree is sequential)"}
         same = all(np.array_equal(a, b) for a, b in zip(G.tree(), O.tree())) and r_last == ro
+        same = same and G.result(*r_last).tobytes() == O.result(*ro).tobytes()
         line["parity_vs_oracle"] = "bit-exact" if same else "MISMATCH"
         # batched CPU baseline on all host cores, bounded sample
         allc = os.cpu_count() or 1
-        qs = min(hi - lo, 16 * allc)
+        qs = min(hi - lo, 32 * allc)
         tb = time.perf_counter()
         refb = ob.plan_batch(ob.default_config(p_direct=P_DIRECT), bs[:qs], bg[:qs], bo[:qs], 1, BATCH_ITERS,
                              query_base=lo, nthreads=allc)
         tb = time.perf_counter() - tb
         line["batched"]["cpu_baseline"] = {"queries_per_sec": qs / tb, "cores": allc, "kind": "port",
-                                           "sample": f"{qs} of the {BATCH_Q} queries"}
+                                           "sample": f"{qs} of the {BATCH_Q} queries, one query per thread at a time"}
         line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
                                                else "MISMATCH")
         # config 0 (rrtstar_benchmark, C1): static obstacles, fixed seed, 10k iterations — GPU and the CPU port, same plan
@@ -454,10 +466,12 @@ def run_ours(args, rank, world, local_rank):
             P_.set_obstacles(scenes.static_obstacles(), 0)
             P_.set_start(start)
         G1.grow(goal, 10000)                       # warm-up
-        G1.set_start(start)
-        flush_l2()
-        r1 = G1.grow(goal, 10000)
-        ms1 = G1.last_timing()["total_ms"]
+        ms1 = 0.0
+        for _ in range(args.steps):
+            G1.set_start(start)
+            flush_l2()
+            r1 = G1.grow(goal, 10000)
+            ms1 += G1.last_timing()["total_ms"] / args.steps
         t0 = time.perf_counter()
         ro1 = O1.grow(goal, 10000)
         dt1 = time.perf_counter() - t0
@@ -465,41 +479,43 @@ def run_ours(args, rank, world, local_rank):
         line["c1_rrtstar_benchmark"] = {
             "workload": "C1: 9 static obstacles, fixed seed, 10000 iterations, p_direct = 0, goal connected (O8)",
             "cost": float(G1.result(*r1)["cost"]) if r1[0] else None,
-            "expansions_per_sec": 10000 / (ms1 * 1e-3), "ms": ms1, "nodes": G1.size, "solved": bool(r1[0]),
+            "expansions_per_sec": 10000 / (ms1 * 1e-3), "ms": ms1, "steps": args.steps, "nodes": G1.size, "solved": bool(r1[0]),
             "cpu_baseline": {"value": 10000 / dt1, "unit": UNIT, "cores": 1, "kind": "port", "sample": "the full plan, once"},
             "parity_vs_oracle": "bit-exact" if same1 else "MISMATCH"}
         G1.close()
-        # the README's curves: computation time and solution cost against node size on the C1 scene,
-        # 1024 seeds per size through the batched planner; CPU port on all host cores beside it (context: the README's
-        # numbers are an i3 at 2.0 GHz, scene and trial count not stated)
+        # the README's curves: computation time and solution cost against node size, 1024 seeds per size
+        # through the batched planner, on the obstacle-free field (where the README's cost band is reproduced) and on the
+        # C1 scene; CPU port on all host cores beside it (the README's numbers are an i3 at 2.0 GHz, scene not stated)
         curve = []
         qn = 1024
         c_s = np.tile(start, (qn, 1))
         c_g = np.tile(goal, (qn, 1))
-        c_o = np.tile(scenes.static_obstacles(), (qn, 1, 1))
-        for p_dir in (0.0, 0.1):
-            Gc = capi.Planner(device=local_rank, p_direct=p_dir)
-            for nodes in (10, 25, 50, 75, 100, 150, 200):
-                Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
-                Gc.timer_begin()
-                oc = Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
-                msb = Gc.timer_end()
-                tcp = time.perf_counter()
-                rc_ = ob.plan_batch(ob.default_config(p_direct=p_dir), c_s[:4 * allc], c_g[:4 * allc], c_o[:4 * allc], 0,
-                                    nodes, nthreads=allc)
-                tcp = time.perf_counter() - tcp
-                sv = oc["solved"] != 0
-                curve.append({"p_direct": p_dir, "node_size": nodes, "gpu_ms_per_plan_batched": msb / qn,
-                              "cpu_port_ms_per_plan_1core": 1e3 * tcp / 4.0,   # 4 plans per thread, all threads busy
-                              "solved_frac": float(sv.mean()),
-                              "mean_cost": float(oc["cost"][sv].mean()) if sv.any() else None,
-                              "parity": bool(np.array_equal(oc[:4 * allc].view(np.uint8), rc_.view(np.uint8)))})
-            Gc.close()
-        line["readme_curve"] = {"scene": "C1 start/goal, 9 static obstacles, goal connected to the cheapest collision-free node (O8), 1024 seeds per point (query_id = seed)",
+        for scene_name, c_o in (("free field", np.zeros((qn, 0, 4))), ("C1, 9 static robots", np.tile(scenes.static_obstacles(), (qn, 1, 1)))):
+            for p_dir in (0.0, 0.1):
+                Gc = capi.Planner(device=local_rank, p_direct=p_dir)
+                for nodes in (10, 25, 50, 75, 100, 150, 200):
+                    Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
+                    Gc.timer_begin()
+                    oc = Gc.plan_batch(c_s, c_g, c_o, 0, nodes)
+                    msb = Gc.timer_end()
+                    tcp = time.perf_counter()
+                    rc_ = ob.plan_batch(ob.default_config(p_direct=p_dir), c_s[:4 * allc], c_g[:4 * allc], c_o[:4 * allc], 0,
+                                        nodes, nthreads=allc)
+                    tcp = time.perf_counter() - tcp
+                    sv = oc["solved"] != 0
+                    curve.append({"scene": scene_name, "p_direct": p_dir, "node_size": nodes, "gpu_ms_per_plan_batched": msb / qn,
+                                  "cpu_port_ms_per_plan_1core": 1e3 * tcp / 4.0,   # 4 plans per thread, all threads busy
+                                  "solved_frac": float(sv.mean()),
+                                  "mean_cost": float(oc["cost"][sv].mean()) if sv.any() else None,
+                                  "parity": bool(np.array_equal(oc[:4 * allc].view(np.uint8), rc_.view(np.uint8)))})
+                Gc.close()
+        line["readme_curve"] = {"note": "C1 start/goal, goal connected to the cheapest collision-free node (O8), 1024 seeds per "
+                                        "point (query_id = seed); README cost_plot.png: 16.26 @ 10 -> 12.22 @ 200 without direct sampling",
                                 "points": curve}
-        # config 3: single large tree, 100k iterations, static obstacles (+ the 1M-iteration tree with --c3-1m)
+        # config 2 (C3): single large trees on static obstacles — 140k iterations (>= 100k NODES: the tree north_star's 100x
+        # target is quoted on) beside the CPU port on one host core, and the 1M-iteration tree
         if not args.skip_c3:
-            for label, iters in (("c3_100k", 100000),) + ((("c3_1m", 1000000),) if args.c3_1m else ()):
+            for label, iters in (("c3_100k_nodes", 140000), ("c3_1m", 1000000)):
                 G3 = capi.Planner(device=local_rank, capacity=iters + 2, batch=args.batch)
                 G3.set_obstacles(scenes.static_obstacles(), 0)
                 G3.set_start(start)
@@ -511,21 +527,25 @@ def run_ours(args, rank, world, local_rank):
                 t_plain = t3["total_ms"]
                 k3 = G3.kernel_times()
                 ks = sum(v["ms"] for v in k3.values()) or 1.0
-                line[label] = {"expansions_per_sec": iters / (t_plain * 1e-3), "ms": t_plain, "nodes": G3.size,
+                s3 = G3.scan_stats()
+                line[label] = {"iterations": iters, "expansions_per_sec": iters / (t_plain * 1e-3), "ms": t_plain, "nodes": G3.size,
                                "kernel_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t_plain * 1e-3) / 1e9,
-                               "kernel_frac_of_hbm_peak": t3["scan_node_samples"] * 32 / (t_plain * 1e-3) / 1e9 / peak,
                                "scan_phase_GBps_algorithmic": t3["scan_node_samples"] * 32 / (t3["scan_ms"] * 1e-3) / 1e9,
+                               "scan_phase_GBps_visited": 32.0 * s3["visited_pairs"] / (t3["scan_ms"] * 1e-3) / 1e9,
                                "phase_shares": {k: round(v["ms"] / ks, 4) for k, v in k3.items() if v["ms"] > 0},
-                               "scan_index": dict(G3.scan_stats(), visited_bytes=32.0 * G3.scan_stats()["visited_pairs"]),
-                               "rounds": G3.wave_stats()}
-                if label == "c3_100k":   # the same plan on one host core (kd-tree near search), once
+                               "scan_index": dict(s3, visited_bytes=32.0 * s3["visited_pairs"]),
+                               "rounds": G3.wave_stats(),
+                               "note": "kernel_GBps_algorithmic counts the brute-force-equivalent bytes (SURVEY 8d); the indexed, "
+                                       "L2-resident scan reads far fewer (scan_index.visited_bytes), so that figure is an "
+                                       "equivalence, not a bandwidth: it may exceed the HBM peak"}
+                if label == "c3_100k_nodes":   # the same plan on one host core (kd-tree near search), once
                     O3 = ob.OraclePlanner(capacity=iters + 2, query_id=0)
                     O3.set_obstacles(scenes.static_obstacles(), 0)
                     O3.set_start(start)
                     t0 = time.perf_counter()
                     O3.grow(None, iters)
                     dt3 = time.perf_counter() - t0
-                    same3 = all(np.array_equal(a, b) for a, b in zip(G3.tree(), O3.tree()))
+                    same3 = all(np.array_equal(a, b) for a, b in zip(G3.tree(), O3.tree())) and G3.stats() == O3.stats()
                     line[label]["cpu_baseline"] = {"value": iters / dt3, "unit": UNIT, "cores": 1, "kind": "port",
                                                    "sample": f"the full {iters}-iteration plan, once, kd-tree near search"}
                     line[label]["gpu_over_cpu"] = line[label]["expansions_per_sec"] / (iters / dt3)
@@ -533,8 +553,7 @@ def run_ours(args, rank, world, local_rank):
                 G3.close()
     if rank == 0:
         emit(line)
-    if world > 1:
-        dist.destroy_process_group()
+    S.close()
 
 
 def main():
@@ -545,7 +564,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=0, help="window size: samples scanned + steered at once (0 = library default)")
     ap.add_argument("--skip-c3", action="store_true")
-    ap.add_argument("--c3-1m", action="store_true", help="also grow the 1M-iteration single tree (a few seconds)")
+    ap.add_argument("--c3-1m", action="store_true", help="(kept for compatibility: the 1M-iteration tree is part of the default line)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

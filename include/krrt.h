@@ -204,6 +204,12 @@ int krrt_ingest_vision_device(krrt_ctx* ctx, const float* d_team, const int32_t*
                               int32_t* d_n_obs, void* cuda_stream);
 /* oracle-comparable counters summed over the queries of the last batched plan                    */
 int krrt_batch_stats(krrt_ctx* ctx, krrt_stats* out);
+/* integration / benchmarking helpers: page-locked host memory (cudaHostAlloc: copies at full PCIe rate, no staging),
+ * and a cold-cache step for timing loops: overwrites a buffer twice the L2's size on the ctx stream and waits      */
+int krrt_host_alloc(void** p, uint64_t bytes);
+int krrt_host_free(void* p);
+int krrt_flush_l2(krrt_ctx* ctx);
+int krrt_synchronize(krrt_ctx* ctx);
 /* kernels launched by this ctx since creation (bench.py's gpu_launches)                          */
 int64_t krrt_launch_count(const krrt_ctx* ctx);
 /* CUDA-event stopwatch on the ctx stream spanning any sequence of calls (end-to-end timing incl. copies) */

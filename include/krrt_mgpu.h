@@ -65,6 +65,10 @@ int krrt_sweep_multi_gpu(krrt_mgpu* mg, const double* starts, const double* goal
 int krrt_sweep_load(krrt_mgpu* mg, const double* starts, const double* goals, const double* obstacles, int q, int m);
 int krrt_sweep_run(krrt_mgpu* mg, int dynamic, int n_iter, uint32_t query_base, double* device_ms);
 int krrt_sweep_results(krrt_mgpu* mg, krrt_result* out);
+/* device times of the last calls on this handle's first GPU, CUDA events on its planning stream: run_ms = the last
+ * krrt_sweep_run; e2e_ms = from the first host-to-device copy of the last krrt_sweep_load to the last device-to-host
+ * copy of the last krrt_sweep_results (what krrt_sweep_multi_gpu spans, host gaps included)                        */
+int krrt_sweep_last_timing(krrt_mgpu* mg, double* run_ms, double* e2e_ms);
 /* oracle-comparable counters of the last run, summed over ALL queries of the sweep (all ranks)                      */
 int krrt_sweep_stats(krrt_mgpu* mg, krrt_stats* out);
 /* kernels launched by this handle's contexts since creation                                                         */

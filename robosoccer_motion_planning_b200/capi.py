@@ -32,7 +32,7 @@ EXPORTS = (
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_tail_commits", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
     "krrt_solve_inputs", "krrt_scan_stats", "krrt_tree_read", "krrt_goal_index",
-    "krrt_plan_batch_device_chunks",
+    "krrt_plan_batch_device_chunks", "krrt_host_alloc", "krrt_host_free", "krrt_flush_l2", "krrt_synchronize",
 )
 
 
@@ -127,6 +127,10 @@ def lib():
     L.krrt_plan_batch_device_chunks.argtypes = [P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                                 ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
                                                 ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    L.krrt_host_alloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_uint64]
+    L.krrt_host_free.argtypes = [ctypes.c_void_p]
+    L.krrt_flush_l2.argtypes = [P]
+    L.krrt_synchronize.argtypes = [P]
     L.krrt_set_params.argtypes = [P, ctypes.POINTER(KrrtConfig)]
     L.krrt_tree_edges.argtypes = [P, ctypes.c_int, D, ctypes.c_int]
     L.krrt_edge_samples.argtypes = [P, D, D, D, ctypes.c_int, ctypes.c_int, D]
@@ -159,6 +163,35 @@ def _d(a):
 def _f64(a, shape=None):
     a = np.ascontiguousarray(a, dtype=np.float64)
     return a if shape is None else a.reshape(shape)
+
+
+class PinnedArray:
+    """numpy view of page-locked host memory (krrt_host_alloc); keep the object alive as long as the array is used"""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * self.dtype.itemsize
+        self.ptr = ctypes.c_void_p()
+        rc = lib().krrt_host_alloc(ctypes.byref(self.ptr), max(n, 1))
+        if rc != KRRT_OK:
+            raise KrrtError(rc, "krrt_host_alloc failed")
+        buf = (ctypes.c_ubyte * max(n, 1)).from_address(self.ptr.value)
+        self.array = np.frombuffer(buf, dtype=np.uint8, count=n).view(self.dtype).reshape(shape)
+
+    @classmethod
+    def like(cls, a):
+        p = cls(a.shape, a.dtype)
+        p.array[...] = a
+        return p
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                self.array = None
+                lib().krrt_host_free(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
 
 
 def default_config(**kw):
@@ -455,6 +488,12 @@ class Planner:
     @property
     def launch_count(self):
         return lib().krrt_launch_count(self.h)
+
+    def flush_l2(self):
+        self._ck(lib().krrt_flush_l2(self.h))
+
+    def synchronize(self):
+        self._ck(lib().krrt_synchronize(self.h))
 
     def timer_begin(self):
         self._ck(lib().krrt_timer_begin(self.h))

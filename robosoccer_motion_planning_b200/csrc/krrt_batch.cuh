@@ -46,116 +46,74 @@ constexpr int GOAL_MODE_TOLERANCE = 1;  // == KRRT_GOAL_TOLERANCE
 // would move it to local memory for the whole kernel)
 __device__ __forceinline__ State4 goal_load_state(const TreeView& T, int i) { return load_state(T, i); }
 
-constexpr int GOAL_NC = 8;  // offers a lane keeps in registers: trees of up to 32 x GOAL_NC + 1 nodes take the fast path
+constexpr int GOAL_NC = 8;  // offers a lane holds at a time: the tree is walked in blocks of 32 x GOAL_NC nodes
 
+// Every lane steers its nodes of a block once and keeps (cost through the node, edge duration, edge cost); the warp then
+// walks the block's offers in (cost, index) order — the order the sequential planner sorts them in — and tests one edge at a
+// time with all 32 lanes (S x m disc tests spread over the lanes) until one is free or none can beat the best free offer
+// of the earlier blocks.  Kept SMALL on purpose (one steer site, loops not unrolled, the per-lane lists in local memory):
+// the other warps of the CTA are in the planner's main loop, and this code shares the instruction cache with it.
 template <typename Tree>
 __device__ __noinline__ int warp_goal_connect(const Tree T, int n, const State4 goal, double r, const EnvView E,
                                               int* goal_parent) {
   const int lane = threadIdx.x & 31;
-  *goal_parent = -1;
-  if (n - 1 <= 32 * GOAL_NC) {
-    // Fast path.  Every lane steers its nodes once and keeps (cost through the node, arrival time of the edge); then the
-    // warp walks the offers in (cost, index) order — the order the sequential planner sorts them in — and tests one
-    // edge at a time with all 32 lanes (S x m disc tests spread over the lanes) until one is free.
-    double cand[GOAL_NC], tgv[GOAL_NC];
-#pragma unroll
+  double cand[GOAL_NC], tgv[GOAL_NC], cgv[GOAL_NC];
+  double best_c = INFINITY, best_tg = 0.0, best_cg = 0.0;  // cheapest free offer so far (warp-uniform)
+  int best_i = -1;
+  bool best_same = false;
+  for (int first = 1; first < n; first += 32 * GOAL_NC) {
+#pragma unroll 1
     for (int p = 0; p < GOAL_NC; ++p) {
-      cand[p] = INFINITY;
-      tgv[p] = 0.0;
-      if (1 + 32 * p < n) {  // (warp-uniform)
-        const int i = 1 + 32 * p + lane;
-        if (i < n) {
-          const State4 x = goal_load_state(T, i);
-          double tg = 0.0, cg = 0.0;
-          if (dist2(x, goal) != 0.0) steer(x, goal, r, tg, cg);
-          cand[p] = T.ctc[i] + cg;
-          tgv[p] = tg;
-        }
+      const int i = first + 32 * p + lane;
+      double tg = 0.0, cg = 0.0, c = INFINITY;
+      if (i < n) {
+        const State4 x = goal_load_state(T, i);
+        if (dist2(x, goal) != 0.0) steer(x, goal, r, tg, cg);
+        c = T.ctc[i] + cg;
       }
+      cand[p] = c;
+      tgv[p] = tg;
+      cgv[p] = cg;
     }
     for (;;) {
-      double bc = INFINITY, btg = 0.0;
+      double bc = INFINITY;
       int bp = -1;
-#pragma unroll
+#pragma unroll 1
       for (int p = 0; p < GOAL_NC; ++p)
         if (cand[p] < bc) {  // (strict: an equal cost keeps the lower index)
           bc = cand[p];
-          btg = tgv[p];
           bp = p;
         }
       double kc = bc;
-      int ki = bp >= 0 ? 1 + 32 * bp + lane : -1, kl = lane;
+      int ki = bp >= 0 ? first + 32 * bp + lane : -1, kl = lane;
       warp_argmin(kc, ki, kl);
-      if (ki < 0) return -1;
+      // nothing left in this block, or nothing left that beats the best free offer of the earlier blocks (lower indices)
+      if (ki < 0 || (best_i >= 0 && kc >= best_c)) break;
       const State4 x = goal_load_state(T, ki);
-      if (dist2(x, goal) == 0.0) {  // a node that coincides with the goal IS the goal node
-        *goal_parent = ki;
-        return ki;
+      const bool same = dist2(x, goal) == 0.0;  // a node that coincides with the goal offers a zero-length edge
+      const double tg = __shfl_sync(FULL, bp >= 0 ? tgv[bp] : 0.0, kl);
+      const double cg = __shfl_sync(FULL, bp >= 0 ? cgv[bp] : 0.0, kl);
+      if (same || !warp_edge_collide(x, goal, tg, T.tim[ki], E)) {
+        best_c = kc;
+        best_i = ki;
+        best_tg = tg;
+        best_cg = cg;
+        best_same = same;
+        break;
       }
-      const double tg = __shfl_sync(FULL, btg, kl);
-      if (!warp_edge_collide(x, goal, tg, T.tim[ki], E)) {
-        double t2, cg;
-        steer(x, goal, r, t2, cg);  // (the winner's edge cost once more: it was not kept)
-        if (lane == 0) {
-          T.pos[n] = make_double2(goal.x, goal.y);
-          T.vel[n] = make_double2(goal.vx, goal.vy);
-          T.ecost[n] = cg;
-          T.etime[n] = tg;
-          T.ctc[n] = kc;
-          T.tim[n] = T.tim[ki] + tg;
-        }
-        __syncwarp();
-        *goal_parent = ki;
-        return n;
-      }
-      if (lane == kl) {
-#pragma unroll
-        for (int p = 0; p < GOAL_NC; ++p)
-          if (p == bp) cand[p] = INFINITY;
-      }
+      if (lane == kl) cand[bp] = INFINITY;
     }
   }
-  // Big trees: every lane walks its nodes and tests the edges that can still win by itself.
-  double bc = INFINITY, btg = 0.0, bcg = 0.0;
-  int bi = -1, bsame = 0;
-  for (int b0 = 1; b0 < n; b0 += 32) {
-    const int i = b0 + lane;
-    if (i >= n) continue;
-    const State4 x = goal_load_state(T, i);
-    const bool same = dist2(x, goal) == 0.0;
-    double tg = 0.0, cg = 0.0;
-    if (!same) steer(x, goal, r, tg, cg);
-    const double cand = T.ctc[i] + cg;
-    if (bi >= 0 && cand >= bc) continue;  // (i only grows: an equal offer loses on the index)
-    bool hit = false;
-    if (!same && E.m > 0) {
-      const Edge e = make_edge(x, goal, tg, T.tim[i]);
-      for (int k = 0; k < E.S && !hit; ++k) {
-        const double h = (E.S > 1) ? (double)k / (double)(E.S - 1) : 0.0;
-        hit = edge_point_hits_any(e, h, E.obs, E.m, E.dynamic, E.R2);
-      }
-    }
-    if (!hit) {
-      bc = cand; bi = i; btg = tg; bcg = cg; bsame = same ? 1 : 0;
-    }
-  }
-  __syncwarp();
-  // (cost, index) arg-min over the lanes; the winner's lane hands out its edge
-  double kc = bc;
-  int ki = bi, kl = lane;
-  warp_argmin(kc, ki, kl);
-  *goal_parent = ki;
-  if (ki < 0) return -1;
-  const double tg = __shfl_sync(FULL, btg, kl), cg = __shfl_sync(FULL, bcg, kl);
-  const int same = __shfl_sync(FULL, bsame, kl);
-  if (same) return ki;
+  *goal_parent = best_i;
+  if (best_i < 0) return -1;
+  if (best_same) return best_i;  // ... and IS the goal node when it wins
   if (lane == 0) {
     T.pos[n] = make_double2(goal.x, goal.y);
     T.vel[n] = make_double2(goal.vx, goal.vy);
-    T.ecost[n] = cg;
-    T.etime[n] = tg;
-    T.ctc[n] = kc;
-    T.tim[n] = T.tim[ki] + tg;
+    T.ecost[n] = best_cg;
+    T.etime[n] = best_tg;
+    T.ctc[n] = best_c;
+    T.tim[n] = T.tim[best_i] + best_tg;
   }
   __syncwarp();
   return n;

@@ -54,6 +54,8 @@ struct krrt_ctx {
   long long phase_n[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   double* d_user = nullptr;
   size_t user_cap = 0;
+  void* d_flush = nullptr;     // krrt_flush_l2
+  size_t flush_bytes = 0;
   unsigned char* arena = nullptr;
   size_t arena_bytes = 0, arena_used = 0;
 
@@ -171,6 +173,7 @@ void krrt_destroy(krrt_ctx* ctx) {
   for (void* p : ctx->d_scratch)
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
+  if (ctx->d_flush) cudaFree(ctx->d_flush);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
   if (ctx->d_redo) cudaFree(ctx->d_redo);
   if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
@@ -347,6 +350,33 @@ int krrt_create(const krrt_config* c, krrt_ctx** out) {
     return rc;
   }
   *out = ctx;
+  return KRRT_OK;
+}
+
+int krrt_host_alloc(void** p, uint64_t bytes) {
+  if (!p) return KRRT_ERR_INVALID;
+  *p = nullptr;
+  return cudaHostAlloc(p, bytes > 0 ? (size_t)bytes : 1, cudaHostAllocDefault) == cudaSuccess ? KRRT_OK : KRRT_ERR_CUDA;
+}
+
+int krrt_host_free(void* p) { return (!p || cudaFreeHost(p) == cudaSuccess) ? KRRT_OK : KRRT_ERR_CUDA; }
+
+int krrt_flush_l2(krrt_ctx* ctx) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  if (!ctx->d_flush) {
+    ctx->flush_bytes = std::max<size_t>(2 * (size_t)ctx->prop.l2CacheSize, (size_t)256 << 20);
+    CK(cudaMalloc(&ctx->d_flush, ctx->flush_bytes));
+  }
+  CK(cudaMemsetAsync(ctx->d_flush, 0, ctx->flush_bytes, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return KRRT_OK;
+}
+
+int krrt_synchronize(krrt_ctx* ctx) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaStreamSynchronize(ctx->stream));
   return KRRT_OK;
 }
 

@@ -33,7 +33,7 @@ struct Dev {
   int device = 0, rank = 0;
   krrt_ctx* ctx = nullptr;
   cudaStream_t s_plan = nullptr, s_xfer = nullptr;
-  cudaEvent_t e0 = nullptr, e1 = nullptr, e_plan = nullptr, e_xfer = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr, e_plan = nullptr, e_xfer = nullptr, e_load = nullptr, e_res = nullptr;
   ncclComm_t comm = nullptr;
   double *d_starts = nullptr, *d_goals = nullptr, *d_obs = nullptr;
   unsigned char *d_out = nullptr, *d_all = nullptr;  // this GPU's (padded) block of records / the gathered array
@@ -57,7 +57,8 @@ struct krrt_mgpu {
   // the loaded sweep
   int q = 0, m = 0, pad = 0, n_chunks = 0;
   size_t in_cap = 0, obs_cap = 0, rec_cap = 0, done_cap = 0;
-  bool ran = false, overlapped = false;
+  bool ran = false, overlapped = false, have_results = false;
+  double last_run_ms = 0.0;
   int nccl_version = 0;
 };
 
@@ -163,6 +164,8 @@ void krrt_mgpu_destroy(krrt_mgpu* mg) {
     if (d.e1) cudaEventDestroy(d.e1);
     if (d.e_plan) cudaEventDestroy(d.e_plan);
     if (d.e_xfer) cudaEventDestroy(d.e_xfer);
+    if (d.e_load) cudaEventDestroy(d.e_load);
+    if (d.e_res) cudaEventDestroy(d.e_res);
     if (d.s_plan) cudaStreamDestroy(d.s_plan);
     if (d.s_xfer) cudaStreamDestroy(d.s_xfer);
   }
@@ -196,6 +199,8 @@ static int init_devices(krrt_mgpu* mg, const ncclUniqueId* id) {
     MCK(cudaStreamCreateWithPriority(&d.s_xfer, cudaStreamNonBlocking, hi_p));
     MCK(cudaEventCreate(&d.e0));
     MCK(cudaEventCreate(&d.e1));
+    MCK(cudaEventCreate(&d.e_load));
+    MCK(cudaEventCreate(&d.e_res));
     MCK(cudaEventCreateWithFlags(&d.e_plan, cudaEventDisableTiming));
     MCK(cudaEventCreateWithFlags(&d.e_xfer, cudaEventDisableTiming));
     MCK(cudaMalloc((void**)&d.d_red, sizeof(double) * 16));
@@ -408,6 +413,7 @@ int krrt_sweep_load(krrt_mgpu* mg, const double* starts, const double* goals, co
   }
   for (Dev& d : mg->devs) {
     MCK(cudaSetDevice(d.device));
+    MCK(cudaEventRecord(d.e_load, d.s_plan));
     int lo, hi;
     krrt_mgpu_shard(q, d.rank, mg->world, &lo, &hi);
     const size_t n = (size_t)(hi - lo);
@@ -426,6 +432,7 @@ int krrt_sweep_load(krrt_mgpu* mg, const double* starts, const double* goals, co
   mg->pad = pad;
   mg->n_chunks = n_chunks;
   mg->ran = false;
+  mg->have_results = false;
   return KRRT_OK;
 }
 
@@ -493,6 +500,7 @@ int krrt_sweep_run(krrt_mgpu* mg, int dynamic, int n_iter, uint32_t query_base, 
     ms_max = std::max(ms_max, (double)ms);
   }
   if (device_ms) *device_ms = ms_max;
+  mg->last_run_ms = ms_max;
   mg->ran = true;
   mg->overlapped = overlap;
   return KRRT_OK;
@@ -515,7 +523,25 @@ int krrt_sweep_results(krrt_mgpu* mg, krrt_result* out) {
           MCK(cudaMemcpyAsync(out + glob, d.d_all + (size_t)off * ITEM, (size_t)cnt * ITEM, cudaMemcpyDeviceToHost, d.s_plan));
       }
   }
+  MCK(cudaEventRecord(d.e_res, d.s_plan));
   MCK(cudaStreamSynchronize(d.s_plan));
+  mg->have_results = true;
+  return KRRT_OK;
+}
+
+int krrt_sweep_last_timing(krrt_mgpu* mg, double* run_ms, double* e2e_ms) {
+  if (!mg) return KRRT_ERR_INVALID;
+  if (run_ms) *run_ms = mg->last_run_ms;
+  if (e2e_ms) {
+    *e2e_ms = 0.0;
+    if (mg->have_results) {
+      Dev& d = mg->devs[0];
+      MCK(cudaSetDevice(d.device));
+      float ms = 0.f;
+      MCK(cudaEventElapsedTime(&ms, d.e_load, d.e_res));
+      *e2e_ms = ms;
+    }
+  }
   return KRRT_OK;
 }
 

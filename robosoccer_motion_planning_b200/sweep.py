@@ -27,7 +27,7 @@ EXPORTS = (
     "krrt_mgpu_create", "krrt_mgpu_unique_id", "krrt_mgpu_create_rank", "krrt_mgpu_destroy", "krrt_mgpu_last_error",
     "krrt_mgpu_info", "krrt_mgpu_shard", "krrt_mgpu_chunk_layout", "krrt_sweep_multi_gpu", "krrt_sweep_load",
     "krrt_sweep_run", "krrt_sweep_results", "krrt_sweep_stats", "krrt_mgpu_launch_count", "krrt_sweep_overlap",
-    "krrt_mgpu_barrier", "krrt_mgpu_max",
+    "krrt_mgpu_barrier", "krrt_mgpu_max", "krrt_sweep_last_timing",
 )
 
 _lib = None
@@ -65,6 +65,7 @@ def lib():
     L.krrt_mgpu_launch_count.argtypes = [P]
     L.krrt_mgpu_launch_count.restype = ctypes.c_int64
     L.krrt_sweep_overlap.argtypes = [P, I, I]
+    L.krrt_sweep_last_timing.argtypes = [P, D, D]
     L.krrt_mgpu_barrier.argtypes = [P]
     L.krrt_mgpu_max.argtypes = [P, D]
     _lib = L
@@ -224,6 +225,11 @@ class Sweep:
         s = KrrtStats()
         self._ck(lib().krrt_sweep_stats(self.h, ctypes.byref(s)))
         return {n: getattr(s, n) for n, _ in KrrtStats._fields_}
+
+    def last_timing(self):
+        a, b = ctypes.c_double(0.0), ctypes.c_double(0.0)
+        self._ck(lib().krrt_sweep_last_timing(self.h, ctypes.byref(a), ctypes.byref(b)))
+        return {"run_ms": a.value, "e2e_ms": b.value}
 
     def overlap(self):
         a, b = ctypes.c_int32(0), ctypes.c_int32(0)
