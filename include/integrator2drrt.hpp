@@ -33,10 +33,13 @@
 
 namespace Kinodynamic {
 
+// s(i) and s[i] both work (elements.hpp:15-29 uses [i], the node (i)).  On an rvalue s(i) is a VALUE: the caller forms
+// std::array<decltype(std::declval<State>()(0)), 2> (…node.cpp:300-301), which must be an array of double, not of double&.
 template <size_t N>
 struct StateN : std::array<double, N> {
-  const double& operator()(size_t i) const { return (*this)[i]; }
-  double& operator()(size_t i) { return (*this)[i]; }
+  const double& operator()(size_t i) const& { return (*this)[i]; }
+  double& operator()(size_t i) & { return (*this)[i]; }
+  double operator()(size_t i) && { return (*this)[i]; }
 };
 using State4 = StateN<4>;     // (x, y, vx, vy)
 using StateTime = StateN<5>;  // (x, y, vx, vy, t)

@@ -46,7 +46,7 @@ struct krrt_ctx {
   int wave_enabled = 1;       // KRRT_WAVE=0 in the environment forces the in-order commit (debugging / A-B timing)
   int wave_min_n = 32;        // trees smaller than this commit in order (conflicts everywhere; profiles/r1_param_sweep.txt)
   int small_max_n = 256;      // few-expansion calls on trees below this: one CTA, plain launch, in-order commit
-  int grow_grid = 0;          // CTAs of the persistent k_grow (one per SM, all co-resident)
+  int grow_grid = 0;          // CTAs of the persistent k_grow (KRRT_GROW_MINB per SM, all co-resident)
   GridBar* d_bar = nullptr;    // its two grid barriers
   GridIndex gi{};              // spatial index of its neighbour scan
   GoalScratch goal_scr{};      // partials of k_goal_connect
@@ -308,7 +308,11 @@ static int create_impl(krrt_ctx* ctx) {
     int coop = 0;
     CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c.device));
     REQUIRE(per_sm >= 1 && coop, KRRT_ERR_UNSUPPORTED, "k_grow does not fit one CTA per SM / no cooperative launch");
-    ctx->grow_grid = ctx->prop.multiProcessorCount;
+    // every co-resident CTA the kernel's footprint allows (KRRT_GROW_MINB per SM: 128 registers, ~110 KB of shared memory):
+    // a sub-round decides one sample per CTA, so twice the CTAs is twice the prefix a sub-round can commit
+    int per = std::min(per_sm, KRRT_GROW_MINB);
+    if (const char* e = std::getenv("KRRT_GROW_PER_SM")) per = std::max(1, std::min(per, std::atoi(e)));
+    ctx->grow_grid = per * ctx->prop.multiProcessorCount;
     if (const char* e = std::getenv("KRRT_GRID")) ctx->grow_grid = std::max(2, std::min(ctx->grow_grid, std::atoi(e)));
   }
   Params& P = ctx->P;

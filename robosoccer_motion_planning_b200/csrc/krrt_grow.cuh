@@ -41,6 +41,9 @@
 namespace krrt {
 
 constexpr int GROW_THREADS = 256;
+#ifndef KRRT_GROW_MINB
+#define KRRT_GROW_MINB 2   // CTAs of k_grow per SM the register allocation is held to (128 registers: 264 B of spills)
+#endif
 constexpr int GROW_WMAX = 1024;   // window cap
 constexpr int GROW_LEVELS = 62;   // BFS depth below the rewired nodes that the parallel path handles
 constexpr int GROW_SEQ_WINDOW = 64;
@@ -366,7 +369,7 @@ __device__ __forceinline__ void clear_window(const Batch& Bt) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,
+__global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,
                                                             GrowCfg cfg) {
   extern __shared__ __align__(16) unsigned char dyn_raw[];
   GrowShared& sm = *reinterpret_cast<GrowShared*>(dyn_raw);
@@ -696,7 +699,8 @@ __global__ void __launch_bounds__(GROW_THREADS, 1) k_grow(Ctl* ctl, Params P, Tr
     for (int j = t; j < P.m; j += GROW_THREADS) sm.obs[j] = P.obs[j];
     // the CTAs that take part in this window's sub-rounds: enough for twice the prefixes seen lately + the last CTA;
     // the others go straight to the window's end and doze there
-    const int Pn = min(G - 1, max(cfg.pn_min, (cfg.pn_mul * ema_win) / 16 + cfg.pn_add));
+    // (at most GROW_THREADS - 1 of them: validation looks at the earlier samples of the sub-round one thread each)
+    const int Pn = min(min(G - 1, GROW_THREADS - 1), max(cfg.pn_min, (cfg.pn_mul * ema_win) / 16 + cfg.pn_add));
     const bool takes_part = cta < Pn || last;
     // the set changes from window to window: pick the barrier's counters up where they stood before the window's barrier
     bs_sub.arrived = sub_base;

@@ -67,3 +67,43 @@ def test_custom_benchmark_runs(gpu_required):
     last = [w for w in rows if w[0] == "0.50" and w[1] == "200"][0]
     assert int(last[5].split("/")[0]) >= 6 and float(last[7]) > 0.0
     assert float(last[8]) > float(last[6])                     # trials differ (one sample stream per trial)
+
+
+def test_benchmark_builds_and_fails_loudly_without_gpu():
+    exe = native_build.build_benchmark()
+    from robosoccer_motion_planning_b200 import capi
+    if capi.lib().krrt_device_count() > 0:
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_benchmark_runs(gpu_required):
+    """The reference's `rrtstar_benchmark` (README.md:34-37): google-benchmark conventions, config 1 of BASELINE.json."""
+    import json
+    exe = native_build.build_benchmark()
+    r = subprocess.run([exe, "--benchmark_min_time=0.05", "--benchmark_format=json"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    b = {x["name"]: x for x in json.loads(r.stdout)["benchmarks"]}
+    assert len(b) == 9 and b["BM_RRTStarInt2D/10000"]["solved"] == 1 and b["BM_RRTStarInt2D/10000"]["nodes"] > 5000
+    assert all(x["iterations"] >= 3 and x["real_time"] > 0 for x in b.values())
+    # one plan of 75 iterations and the caller's 75 single calls grow the same tree
+    assert b["BM_RRTStarInt2D/75"]["nodes"] == b["BM_RRTStarInt2D_PerCall/75"]["nodes"]
+    assert b["BM_RRTStarInt2D/75"]["cost"] == b["BM_RRTStarInt2D_PerCall/75"]["cost"]
+
+
+def test_cmake_package_builds():
+    """CMakeLists.txt + package.xml of the `rrtstar` package: plain CMake builds both libraries and both tools, and the
+    library exports the C ABI."""
+    import ctypes
+    import os
+    d = native_build.build_cmake_package()
+    if d is None:
+        pytest.skip("cmake not installed")
+    for f in ("libkrrt.so", "libkrrt_mgpu.so", "rrtstar_benchmark", "rrtstar_custom_benchmark"):
+        assert os.path.exists(os.path.join(d, f)), f
+    L = ctypes.CDLL(os.path.join(d, "libkrrt.so"))
+    from robosoccer_motion_planning_b200 import capi
+    for name in capi.EXPORTS:
+        assert hasattr(L, name), name
