@@ -63,7 +63,11 @@ enum { KRRT_GOAL_CONNECT = 0, KRRT_GOAL_TOLERANCE = 1 };
 
 typedef struct krrt_config {
   int32_t device;     /* CUDA device ordinal                                                 */
-  int32_t precision;  /* KRRT_F64 (bit-exact with the oracle). KRRT_F32 -> KRRT_ERR_UNSUPPORTED for now */
+  int32_t precision;  /* KRRT_F64: binary64 throughout, as the reference (robotsubscriber.h:14), bit-exact with the CPU checker.
+                         KRRT_F32: binary32 states, steering and collision tests for krrt_plan_batch*, krrt_steer_cost and
+                         krrt_edge_collide (the same kernels compiled in float, bit-exact with the checker's float build; costs and
+                         times within 1e-4 of binary64 on the same edge); arrays at this interface stay binary64.  The single-tree
+                         planner (krrt_set_start / krrt_grow / tree read-outs) is binary64 only: KRRT_ERR_UNSUPPORTED on such a context */
   int32_t capacity;   /* max tree nodes                                                      */
   int32_t S;          /* samples per edge for collision checks, both end points included     */
   double r;           /* input weight of J = int (1 + r|u|^2) dt; solver.set_weight(r) (…node.cpp:91-92) */

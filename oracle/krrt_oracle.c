@@ -7,19 +7,33 @@
  * every fused multiply-add written explicitly, everything else evaluated in
  * the written order.  Build with -ffp-contract=off (see oracle/Makefile).
  */
-#include "krrt_oracle.h"
-
 #include <math.h>
 #include <pthread.h>
+#include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+
+/* The binary32 build (oracle/Makefile: libkrrt_oracle_f32.so, the checker of KRRT_F32 contexts) is THIS source with
+ * every `double` replaced by `float`: -DKO_F32 below, gcc -fsingle-precision-constant for the literals, <tgmath.h> so
+ * that fma / sqrt / fabs / log on float operands are the float functions.  Its interface is float throughout
+ * (tests/oracle_binding.py builds a second set of ctypes structures for it). */
+#ifdef KO_F32
+#include <tgmath.h>
+#define double float
+#endif
+
+#include "krrt_oracle.h"
 
 #define KO_MAX_NEWTON 100
 /* Newton on f' converges only linearly (ratio 1/2) when its two positive roots nearly coincide: 48 steps = 2^-48 */
 #define KO_MAX_STATIONARY 48
 /* relative step below which a Newton iteration has converged: a few ulp.  Without it the iteration dithers by
  * +-1 ulp around the root for ~20 more steps (the rounding noise of f is of the order of one step). */
+#ifdef KO_F32
+#define KO_XTOL 5e-7 /* == KRRT_XTOL of the kernels' binary32 build */
+#else
 #define KO_XTOL 1e-15
+#endif
 
 /* ------------------------------------------------------------------ */
 /* Steering: tau^4 - a tau^2 + b tau - c0 = 0, SURVEY.md §8-M          */

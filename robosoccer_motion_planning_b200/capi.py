@@ -18,6 +18,7 @@ KRRT_MAX_OBS = 64
 KRRT_MAX_WAYPOINTS = 32
 KRRT_OK, KRRT_ERR_INVALID, KRRT_ERR_CUDA, KRRT_ERR_NO_DEVICE, KRRT_ERR_NEAR_OVERFLOW, KRRT_ERR_STATE, \
     KRRT_ERR_UNSUPPORTED = range(7)
+KRRT_F64, KRRT_F32 = 0, 1   # krrt_config.precision
 
 D = ctypes.POINTER(ctypes.c_double)
 I = ctypes.POINTER(ctypes.c_int32)

@@ -8,22 +8,22 @@
 
 namespace krrt {
 
-struct ResultRec {  // layout == krrt_result (include/krrt.h)
+struct ResultRec {  // layout == krrt_result (include/krrt.h): binary64 in both precisions (krrt_real.cuh)
   int solved, goal_index, n_nodes, path_len;
-  double cost, time;
-  double waypoints[32][5];
+  krrt_io_real cost, time;
+  krrt_io_real waypoints[32][5];
 };
 
 struct BatchJob {
-  const double* starts;     // q x 4
-  const double* goals;      // q x 4
-  const double* obstacles;  // q x m x 4
+  const krrt_io_real* starts;     // q x 4   (inputs and the radius table are binary64 in both precisions: rounded to the
+  const krrt_io_real* goals;      // q x 4    arithmetic type when loaded)
+  const krrt_io_real* obstacles;  // q x m x 4
   ResultRec* out;           // q
   int* next_query;          // work counter
   const int* list;          // when set: plan only the queries list[0 .. *list_count) (k_plan_batch2's redo list)
   const int* list_count;
   long long* stats;         // [10] accumulated over queries
-  const double* rho2;       // [cap + 1]
+  const krrt_io_real* rho2;       // [cap + 1]
   int q, m, dynamic, n_iter, cap;  // cap: most nodes a tree can hold; the arrays have cap + 1 slots (goal node)
   uint32_t query_base;
   double r, R2, goal_tol2;
@@ -58,17 +58,17 @@ __device__ __noinline__ int warp_goal_connect(const Tree T, int n, const State4 
                                               int* goal_parent) {
   const int lane = threadIdx.x & 31;
   double cand[GOAL_NC], tgv[GOAL_NC], cgv[GOAL_NC];
-  double best_c = INFINITY, best_tg = 0.0, best_cg = 0.0;  // cheapest free offer so far (warp-uniform)
+  double best_c = INFINITY, best_tg = KR(0.0), best_cg = KR(0.0);  // cheapest free offer so far (warp-uniform)
   int best_i = -1;
   bool best_same = false;
   for (int first = 1; first < n; first += 32 * GOAL_NC) {
 #pragma unroll 1
     for (int p = 0; p < GOAL_NC; ++p) {
       const int i = first + 32 * p + lane;
-      double tg = 0.0, cg = 0.0, c = INFINITY;
+      double tg = KR(0.0), cg = KR(0.0), c = INFINITY;
       if (i < n) {
         const State4 x = goal_load_state(T, i);
-        if (dist2(x, goal) != 0.0) steer(x, goal, r, tg, cg);
+        if (dist2(x, goal) != KR(0.0)) steer(x, goal, r, tg, cg);
         c = T.ctc[i] + cg;
       }
       cand[p] = c;
@@ -90,9 +90,9 @@ __device__ __noinline__ int warp_goal_connect(const Tree T, int n, const State4 
       // nothing left in this block, or nothing left that beats the best free offer of the earlier blocks (lower indices)
       if (ki < 0 || (best_i >= 0 && kc >= best_c)) break;
       const State4 x = goal_load_state(T, ki);
-      const bool same = dist2(x, goal) == 0.0;  // a node that coincides with the goal offers a zero-length edge
-      const double tg = __shfl_sync(FULL, bp >= 0 ? tgv[bp] : 0.0, kl);
-      const double cg = __shfl_sync(FULL, bp >= 0 ? cgv[bp] : 0.0, kl);
+      const bool same = dist2(x, goal) == KR(0.0);  // a node that coincides with the goal offers a zero-length edge
+      const double tg = __shfl_sync(FULL, bp >= 0 ? tgv[bp] : KR(0.0), kl);
+      const double cg = __shfl_sync(FULL, bp >= 0 ? cgv[bp] : KR(0.0), kl);
       if (same || !warp_edge_collide(x, goal, tg, T.tim[ki], E)) {
         best_c = kc;
         best_i = ki;
@@ -130,9 +130,9 @@ __device__ __forceinline__ void batch_query_done(const BatchJob& J, int qi) {
 __host__ __device__ inline size_t batch_warp_smem_bytes(int cap, int m) {
   cap += 1;  // the goal node's slot
   size_t b = 0;
-  b += (size_t)cap * 16 * 2;                        // pos, vel
-  b += (size_t)(m > 0 ? m : 1) * 32;                // obstacles
-  b += (size_t)cap * 8 * 8;                         // ctc, tim, ecost, etime, cf, tf, cb, tb
+  b += (size_t)cap * sizeof(double2) * 2;           // pos, vel
+  b += (size_t)(m > 0 ? m : 1) * sizeof(double4);   // obstacles
+  b += (size_t)cap * sizeof(double) * 8;            // ctc, tim, ecost, etime, cf, tf, cb, tb
   b += (size_t)cap * 4 * 6;                         // link (first child, next sibling), parent, prev, queue, near idx
   b += ((size_t)cap + 15) / 16 * 16;                // tried
   return (b + 15) / 16 * 16;
@@ -175,18 +175,18 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
     if (qi >= n_work) break;
     if (J.list) qi = J.list[qi];
     const uint32_t query_id = J.query_base + (uint32_t)qi;
-    const double* gs = J.goals + 4 * (size_t)qi;
-    const double* xs = J.starts + 4 * (size_t)qi;
-    const State4 goal = {gs[0], gs[1], gs[2], gs[3]};
+    const krrt_io_real* gs = J.goals + 4 * (size_t)qi;
+    const krrt_io_real* xs = J.starts + 4 * (size_t)qi;
+    const State4 goal = {(double)gs[0], (double)gs[1], (double)gs[2], (double)gs[3]};
     for (int j = lane; j < J.m; j += 32) {
-      const double* o = J.obstacles + ((size_t)qi * J.m + j) * 4;
-      s_obs[j] = make_double4(o[0], o[1], o[2], o[3]);
+      const krrt_io_real* o = J.obstacles + ((size_t)qi * J.m + j) * 4;
+      s_obs[j] = make_double4((double)o[0], (double)o[1], (double)o[2], (double)o[3]);
     }
     if (lane == 0) {
-      T.pos[0] = make_double2(xs[0], xs[1]);
-      T.vel[0] = make_double2(xs[2], xs[3]);
+      T.pos[0] = make_double2((double)xs[0], (double)xs[1]);
+      T.vel[0] = make_double2((double)xs[2], (double)xs[3]);
       T.parent[0] = -1;
-      T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
+      T.ctc[0] = KR(0.0); T.tim[0] = KR(0.0); T.ecost[0] = KR(0.0); T.etime[0] = KR(0.0);
       T.link[0] = make_int2(-1, -1); T.prev[0] = -1;
     }
     __syncwarp();
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
         continue;
       }
       if (n >= J.cap) break;
-      const double rho2n = J.rho2[n];
+      const double rho2n = (double)J.rho2[n];
       // near set (ascending by construction) + nearest + duplicate detection
       int K = 0;
       bool dup = false;
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
             bi = i;
           }
           valid = d <= rho2n;
-          dup |= d == 0.0;
+          dup |= d == KR(0.0);
         }
         unsigned mk = __ballot_sync(FULL, valid);
         if (valid) N.idx[K + __popc(mk & ((1u << lane) - 1))] = i;
@@ -264,8 +264,8 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       __syncwarp();
     }
     ResultRec* R = J.out + qi;
-    double* wp = &R->waypoints[0][0];
-    for (int k = lane; k < 32 * 5; k += 32) wp[k] = 0.0;
+    krrt_io_real* wp = &R->waypoints[0][0];
+    for (int k = lane; k < 32 * 5; k += 32) wp[k] = KR(0.0);
     __syncwarp();
     if (lane == 0) {
       R->solved = gi >= 0;
@@ -274,8 +274,8 @@ __global__ void __launch_bounds__(256) k_plan_batch(BatchJob J) {
       int len = 0;
       for (int i = gi; i >= 0 && len <= n; i = T.parent[i]) ++len;
       R->path_len = len;
-      R->cost = gi >= 0 ? T.ctc[gi] : 0.0;
-      R->time = gi >= 0 ? T.tim[gi] : 0.0;
+      R->cost = gi >= 0 ? T.ctc[gi] : KR(0.0);
+      R->time = gi >= 0 ? T.tim[gi] : KR(0.0);
       int p = len - 1;
       for (int i = gi; i >= 0 && p >= 0; i = T.parent[i], --p) {
         if (p < 32) {

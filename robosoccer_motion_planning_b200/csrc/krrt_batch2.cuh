@@ -24,7 +24,16 @@ constexpr unsigned B2_NIL = 0xffffu;
 constexpr int B2_SLOTS = 2;          // near candidates per lane (registers)
 constexpr int B2_KMAX = 32 * B2_SLOTS;
 constexpr int B2_HMAX = 64;          // edge sample counts up to this use the table of h = k / (S - 1)
-constexpr int B2_MAX_WARPS = 16;
+#ifdef KRRT_F32_BUILD
+#ifndef KRRT_B2_MAX_WARPS_F32
+#define KRRT_B2_MAX_WARPS_F32 20   // 42 B per node: 26 warps of 200-node trees would fit; measured 16 / 20 / 24 / 32: 2.44 / 2.49 / 2.34 / 2.25 M
+                                   // queries/s on C4 (profiles/r2_c4_warps_s4.txt) - a warp is a latency chain, more of them share the issue slots
+#endif
+#define KRRT_B2_MAX_WARPS KRRT_B2_MAX_WARPS_F32
+#else
+#define KRRT_B2_MAX_WARPS 16
+#endif
+constexpr int B2_MAX_WARPS = KRRT_B2_MAX_WARPS;
 
 struct Batch2Job {
   BatchJob b;        // inputs, outputs, parameters (next_query / stats as in k_plan_batch)
@@ -50,9 +59,9 @@ struct B2Tree {
 __host__ __device__ inline size_t batch2_warp_smem_bytes(int cap, int m) {
   cap += 1;  // the goal node's slot
   size_t b = 0;
-  b += (size_t)cap * 16 * 2;                            // pos, vel
-  b += (size_t)cap * 8 * 4;                             // ctc, tim, ecost, etime
-  b += (size_t)(m > 0 ? m : 1) * 32;                    // obstacles
+  b += (size_t)cap * sizeof(double2) * 2;               // pos, vel
+  b += (size_t)cap * sizeof(double) * 4;                // ctc, tim, ecost, etime
+  b += (size_t)(m > 0 ? m : 1) * sizeof(double4);       // obstacles
   b += (((size_t)cap + 7) / 8 * 8) * 2 * 5;             // child, sib, parent, prev, scr (each 16-byte aligned)
   return (b + 15) / 16 * 16;
 }
@@ -65,6 +74,22 @@ __device__ __forceinline__ State4 b2_state(const B2Tree& T, int i) {
 
 __device__ __forceinline__ State4 goal_load_state(const B2Tree& T, int i) { return b2_state(T, i); }
 
+#ifdef KRRT_F32_BUILD
+// binary32 build: the key is one word — two REDUX + one ballot
+__device__ __forceinline__ unsigned b2_key(double x) {
+  const unsigned u = __float_as_uint(x);
+  return (u >> 31) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ unsigned b2_argmin(bool have, double key, unsigned idx, int& owner) {
+  const unsigned kb = have ? b2_key(key) : 0xffffffffu;
+  const unsigned mk = __reduce_min_sync(FULL, kb);
+  const bool top = have && kb == mk;
+  const unsigned mn = __reduce_min_sync(FULL, top ? idx : 0xffffffffu);
+  const unsigned own = __ballot_sync(FULL, top && idx == mn);
+  owner = own ? (__ffs(own) - 1) : 0;
+  return mn;
+}
+#else
 // order-preserving map of a double onto an unsigned 64-bit key (total order of the finite values and infinities)
 __device__ __forceinline__ unsigned long long b2_key(double x) {
   const unsigned long long u = (unsigned long long)__double_as_longlong(x);
@@ -84,6 +109,7 @@ __device__ __forceinline__ unsigned b2_argmin(bool have, double key, unsigned id
   owner = own ? (__ffs(own) - 1) : 0;
   return mn;
 }
+#endif
 
 // lane -> (sample point, obstacle group) map of the edge test
 struct B2Lanes {
@@ -110,7 +136,7 @@ __device__ __forceinline__ bool b2_edge_collide(const State4& a, const State4& b
   bool hit = false;
   if (L.k0 >= 0) {
     for (int k = L.k0; k < E.S; k += L.kstep) {
-      const double h = E.S <= B2_HMAX ? s_h[k] : ((E.S > 1) ? (double)k / (double)(E.S - 1) : 0.0);
+      const double h = E.S <= B2_HMAX ? s_h[k] : ((E.S > 1) ? (double)k / (double)(E.S - 1) : KR(0.0));
       const double px = axis_pos(e.kx, h), py = axis_pos(e.ky, h);
       const double t = e.t0 + e.tau * h;
       for (int j = L.g; j < E.m; j += L.G) {
@@ -186,7 +212,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
   const BatchJob& J = JJ.b;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ double s_h[B2_HMAX];
-  for (int k = threadIdx.x; k < B2_HMAX; k += blockDim.x) s_h[k] = (J.S > 1) ? (double)k / (double)(J.S - 1) : 0.0;
+  for (int k = threadIdx.x; k < B2_HMAX; k += blockDim.x) s_h[k] = (J.S > 1) ? (double)k / (double)(J.S - 1) : KR(0.0);
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -218,15 +244,15 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
     if (qi >= J.q) break;
     const uint32_t query_id = J.query_base + (uint32_t)qi;
     for (int j = lane; j < J.m; j += 32) {
-      const double* o = J.obstacles + ((size_t)qi * J.m + j) * 4;
-      s_obs[j] = make_double4(o[0], o[1], o[2], o[3]);
+      const krrt_io_real* o = J.obstacles + ((size_t)qi * J.m + j) * 4;
+      s_obs[j] = make_double4((double)o[0], (double)o[1], (double)o[2], (double)o[3]);
     }
     if (lane == 0) {
-      const double* xs = J.starts + 4 * (size_t)qi;
-      T.pos[0] = make_double2(xs[0], xs[1]);
-      T.vel[0] = make_double2(xs[2], xs[3]);
+      const krrt_io_real* xs = J.starts + 4 * (size_t)qi;
+      T.pos[0] = make_double2((double)xs[0], (double)xs[1]);
+      T.vel[0] = make_double2((double)xs[2], (double)xs[3]);
       T.parent[0] = (unsigned short)B2_NIL;
-      T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
+      T.ctc[0] = KR(0.0); T.tim[0] = KR(0.0); T.ecost[0] = KR(0.0); T.etime[0] = KR(0.0);
       T.child[0] = (unsigned short)B2_NIL; T.sib[0] = (unsigned short)B2_NIL; T.prev[0] = (unsigned short)B2_NIL;
     }
     __syncwarp();
@@ -239,8 +265,8 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       // the next 32 samples, one per lane
       State4 mine;
       {
-        const double* gs = J.goals + 4 * (size_t)qi;
-        const State4 goal = {gs[0], gs[1], gs[2], gs[3]};
+        const krrt_io_real* gs = J.goals + 4 * (size_t)qi;
+        const State4 goal = {(double)gs[0], (double)gs[1], (double)gs[2], (double)gs[3]};
         mine = draw_sample(J.sp, query_id, (uint64_t)(it0 + lane), true, goal);
       }
       const int lim = min(32, J.n_iter - it0);
@@ -259,7 +285,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
           full = true;
           break;
         }
-        const double rho2n = J.rho2[n];
+        const double rho2n = (double)J.rho2[n];
         // near set (ascending by construction) + nearest + duplicate detection
         int K = 0;
         bool dup = false;
@@ -275,7 +301,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
               bi = i;
             }
             valid = d <= rho2n;
-            dup |= d == 0.0;
+            dup |= d == KR(0.0);
           }
           const unsigned mk = __ballot_sync(FULL, valid);
           if (valid) T.scr[K + __popc(mk & lt_mask)] = (unsigned short)i;
@@ -299,7 +325,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
         // this lane's candidates: k = lane and lane + 32 of the near list
         const int ci0 = lane < K ? (int)T.scr[lane] : -1;
         const int ci1 = lane + 32 < K ? (int)T.scr[lane + 32] : -1;
-        double cf0 = 0.0, tf0 = 0.0, cb0 = 0.0, tb0 = 0.0, cf1 = 0.0, tf1 = 0.0, cb1 = 0.0, tb1 = 0.0;
+        double cf0 = KR(0.0), tf0 = KR(0.0), cb0 = KR(0.0), tb0 = KR(0.0), cf1 = KR(0.0), tf1 = KR(0.0), cb1 = KR(0.0), tb1 = KR(0.0);
         // both steering directions of every near node: 2K independent tasks over the lanes (task t < K: node -> sample of
         // candidate t; task t >= K: sample -> node of candidate t - K), ONE call site so the lanes iterate Newton together;
         // a backward result is handed to the lane that owns the candidate by a shuffle
@@ -308,7 +334,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
           const int t = lane + 32 * p;
           const bool valid = t < 2 * K;
           const bool fwd = t < K;
-          double tau = 0.0, c = 0.0;
+          double tau = KR(0.0), c = KR(0.0);
           if (valid) {
             const State4 x = b2_state(T, T.scr[fwd ? t : t - K]);
             steer(fwd ? x : s, fwd ? s : x, J.r, tau, c);
@@ -331,7 +357,7 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
         c_steer += K;
         // parent = arg-min over collision-free candidates of ctc[i] + c*(i -> new); lowest index on ties
         int par = -1;
-        double cfp = 0.0, tfp = 0.0;
+        double cfp = KR(0.0), tfp = KR(0.0);
         unsigned tried = 0;
         for (;;) {
           double bc = INFINITY;
@@ -429,8 +455,8 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
     // goal_tol of the goal (warp_find_goal); lowest index on ties
     int gi;
     {
-      const double* gs = J.goals + 4 * (size_t)qi;
-      const State4 goal = {gs[0], gs[1], gs[2], gs[3]};
+      const krrt_io_real* gs = J.goals + 4 * (size_t)qi;
+      const State4 goal = {(double)gs[0], (double)gs[1], (double)gs[2], (double)gs[3]};
       if (J.goal_mode == GOAL_MODE_TOLERANCE) {
         double bc = INFINITY;
         int bn = -1;
@@ -454,8 +480,8 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       }
     }
     ResultRec* R = J.out + qi;
-    double* wp = &R->waypoints[0][0];
-    for (int k = lane; k < 32 * 5; k += 32) wp[k] = 0.0;
+    krrt_io_real* wp = &R->waypoints[0][0];
+    for (int k = lane; k < 32 * 5; k += 32) wp[k] = KR(0.0);
     __syncwarp();
     if (lane == 0) {
       R->solved = gi >= 0;
@@ -464,8 +490,8 @@ __global__ void __launch_bounds__(B2_MAX_WARPS * 32, 1) k_plan_batch2(Batch2Job 
       int len = 0;
       for (int i = gi; i >= 0 && len <= n; i = (T.parent[i] == B2_NIL ? -1 : (int)T.parent[i])) ++len;
       R->path_len = len;
-      R->cost = gi >= 0 ? T.ctc[gi] : 0.0;
-      R->time = gi >= 0 ? T.tim[gi] : 0.0;
+      R->cost = gi >= 0 ? T.ctc[gi] : KR(0.0);
+      R->time = gi >= 0 ? T.tim[gi] : KR(0.0);
       int p = len - 1;
       for (int i = gi; i >= 0 && p >= 0; i = (T.parent[i] == B2_NIL ? -1 : (int)T.parent[i]), --p) {
         if (p < 32) {

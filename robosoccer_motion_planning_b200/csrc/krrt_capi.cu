@@ -18,6 +18,7 @@
 #include "krrt_grow.cuh"
 #include "krrt_ops.cuh"
 #include "krrt_yaw.cuh"
+#include "krrt_f32_api.h"
 
 using namespace krrt;
 
@@ -98,6 +99,12 @@ struct krrt_ctx {
       return (code);             \
     }                            \
   } while (0)
+// entry points of the single-tree planner and of the Tree / Connector read-outs: binary64 contexts only (a KRRT_F32 context
+// serves the batched planner and the stateless Cost / Environment operators, krrt_f32.cu)
+#define F64_ONLY()                                                                                                    \
+  REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
+          "KRRT_F32 contexts serve krrt_plan_batch* / krrt_steer_cost / krrt_edge_collide; the single-tree planner and its " \
+          "read-outs are binary64 only")
 
 // Everything a context owns on the device comes out of ONE allocation: the sub-rounds of k_grow are chains of
 // dependent gathers over ~25 arrays, and one arena keeps them inside a handful of 2 MB pages (TLB reach).
@@ -187,7 +194,7 @@ void krrt_destroy(krrt_ctx* ctx) {
 
 static int create_impl(krrt_ctx* ctx) {
   const krrt_config& c = ctx->cfg;
-  REQUIRE(c.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED, "only KRRT_F64 is implemented");
+  REQUIRE(c.precision == KRRT_F64 || c.precision == KRRT_F32, KRRT_ERR_INVALID, "precision is KRRT_F64 or KRRT_F32");
   REQUIRE(c.capacity >= 2 && c.S >= 1 && c.r > 0.0 && c.R >= 0.0, KRRT_ERR_INVALID, "bad capacity / S / r / R");
   REQUIRE(c.batch >= 1 && c.batch <= GROW_WMAX, KRRT_ERR_INVALID, "batch must be in [1,1024]");
   REQUIRE(c.near_cap >= 32 && c.near_cap <= 4096, KRRT_ERR_INVALID, "near_cap must be in [32,4096]");
@@ -438,6 +445,7 @@ __global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
 
 int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   if (!ctx || !x0) return KRRT_ERR_INVALID;
+  F64_ONLY();
   CK(cudaSetDevice(ctx->cfg.device));
   State4 s = {x0[0], x0[1], x0[2], x0[3]};
   ctx->ctl_valid = false;
@@ -494,6 +502,7 @@ static int fetch_ctl(krrt_ctx* ctx, Ctl* h) {
 
 int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index) {
   if (!ctx) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
   REQUIRE(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -604,6 +613,7 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
 
 int krrt_tree_size(krrt_ctx* ctx, int* n) {
   if (!ctx || !n) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -615,6 +625,7 @@ int krrt_tree_size(krrt_ctx* ctx, int* n) {
 
 int krrt_iteration(krrt_ctx* ctx, int64_t* iter) {
   if (!ctx || !iter) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -626,6 +637,7 @@ int krrt_iteration(krrt_ctx* ctx, int64_t* iter) {
 
 int krrt_last_sample(krrt_ctx* ctx, double out[4]) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -637,6 +649,7 @@ int krrt_last_sample(krrt_ctx* ctx, double out[4]) {
 
 int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;

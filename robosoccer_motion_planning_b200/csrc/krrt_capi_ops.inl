@@ -15,6 +15,7 @@ extern "C" {
 
 int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time) {
   if (!ctx) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   int n = 0;
@@ -35,6 +36,7 @@ int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* c
 
 int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t* parent, double* cost, double* time) {
   if (!ctx) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   int n = 0, ng = 0;
@@ -56,6 +58,7 @@ int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t*
 
 int krrt_goal_index(krrt_ctx* ctx, int* goal_index) {
   if (!ctx || !goal_index) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -67,6 +70,7 @@ int krrt_goal_index(krrt_ctx* ctx, int* goal_index) {
 
 int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len) {
   if (!ctx || !len) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(cap >= 0, KRRT_ERR_INVALID, "cap < 0");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -99,6 +103,7 @@ int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, in
 
 int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   std::memset(out, 0, sizeof(*out));
   int n = 0;
@@ -163,6 +168,7 @@ static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const doub
 
 int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_rows, int* n_rows) {
   if (!ctx || !n_rows) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -189,6 +195,7 @@ int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_row
 int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                int cap_rows, int* n_rows) {
   if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   CK(cudaSetDevice(ctx->cfg.device));
   int rc;
@@ -205,6 +212,7 @@ int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt,
 int krrt_solve_inputs(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                       double* inputs, int cap_rows, int* n_rows) {
   if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   REQUIRE(cap_rows == 0 || (rows && inputs), KRRT_ERR_INVALID, "null buffer");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -233,8 +241,12 @@ int krrt_steer_cost(krrt_ctx* ctx, const double* xi, const double* xf, int n, do
   if ((rc = ensure_scratch(ctx, 5, ob)) != KRRT_OK) return rc;
   CK(cudaMemcpyAsync(ctx->d_scratch[0], xi, sb, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(ctx->d_scratch[1], xf, sb, cudaMemcpyHostToDevice, st));
-  k_steer_batch<<<(n + 127) / 128, 128, 0, st>>>((const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], n,
-                                                 ctx->cfg.r, (double*)ctx->d_scratch[3], (double*)ctx->d_scratch[5]);
+  if (ctx->cfg.precision == KRRT_F32)
+    CK((cudaError_t)krrt_f32_api::steer_batch((const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], n, ctx->cfg.r,
+                                              (double*)ctx->d_scratch[3], (double*)ctx->d_scratch[5], st));
+  else
+    k_steer_batch<<<(n + 127) / 128, 128, 0, st>>>((const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], n,
+                                                   ctx->cfg.r, (double*)ctx->d_scratch[3], (double*)ctx->d_scratch[5]);
   ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(t, ctx->d_scratch[3], ob, cudaMemcpyDeviceToHost, st));
@@ -262,10 +274,16 @@ int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const d
   CK(cudaMemcpyAsync(ctx->d_scratch[3], tau, ob, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(ctx->d_scratch[5], t0, ob, cudaMemcpyHostToDevice, st));
   const long long threads = (long long)n * 32;
-  k_edge_collide_batch<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(
-      (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], (const double*)ctx->d_scratch[3],
-      (const double*)ctx->d_scratch[5], n, ctx->d_obs, ctx->P.m, ctx->P.dynamic, ctx->P.R2, ctx->P.S,
-      (unsigned char*)ctx->d_scratch[6]);
+  if (ctx->cfg.precision == KRRT_F32)
+    CK((cudaError_t)krrt_f32_api::edge_collide_batch(
+        (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], (const double*)ctx->d_scratch[3],
+        (const double*)ctx->d_scratch[5], n, reinterpret_cast<const double*>(ctx->d_obs), ctx->P.m, ctx->P.dynamic, ctx->cfg.R,
+        ctx->P.S, (unsigned char*)ctx->d_scratch[6], st));
+  else
+    k_edge_collide_batch<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(
+        (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], (const double*)ctx->d_scratch[3],
+        (const double*)ctx->d_scratch[5], n, ctx->d_obs, ctx->P.m, ctx->P.dynamic, ctx->P.R2, ctx->P.S,
+        (unsigned char*)ctx->d_scratch[6]);
   ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(hit, ctx->d_scratch[6], (size_t)n, cudaMemcpyDeviceToHost, st));
@@ -276,6 +294,7 @@ int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const d
 int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, int cap, int* count, int32_t* nearest,
               double* nearest_d2) {
   if (!ctx || !x) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(cap >= 0 && (cap == 0 || idx), KRRT_ERR_INVALID, "null buffer");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -320,10 +339,11 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
   const size_t smem_sm = ctx->prop.sharedMemPerMultiprocessor;         // 228 KB
   // what fits: k_plan_batch2 (near lists in registers, 16-bit links) and its redo pass k_plan_batch (everything in shared
   // memory, 121 B per node against 74).  Decided BEFORE anything is launched.
-  const size_t pw2 = batch2_warp_smem_bytes(cap, m);
-  const int w2 = (int)std::min<size_t>(B2_MAX_WARPS, (smem_max - 1024) / pw2);
+  const bool f32 = c.precision == KRRT_F32;  // the binary32 build of the same two kernels (krrt_f32.cu)
+  const size_t pw2 = f32 ? krrt_f32_api::batch2_warp_smem_bytes(cap, m) : batch2_warp_smem_bytes(cap, m);
+  const int w2 = (int)std::min<size_t>(f32 ? krrt_f32_api::batch2_max_warps() : B2_MAX_WARPS, (smem_max - 1024) / pw2);
   const bool use_v2 = !ctx->batch_v1 && cap <= 65533 && w2 >= 1;
-  const size_t pw = batch_warp_smem_bytes(cap, m);
+  const size_t pw = f32 ? krrt_f32_api::batch_warp_smem_bytes(cap, m) : batch_warp_smem_bytes(cap, m);
   const bool v1_fits = pw <= smem_max;
   REQUIRE(use_v2 || v1_fits, KRRT_ERR_UNSUPPORTED,
           "n_iter too large for the shared-memory batched planner; use krrt_grow per query");
@@ -341,7 +361,8 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
       ctx->rho2_batch_alloc = cap + 1;
     }
     ctx->h_rho2_batch.resize(cap + 1);  // (owned by the context: the copy below is asynchronous)
-    for (int n = 0; n <= cap; ++n) ctx->h_rho2_batch[n] = near_radius2(c, n);
+    for (int n = 0; n <= cap; ++n)
+      ctx->h_rho2_batch[n] = f32 ? krrt_f32_api::near_radius2(c.gamma, c.rho_max, n) : near_radius2(c, n);
     CK(cudaMemcpyAsync(ctx->d_rho2_batch, ctx->h_rho2_batch.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice, st));
     ctx->rho2_batch_cap = cap;
   }
@@ -363,6 +384,19 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
   J.sp.seed = c.seed;
   CK(cudaMemsetAsync(ctx->d_counter, 0, sizeof(int), st));
   CK(cudaMemsetAsync(ctx->d_batch_stats, 0, sizeof(long long) * 10, st));
+  krrt_f32_api::BatchArgs A;
+  if (f32) {
+    A.starts = d_starts; A.goals = d_goals; A.obstacles = d_obs; A.out = d_out;
+    A.next_query = ctx->d_counter; A.list = nullptr; A.list_count = nullptr;
+    A.stats = ctx->d_batch_stats; A.rho2 = ctx->d_rho2_batch;
+    A.redo_list = nullptr; A.redo_count = nullptr;
+    A.chunk_done = d_chunk_done; A.chunk_queries = J.chunk_queries;
+    A.q = q; A.m = m; A.dynamic = J.dynamic; A.n_iter = n_iter; A.cap = cap; A.S = c.S; A.goal_mode = c.goal_mode;
+    A.query_base = query_base;
+    A.r = c.r; A.R = c.R; A.goal_tol = c.goal_tol;
+    for (int k = 0; k < 4; ++k) { A.lo[k] = c.lo[k]; A.hi[k] = c.hi[k]; }
+    A.p_direct = c.p_direct; A.seed = c.seed;
+  }
 
   // ---- k_plan_batch2: near lists in registers, 16-bit links, one CTA of up to 16 warps per SM
   if (use_v2) {
@@ -379,16 +413,23 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
     J2.redo_count = ctx->d_redo + 1;
     J2.redo_list = ctx->d_redo + 2;
     const size_t smem2 = (size_t)w2 * pw2;
-    CK(cudaFuncSetAttribute(k_plan_batch2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     int grid2 = ctx->prop.multiProcessorCount;
     grid2 = (int)std::max<long long>(1, std::min<long long>(grid2, ((long long)q + w2 - 1) / w2));
-    k_plan_batch2<<<grid2, w2 * 32, smem2, st>>>(J2);
+    if (f32) {
+      A.redo_count = J2.redo_count;
+      A.redo_list = J2.redo_list;
+      CK((cudaError_t)krrt_f32_api::launch_batch2(A, grid2, w2, smem2, st));
+    } else {
+      CK(cudaFuncSetAttribute(k_plan_batch2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      k_plan_batch2<<<grid2, w2 * 32, smem2, st>>>(J2);
+    }
     ctx->launches++;
     CK(cudaGetLastError());
     // queries whose near set outgrew the registers (none on the soccer-field configurations) are planned by k_plan_batch
     J.next_query = ctx->d_redo;
     J.list = ctx->d_redo + 2;
     J.list_count = ctx->d_redo + 1;
+    A.next_query = J.next_query; A.list = J.list; A.list_count = J.list_count;
     if (!v1_fits) return KRRT_OK;
   }
 
@@ -407,11 +448,15 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
     }
   }
   const size_t smem = (size_t)best_w * pw;
-  CK(cudaFuncSetAttribute(k_plan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long warps_needed = q;   // (as the redo pass: every warp exits after one atomic when the list is empty)
   int grid = ctx->prop.multiProcessorCount * best_ctas;
   grid = (int)std::max<long long>(1, std::min<long long>(grid, (warps_needed + best_w - 1) / best_w));
-  k_plan_batch<<<grid, best_w * 32, smem, st>>>(J);
+  if (f32) {
+    CK((cudaError_t)krrt_f32_api::launch_batch(A, grid, best_w, smem, st));
+  } else {
+    CK(cudaFuncSetAttribute(k_plan_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_plan_batch<<<grid, best_w * 32, smem, st>>>(J);
+  }
   ctx->launches++;
   CK(cudaGetLastError());
   return KRRT_OK;
@@ -528,6 +573,7 @@ int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
 
 int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const double* t0, int n, int S, double* rows) {
   if (!ctx) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(n >= 0 && S >= 1 && (n == 0 || (xi && xf && t0 && rows)), KRRT_ERR_INVALID, "null buffer / S < 1");
   if (n == 0) return KRRT_OK;
   CK(cudaSetDevice(ctx->cfg.device));
@@ -556,6 +602,7 @@ int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const d
 
 int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes) {
   if (!ctx || !rows) return KRRT_ERR_INVALID;
+  F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(S >= 1 && cap_nodes >= 0, KRRT_ERR_INVALID, "S < 1 / cap_nodes < 0");
   CK(cudaSetDevice(ctx->cfg.device));

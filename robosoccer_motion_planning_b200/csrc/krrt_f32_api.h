@@ -1,0 +1,46 @@
+// krrt_f32_api.h — what krrt_capi.cu calls in the binary32 build of the batched planner and of the stateless
+// Cost / Environment operators (krrt_f32.cu; KRRT_F32 contexts of include/krrt.h).  Plain types only: this header is
+// seen by krrt_f32.cu BEFORE it redefines `double`, so every `double` below is binary64 in both translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace krrt_f32_api {
+
+struct BatchArgs {              // one batched plan: device buffers of the C ABI (binary64) + the context's scratch
+  const double* starts;         // q x 4
+  const double* goals;          // q x 4
+  const double* obstacles;      // q x m x 4
+  void* out;                    // q x krrt_result
+  int* next_query;              // work counter (zeroed by the caller)
+  const int* list;              // redo pass: queries list[0 .. *list_count)
+  const int* list_count;
+  long long* stats;             // [10]
+  const double* rho2;           // [cap + 1] squared near radii, binary32 values held in binary64
+  int* redo_list;
+  int* redo_count;
+  unsigned* chunk_done;
+  int chunk_queries;
+  int q, m, dynamic, n_iter, cap, S, goal_mode;
+  uint32_t query_base;
+  double r, R, goal_tol;        // rounded to binary32 by the launcher (R2 = R * R and tol^2 in binary32)
+  double lo[4], hi[4], p_direct;
+  uint64_t seed;
+};
+
+size_t batch2_warp_smem_bytes(int cap, int m);
+size_t batch_warp_smem_bytes(int cap, int m);
+int batch2_max_warps();
+// k_plan_batch2 / k_plan_batch of namespace krrt_f32; return a cudaError_t as int
+int launch_batch2(const BatchArgs& a, int grid, int warps, size_t smem, cudaStream_t st);
+int launch_batch(const BatchArgs& a, int grid, int warps, size_t smem, cudaStream_t st);
+// squared near radius of a tree of n nodes, evaluated in binary32 exactly as the CPU checker's float build does
+double near_radius2(double gamma, double rho_max, int n);
+// stateless operators: device arrays in binary64 (as the C ABI hands them over), arithmetic in binary32
+int steer_batch(const double* d_xi, const double* d_xf, int n, double r, double* d_t, double* d_c, cudaStream_t st);
+int edge_collide_batch(const double* d_xi, const double* d_xf, const double* d_tau, const double* d_t0, int n,
+                       const double* d_obs /* m x 4 */, int m, int dynamic, double R, int S, unsigned char* d_hit,
+                       cudaStream_t st);
+
+}  // namespace krrt_f32_api

@@ -42,7 +42,8 @@ namespace krrt {
 
 constexpr int GROW_THREADS = 256;
 #ifndef KRRT_GROW_MINB
-#define KRRT_GROW_MINB 2   // CTAs of k_grow per SM the register allocation is held to (128 registers: 264 B of spills)
+#define KRRT_GROW_MINB 1   // CTAs of k_grow per SM the register allocation is held to.  2 (128 registers, 264 B of spills, 295 samples per
+                           // sub-round) was measured: the spills cost what the longer prefixes gain (profiles/r2_grow_two_ctas_s2.txt)
 #endif
 constexpr int GROW_WMAX = 1024;   // window cap
 constexpr int GROW_LEVELS = 62;   // BFS depth below the rewired nodes that the parallel path handles

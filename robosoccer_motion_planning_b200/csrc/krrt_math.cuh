@@ -14,13 +14,18 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include "krrt_real.cuh"
 
 #define KRRT_HD __host__ __device__ __forceinline__
 #define KRRT_NEWTON_MAX 100
 #define KRRT_STATIONARY_MAX 48  // == KO_MAX_STATIONARY: linear convergence (ratio 1/2) at a near-double root of f'
 // relative Newton step that counts as converged (a few ulp; the CPU checker uses the same constant): without it the
 // iteration dithers +-1 ulp around the root for ~20 more steps and every lane of the warp waits for the slowest
+#ifdef KRRT_F32_BUILD
+#define KRRT_XTOL 5e-7f   // binary32 build (krrt_real.cuh): the same few ulp (== KO_XTOL of the CPU checker's float build)
+#else
 #define KRRT_XTOL 1e-15
+#endif
 #ifndef KRRT_ITER_HOOK
 #define KRRT_ITER_HOOK(which)  // test instrumentation point (tests/native/newton_iters.cu counts iterations here)
 #endif
@@ -33,12 +38,12 @@ struct State4 {
 
 // quartic f(t) = t^4 - a t^2 + b t - c0 and derivatives (Horner with explicit fma)
 KRRT_HD double quartic(double t, double a, double b, double c0) { return fma(fma(fma(t, t, -a), t, b), t, -c0); }
-KRRT_HD double quartic_d1(double t, double a, double b) { return fma(fma(4.0 * t, t, -2.0 * a), t, b); }
-KRRT_HD double quartic_d2(double t, double a) { return fma(12.0 * t, t, -2.0 * a); }
+KRRT_HD double quartic_d1(double t, double a, double b) { return fma(fma(KR(4.0) * t, t, -KR(2.0) * a), t, b); }
+KRRT_HD double quartic_d2(double t, double a) { return fma(KR(12.0) * t, t, -KR(2.0) * a); }
 // J(t) = t + a/t - (b/2)/t^2 + (c0/3)/t^3
 KRRT_HD double arrival_cost(double t, double a, double b, double c0) {
-  double w = 1.0 / t;
-  return fma(w, fma(w, fma(w, c0 / 3.0, -0.5 * b), a), t);
+  double w = KR(1.0) / t;
+  return fma(w, fma(w, fma(w, c0 / KR(3.0), -KR(0.5) * b), a), t);
 }
 
 // Newton safeguarded by a sign bracket [lo,hi] with f(lo) <= 0 <= f(hi)
@@ -46,10 +51,10 @@ KRRT_HD double bracketed_root(double lo, double hi, double x, double a, double b
   for (int it = 0; it < KRRT_NEWTON_MAX; ++it) {
     KRRT_ITER_HOOK(0)
     double f = quartic(x, a, b, c0);
-    if (f == 0.0) return x;
-    if (f < 0.0) lo = x; else hi = x;
+    if (f == KR(0.0)) return x;
+    if (f < KR(0.0)) lo = x; else hi = x;
     double xn = x - f / quartic_d1(x, a, b);
-    if (!(xn >= lo && xn <= hi)) xn = lo + 0.5 * (hi - lo);  // Newton left the bracket: bisect
+    if (!(xn >= lo && xn <= hi)) xn = lo + KR(0.5) * (hi - lo);  // Newton left the bracket: bisect
     if (fabs(xn - x) <= KRRT_XTOL * x) return xn;
     x = xn;
   }
@@ -58,11 +63,11 @@ KRRT_HD double bracketed_root(double lo, double hi, double x, double a, double b
 
 // stationary points of f: monotone Newton on f' from the left (start 0) and from the right (start sqrt(a/2))
 KRRT_HD double stationary_left(double a, double b) {
-  double x = 0.0;
+  double x = KR(0.0);
   for (int it = 0; it < KRRT_STATIONARY_MAX; ++it) {
     KRRT_ITER_HOOK(1)
     double g = quartic_d1(x, a, b);
-    if (!(g > 0.0)) break;
+    if (!(g > KR(0.0))) break;
     double xn = x - g / quartic_d2(x, a);
     if (!(xn > x)) break;
     if (xn - x <= KRRT_XTOL * xn) {
@@ -74,11 +79,11 @@ KRRT_HD double stationary_left(double a, double b) {
   return x;
 }
 KRRT_HD double stationary_right(double a, double b) {
-  double x = sqrt(0.5 * a);
+  double x = sqrt(KR(0.5) * a);
   for (int it = 0; it < KRRT_STATIONARY_MAX; ++it) {
     KRRT_ITER_HOOK(2)
     double g = quartic_d1(x, a, b);
-    if (!(g > 0.0)) break;
+    if (!(g > KR(0.0))) break;
     double xn = x - g / quartic_d2(x, a);
     if (!(xn < x)) break;
     if (x - xn <= KRRT_XTOL * x) {
@@ -107,46 +112,46 @@ KRRT_HD void steer(const State4& x0, const State4& x1, double r, double& tau_out
   double v01 = fma(x0.vy, x1.vy, x0.vx * x1.vx);
   double v11 = fma(x1.vy, x1.vy, x1.vx * x1.vx);
   double vv = (v00 + v01) + v11;
-  double a = (4.0 * r) * vv;
-  double b = (24.0 * r) * ds;
-  double c0 = (36.0 * r) * dd;
-  if (a < 0.0) a = 0.0;
-  if (c0 == 0.0) {  // coincident positions: f = t^2 (t^2 - a)
+  double a = (KR(4.0) * r) * vv;
+  double b = (KR(24.0) * r) * ds;
+  double c0 = (KR(36.0) * r) * dd;
+  if (a < KR(0.0)) a = KR(0.0);
+  if (c0 == KR(0.0)) {  // coincident positions: f = t^2 (t^2 - a)
     double t = sqrt(a);
     tau_out = t;
     cost_out = t + t;
     return;
   }
-  double disc = sqrt(fma(a, a, 4.0 * c0));
-  double T2 = 0.5 * (a + disc);
+  double disc = sqrt(fma(a, a, KR(4.0) * c0));
+  double T2 = KR(0.5) * (a + disc);
   double T = sqrt(T2);  // root of the b = 0 quartic: upper bound when b >= 0, lower bound when b < 0
   // bracket [lo, hi] and start x of the primary root
   double lo, hi, x;
-  double s1 = 0.0;
+  double s1 = KR(0.0);
   bool three = false;  // three-root zone: a second root right of the right stationary point may be cheaper
-  if (b < 0.0) {
+  if (b < KR(0.0)) {
     lo = T;
     hi = T + (-b) / T2;
     x = hi;
   } else {
-    double ti = sqrt(a / 6.0);  // inflection of f
-    double bcrit = (4.0 * a / 3.0) * ti;
+    double ti = sqrt(a / KR(6.0));  // inflection of f
+    double bcrit = (KR(4.0) * a / KR(3.0)) * ti;
     hi = T;
     x = T;
     if (b >= bcrit) {  // f monotone for t > 0
-      lo = 0.0;
+      lo = KR(0.0);
     } else if (b * ti < c0) {  // f < 0 on (0, ti]
       lo = ti;
     } else {
       s1 = stationary_left(a, b);
-      if (quartic(s1, a, b, c0) < 0.0) {
+      if (quartic(s1, a, b, c0) < KR(0.0)) {
         lo = ti;
       } else {
         three = true;
-        lo = 0.0;
+        lo = KR(0.0);
         hi = s1;
         x = c0 / b;
-        if (!(x < s1)) x = 0.5 * s1;
+        if (!(x < s1)) x = KR(0.5) * s1;
       }
     }
   }
@@ -154,7 +159,7 @@ KRRT_HD void steer(const State4& x0, const State4& x1, double r, double& tau_out
   double cost = arrival_cost(tau, a, b, c0);
   if (three) {
     double s2 = stationary_right(a, b);
-    if (quartic(s2, a, b, c0) <= 0.0) {
+    if (quartic(s2, a, b, c0) <= KR(0.0)) {
       double t3 = bracketed_root(s2, T, T, a, b, c0);
       double c3 = arrival_cost(t3, a, b, c0);
       if (c3 < cost) {
@@ -176,20 +181,20 @@ KRRT_HD AxisCubic axis_cubic(double p0, double v0, double p1, double v1, double 
   double dp = p1 - p0;
   k.p0 = p0;
   k.A = v0 * tau;
-  k.B = fma(-(2.0 * v0 + v1), tau, 3.0 * dp);
-  k.C = fma(v0 + v1, tau, -2.0 * dp);
+  k.B = fma(-(KR(2.0) * v0 + v1), tau, KR(3.0) * dp);
+  k.C = fma(v0 + v1, tau, -KR(2.0) * dp);
   return k;
 }
 KRRT_HD double axis_pos(const AxisCubic& k, double h) { return fma(h, fma(h, fma(h, k.C, k.B), k.A), k.p0); }
 KRRT_HD double axis_vel(const AxisCubic& k, double h, double v0, double tau) {
-  if (tau == 0.0) return v0;
-  return v0 + (h * fma(3.0 * h, k.C, 2.0 * k.B)) / tau;
+  if (tau == KR(0.0)) return v0;
+  return v0 + (h * fma(KR(3.0) * h, k.C, KR(2.0) * k.B)) / tau;
 }
 
 // control input u = p'' of the edge at h (the service response's `inputs` for the 2-D integrator model)
 KRRT_HD double axis_acc(const AxisCubic& k, double h, double tau) {
-  if (tau == 0.0) return 0.0;
-  return fma(6.0 * h, k.C, 2.0 * k.B) / (tau * tau);
+  if (tau == KR(0.0)) return KR(0.0);
+  return fma(KR(6.0) * h, k.C, KR(2.0) * k.B) / (tau * tau);
 }
 
 struct Edge {
@@ -209,7 +214,7 @@ KRRT_HD Edge make_edge(const State4& a, const State4& b, double tau, double t0) 
 
 // disc test of edge sample k (of S) against obstacle o = (x,y,vx,vy); R2 = R*R
 KRRT_HD bool edge_point_hits(const Edge& e, int k, int S, const double4& o, int dynamic, double R2) {
-  double h = (S > 1) ? (double)k / (double)(S - 1) : 0.0;
+  double h = (S > 1) ? (double)k / (double)(S - 1) : KR(0.0);
   double px = axis_pos(e.kx, h), py = axis_pos(e.ky, h);
   double ox = o.x, oy = o.y;
   if (dynamic) {
@@ -267,7 +272,7 @@ KRRT_HD U4 philox4x32_10(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2, u
 }
 KRRT_HD double unit53(uint32_t hi, uint32_t lo) {
   uint64_t u = ((uint64_t)hi << 32) | lo;
-  return (double)(u >> 11) * 0x1.0p-53;
+  return (double)(u >> 11) * KR(0x1.0p-53);
 }
 
 struct SamplerParams {
@@ -279,7 +284,7 @@ struct SamplerParams {
 KRRT_HD State4 draw_sample(const SamplerParams& sp, uint32_t query_id, uint64_t iter, bool has_goal,
                            const State4& goal) {
   uint32_t i0 = (uint32_t)iter, i3 = (uint32_t)(iter >> 32);
-  if (has_goal && sp.p_direct > 0.0) {
+  if (has_goal && sp.p_direct > KR(0.0)) {
     U4 w = philox4x32_10(sp.seed, i0, query_id, 2u, i3);
     if (unit53(w.a, w.b) < sp.p_direct) return goal;
   }

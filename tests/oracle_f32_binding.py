@@ -1,0 +1,116 @@
+"""ctypes binding of the CPU oracle's binary32 build (oracle/_build/libkrrt_oracle_f32.so: krrt_oracle.c compiled with
+every `double` a `float`, see the head of that file) — the checker of KRRT_F32 contexts.
+
+Test infrastructure like oracle_binding.py.  The library's interface is float throughout; this module takes and returns
+the binary64 arrays of the C ABI (inputs rounded to binary32 exactly as the kernels round them when they load, outputs
+widened exactly) so that results compare byte for byte with libkrrt's."""
+import ctypes
+import os
+
+import numpy as np
+
+import oracle_binding as ob
+
+ORACLE_F32_SO = os.path.join(ob.ORACLE_DIR, "_build", "libkrrt_oracle_f32.so")
+F = ctypes.POINTER(ctypes.c_float)
+I = ctypes.POINTER(ctypes.c_int32)
+
+
+class KoConfigF(ctypes.Structure):
+    _fields_ = [
+        ("r", ctypes.c_float), ("R", ctypes.c_float), ("S", ctypes.c_int32), ("capacity", ctypes.c_int32),
+        ("lo", ctypes.c_float * 4), ("hi", ctypes.c_float * 4),
+        ("gamma", ctypes.c_float), ("rho_max", ctypes.c_float), ("p_direct", ctypes.c_float), ("goal_tol", ctypes.c_float),
+        ("seed", ctypes.c_uint64), ("query_id", ctypes.c_uint32), ("use_kdtree", ctypes.c_int32), ("goal_mode", ctypes.c_int32),
+    ]
+
+
+RESULT_F32 = np.dtype([
+    ("solved", "<i4"), ("goal_index", "<i4"), ("n_nodes", "<i4"), ("path_len", "<i4"),
+    ("cost", "<f4"), ("time", "<f4"), ("waypoints", "<f4", (ob.KO_MAX_WAYPOINTS, 5))])
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    ob.build_oracle(force=not os.path.exists(ORACLE_F32_SO))
+    L = ctypes.CDLL(ORACLE_F32_SO)
+    L.ko_default_config.argtypes = [ctypes.POINTER(KoConfigF)]
+    L.ko_steer_batch.argtypes = [F, F, ctypes.c_int, ctypes.c_float, F, F]
+    L.ko_edge_collide.argtypes = [F, F, ctypes.c_float, ctypes.c_float, F, ctypes.c_int, ctypes.c_int, ctypes.c_float,
+                                  ctypes.c_int]
+    L.ko_edge_collide.restype = ctypes.c_int
+    L.ko_rho2.argtypes = [ctypes.POINTER(KoConfigF), ctypes.c_int]
+    L.ko_rho2.restype = ctypes.c_float
+    L.ko_sample.argtypes = [ctypes.POINTER(KoConfigF), ctypes.c_uint64, F, F]
+    L.ko_plan_batch.argtypes = [ctypes.POINTER(KoConfigF), F, F, F, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                ctypes.c_uint32, ctypes.c_void_p, ctypes.c_int]
+    _lib = L
+    return L
+
+
+def _f(a):
+    return a.ctypes.data_as(F)
+
+
+def _f32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64).astype(np.float32))
+
+
+def default_config(**kw):
+    c = KoConfigF()
+    lib().ko_default_config(ctypes.byref(c))
+    ob.set_fields(c, **kw)
+    return c
+
+
+def steer(x0, x1, r=0.5):
+    """(tau*, c*) of x0[i] -> x1[i] in binary32, returned as binary64 arrays."""
+    x0 = _f32(x0).reshape(-1, 4)
+    x1 = _f32(x1).reshape(-1, 4)
+    n = x0.shape[0]
+    t = np.empty(n, dtype=np.float32)
+    c = np.empty(n, dtype=np.float32)
+    lib().ko_steer_batch(_f(x0), _f(x1), n, float(r), _f(t), _f(c))
+    return t.astype(np.float64), c.astype(np.float64)
+
+
+def edge_collide(x0, x1, tau, t0, obs, dynamic, R=1.35, S=10):
+    x0 = _f32(x0)
+    x1 = _f32(x1)
+    obs = _f32(obs).reshape(-1, 4)
+    return lib().ko_edge_collide(_f(x0), _f(x1), float(np.float32(tau)), float(np.float32(t0)), _f(obs), obs.shape[0],
+                                 int(dynamic), float(R), int(S))
+
+
+def rho2(cfg, n):
+    return float(lib().ko_rho2(ctypes.byref(cfg), int(n)))
+
+
+def sample(cfg, it, goal=None):
+    out = np.empty(4, dtype=np.float32)
+    g = _f32(goal) if goal is not None else None
+    lib().ko_sample(ctypes.byref(cfg), int(it), _f(g) if g is not None else None, _f(out))
+    return out.astype(np.float64)
+
+
+def plan_batch(cfg, starts, goals, obstacles, dynamic, n_iter, query_base=0, nthreads=1):
+    """ko_plan_batch of the float build; the records come back in the binary64 layout of krrt_result."""
+    starts = _f32(starts).reshape(-1, 4)
+    goals = _f32(goals).reshape(-1, 4)
+    q = starts.shape[0]
+    obstacles = _f32(obstacles)
+    obstacles = obstacles.reshape(q, -1, 4) if obstacles.size else np.zeros((q, 0, 4), dtype=np.float32)
+    m = obstacles.shape[1]
+    raw = np.zeros(q, dtype=RESULT_F32)
+    lib().ko_plan_batch(ctypes.byref(cfg), _f(starts), _f(goals), _f(obstacles), q, m, int(dynamic), int(n_iter),
+                        int(query_base), raw.ctypes.data, int(nthreads))
+    out = np.zeros(q, dtype=ob.RESULT_DTYPE)
+    for k in ("solved", "goal_index", "n_nodes", "path_len"):
+        out[k] = raw[k]
+    for k in ("cost", "time", "waypoints"):
+        out[k] = raw[k].astype(np.float64)
+    return out

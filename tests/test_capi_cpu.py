@@ -51,7 +51,7 @@ def test_no_cpu_fallback(built):
 
 
 def test_invalid_config_rejected(built):
-    for kw in (dict(capacity=1), dict(batch=2000), dict(near_cap=7), dict(r=0.0), dict(precision=1)):
+    for kw in (dict(capacity=1), dict(batch=2000), dict(near_cap=7), dict(r=0.0), dict(precision=2)):
         with pytest.raises(capi.KrrtError) as e:
             capi.Planner(**kw)
         assert e.value.code in (capi.KRRT_ERR_INVALID, capi.KRRT_ERR_UNSUPPORTED)

@@ -1,0 +1,155 @@
+"""fp32 mode (KRRT_F32 contexts; BASELINE.json north_star: "1e-4 in fp32 mode").
+
+The binary32 planner is the binary64 planner's source compiled in float on both sides (kernels: csrc/krrt_f32.cu; checker:
+oracle/_build/libkrrt_oracle_f32.so), so GPU results compare BIT FOR BIT with the float checker; the float checker in turn
+stays within north_star's 1e-4 of the binary64 one on costs and arrival times of identical edges (the tolerance is written
+below), and plans with the same statistics."""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+import oracle_f32_binding as of
+
+RTOL_F32 = 1e-4   # north_star: path costs and arrival times within 1e-4 relative in fp32 mode
+
+
+def _pairs(n, seed=0):
+    rng = np.random.default_rng(seed)
+    lo = np.array([-9.0, -6.0, -2.0, -2.0])
+    hi = np.array([9.0, 6.0, 2.0, 2.0])
+    x0 = rng.uniform(lo, hi, (n, 4)).astype(np.float32).astype(np.float64)   # float-representable: both builds see the same edge
+    x1 = rng.uniform(lo, hi, (n, 4)).astype(np.float32).astype(np.float64)
+    return x0, x1
+
+
+def test_float_checker_steering_within_1e4_of_double():
+    x0, x1 = _pairs(200000)
+    t32, c32 = of.steer(x0, x1)
+    t64 = np.empty(len(x0))
+    c64 = np.empty(len(x0))
+    ob.lib().ko_steer_batch(ob._d(x0), ob._d(x1), len(x0), 0.5, ob._d(t64), ob._d(c64))
+    rc = np.abs(c32 - c64) / c64
+    rt = np.abs(t32 - t64) / t64
+    assert rc.max() <= RTOL_F32, rc.max()
+    # the arrival time of the optimum is as well conditioned except where two roots of the quartic cost the same to within
+    # float rounding (three-root zone, SURVEY.md 8-M: 0.07 % of field-scale pairs) and the other one is picked
+    assert np.mean(rt <= RTOL_F32) >= 0.999, np.mean(rt <= RTOL_F32)
+    assert np.median(rc) < 1e-6
+
+
+def test_float_checker_sampler_and_radius_follow_the_double_ones():
+    c64 = ob.default_config(p_direct=0.1, query_id=7)
+    c32 = of.default_config(p_direct=0.1, query_id=7)
+    goal = np.array([7.0, 0.0, 0.0, 0.0])
+    for it in range(200):
+        a = ob.sample(c64, it, goal)
+        b = of.sample(c32, it, goal)
+        assert np.allclose(a, b, rtol=0, atol=2e-6)                 # same Philox words, rounded to binary32
+    for n in (2, 10, 200, 5000):
+        assert abs(of.rho2(c32, n) - ob.lib().ko_rho2(c64, n)) <= 1e-5 * ob.lib().ko_rho2(c64, n)
+
+
+def test_float_checker_plans_like_the_double_one():
+    from robosoccer_motion_planning_b200 import scenes
+    starts, goals, obs = scenes.batch_queries(256, 9, seed=3)
+    r64 = ob.plan_batch(ob.default_config(p_direct=0.1), starts, goals, obs, 1, 200, nthreads=8)
+    r32 = of.plan_batch(of.default_config(p_direct=0.1), starts, goals, obs, 1, 200, nthreads=8)
+    assert abs(r64["solved"].mean() - r32["solved"].mean()) <= 0.02
+    both = (r64["solved"] != 0) & (r32["solved"] != 0)
+    assert both.mean() > 0.9
+    # trees diverge once a float rounding flips a decision (any RRT* does under perturbation); the plans' quality does not
+    assert abs(r64["cost"][both].mean() - r32["cost"][both].mean()) <= 0.03 * r64["cost"][both].mean()
+    # a plan's own record is consistent: arrival time of the last waypoint == reported time, first waypoint == start
+    for rec, s in zip(r32[both][:32], starts[both][:32]):
+        n = min(int(rec["path_len"]), 32)
+        assert np.array_equal(rec["waypoints"][0, :4], s.astype(np.float32).astype(np.float64))
+        if rec["path_len"] <= 32:
+            assert rec["waypoints"][n - 1, 4] == rec["time"]
+
+
+def test_float_checker_meets_north_star_against_the_double_one():
+    """north_star's fp32 criterion, checker against checker: same parents / near sets (here: same tree sizes, goal nodes and
+    path lengths) wherever no decision sat within float rounding of a tie, costs and arrival times within 1e-4."""
+    from robosoccer_motion_planning_b200 import scenes
+    starts, goals, obs = scenes.batch_queries(1024, 9, seed=0)
+    r64 = ob.plan_batch(ob.default_config(p_direct=0.1), starts, goals, obs, 1, 200, nthreads=8)
+    r32 = of.plan_batch(of.default_config(p_direct=0.1), starts, goals, obs, 1, 200, nthreads=8)
+    same = (r64["n_nodes"] == r32["n_nodes"]) & (r64["goal_index"] == r32["goal_index"]) & (r64["path_len"] == r32["path_len"])
+    assert same.mean() >= 0.99, same.mean()          # measured: 1024 of 1024
+    ok = same & (r64["solved"] != 0)
+    assert (np.abs(r32["cost"][ok] - r64["cost"][ok]) <= RTOL_F32 * r64["cost"][ok]).all()
+    assert (np.abs(r32["time"][ok] - r64["time"][ok]) <= RTOL_F32 * r64["time"][ok]).all()
+    wp = np.abs(r32["waypoints"][ok] - r64["waypoints"][ok])
+    assert wp.max() <= 1e-4 * 18.0                  # waypoints: 1e-4 of the field's length
+
+
+# ------------------------------------------------------------------------------------------------ GPU: bit-exact
+@pytest.mark.gpu
+def test_f32_steer_and_collide_bit_exact(gpu_required):
+    from robosoccer_motion_planning_b200 import capi, scenes
+    G = capi.Planner(precision=capi.KRRT_F32)
+    x0, x1 = _pairs(100000, seed=5)
+    t, c = G.steer_cost(x0, x1)
+    to, co = of.steer(x0, x1)
+    assert np.array_equal(t, to) and np.array_equal(c, co)
+    # inputs that are NOT float-representable are rounded on load, exactly as the checker's binding rounds them
+    y0, y1 = x0[:1000] + 1e-9, x1[:1000] - 1e-9
+    t2, c2 = G.steer_cost(y0, y1)
+    to2, co2 = of.steer(y0, y1)
+    assert np.array_equal(t2, to2) and np.array_equal(c2, co2)
+    for dynamic in (0, 1):
+        obs = scenes.dynamic_obstacles()
+        G.set_obstacles(obs, dynamic)
+        n = 4000
+        t0 = np.random.default_rng(1).uniform(0, 5, n)
+        hit = G.edge_collide(x0[:n], x1[:n], t[:n], t0)
+        ref = np.array([of.edge_collide(x0[i], x1[i], t[i], t0[i], obs, dynamic) for i in range(n)], dtype=np.uint8)
+        assert np.array_equal(hit, ref)
+        assert 0 < hit.sum() < n
+    G.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dynamic,p_direct,n_iter,goal_mode", [(1, 0.1, 200, 0), (0, 0.0, 75, 0), (1, 0.1, 120, 1)])
+def test_f32_plan_batch_bit_exact(gpu_required, dynamic, p_direct, n_iter, goal_mode):
+    from robosoccer_motion_planning_b200 import capi, scenes
+    q = 512
+    starts, goals, obs = scenes.batch_queries(q, 9, seed=11)
+    kw = dict(p_direct=p_direct, goal_mode=goal_mode, goal_tol=0.75 if goal_mode else 0.0)
+    G = capi.Planner(precision=capi.KRRT_F32, **kw)
+    out = G.plan_batch(starts, goals, obs, dynamic, n_iter, query_base=100)
+    ref = of.plan_batch(of.default_config(**kw), starts, goals, obs, dynamic, n_iter, query_base=100, nthreads=8)
+    assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
+    assert out["solved"].mean() > (0.9 if goal_mode == 0 else 0.05)
+    # ... and it is not the binary64 plan: costs differ in the low bits
+    G64 = capi.Planner(**kw)
+    out64 = G64.plan_batch(starts, goals, obs, dynamic, n_iter, query_base=100)
+    assert not np.array_equal(out["cost"], out64["cost"])
+    both = (out["solved"] != 0) & (out64["solved"] != 0)
+    assert abs(out["cost"][both].mean() - out64["cost"][both].mean()) <= 0.03 * out64["cost"][both].mean()
+    G.close()
+    G64.close()
+
+
+@pytest.mark.gpu
+def test_f32_near_overflow_takes_the_redo_pass(gpu_required):
+    """A near radius that covers the whole field: every near set outgrows k_plan_batch2's 64 registers, the float k_plan_batch
+    plans those queries, the result is the checker's."""
+    from robosoccer_motion_planning_b200 import capi, scenes
+    starts, goals, obs = scenes.batch_queries(64, 9, seed=2)
+    kw = dict(p_direct=0.1, gamma=40.0, rho_max=30.0)
+    G = capi.Planner(precision=capi.KRRT_F32, **kw)
+    out = G.plan_batch(starts, goals, obs, 1, 150)
+    ref = of.plan_batch(of.default_config(**kw), starts, goals, obs, 1, 150, nthreads=8)
+    assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
+    G.close()
+
+
+@pytest.mark.gpu
+def test_f32_context_refuses_the_single_tree_planner(gpu_required):
+    from robosoccer_motion_planning_b200 import capi, scenes
+    G = capi.Planner(precision=capi.KRRT_F32)
+    with pytest.raises(capi.KrrtError) as e:
+        G.set_start(scenes.START)
+    assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
+    G.close()
