@@ -459,6 +459,45 @@ def run_ours(args, rank, world, local_rank):
                                            "sample": f"{qs} of the {BATCH_Q} queries, one query per thread at a time"}
         line["batched"]["parity_vs_oracle"] = ("bit-exact" if np.array_equal(out_h[:qs].view(np.uint8), refb.view(np.uint8))
                                                else "MISMATCH")
+        # fp32 mode (KRRT_F32 contexts): the same C4 workload through the binary32 build of the batched planner, its own line
+        # (the headline stays fp64); checked against the CPU checker's float build, and against the fp64 records within
+        # north_star's 1e-4
+        import oracle_f32_binding as of
+        S32 = sweep.Sweep.single_process(1, devices=[local_rank], p_direct=P_DIRECT, precision=capi.KRRT_F32)
+        S32.load(bs[:BATCH_Q], bg[:BATCH_Q], bo[:BATCH_Q])
+        for _ in range(3):
+            S32.run(1, BATCH_ITERS)
+        f_ms = 0.0
+        for _ in range(bsteps):
+            flush_l2()
+            f_ms += S32.run(1, BATCH_ITERS)
+        rec32 = S32.results()
+        st32 = S32.stats()
+        ref32 = of.plan_batch(of.default_config(p_direct=P_DIRECT), bs[:qs], bg[:qs], bo[:qs], 1, BATCH_ITERS, nthreads=allc)
+        rec64 = out_h[:BATCH_Q]
+        same_tree = ((rec32["n_nodes"] == rec64["n_nodes"]) & (rec32["goal_index"] == rec64["goal_index"])
+                     & (rec32["path_len"] == rec64["path_len"]))
+        okc = same_tree & (rec64["solved"] != 0)
+        relc = np.abs(rec32["cost"][okc] - rec64["cost"][okc]) / rec64["cost"][okc]
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_fp_peak.json")) as f:
+                f32_peak = float(json.load(f)["fp32_fma_tflops"])
+        except Exception:
+            f32_peak = 75.0
+        f_flop = 134.0 * st32["steer_calls"] + 1180.0 * st32["collide_calls"]
+        f_tflops = f_flop * bsteps / (f_ms * 1e-3) / 1e12
+        line["batched_f32"] = {
+            "dtype": "f32", "workload": line["batched"]["workload"] + ", KRRT_F32 context",
+            "queries_per_sec": BATCH_Q * bsteps / (f_ms * 1e-3), "ms_per_step": f_ms / bsteps,
+            "speedup_over_f64": (b_ms / bsteps) / (f_ms / bsteps),
+            "solved_frac": float((rec32["solved"] != 0).mean()),
+            "parity_vs_float_checker": ("bit-exact" if np.array_equal(rec32[:qs].view(np.uint8), ref32.view(np.uint8)) else "MISMATCH"),
+            "vs_f64_records": {"same_tree_size_goal_and_path_length": float(same_tree.mean()),
+                               "max_rel_cost_diff": float(relc.max()) if relc.size else None, "tolerance": 1e-4},
+            "roofline": {"bound": "fp32 pipe / latency", "kernel": "krrt_f32::k_plan_batch2", "achieved": f_tflops,
+                         "peak": f32_peak, "unit": "TFLOP/s", "frac": f_tflops / f32_peak,
+                         "peak_source": "measured (profiles/r1_fp_peak.json, FMA-chain microbenchmark)"}}
+        S32.close()
         # config 0 (rrtstar_benchmark, C1): static obstacles, fixed seed, 10k iterations — GPU and the CPU port, same plan
         G1 = capi.Planner(device=local_rank, capacity=10002, batch=args.batch)
         O1 = ob.OraclePlanner(capacity=10002, query_id=0)

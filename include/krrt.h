@@ -119,6 +119,9 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]);
  * host doubles; a row whose first entry is NaN means "draw from the internal Philox sampler". */
 int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved,
               int* goal_index);
+/* how the last krrt_grow call ended: the iterations it really ran and whether it stopped because the tree had reached
+ * `capacity` (the call itself returns KRRT_OK: the tree is valid, only shorter than asked for) */
+int krrt_grow_done(krrt_ctx* ctx, int64_t* iterations_done, int* full);
 int krrt_tree_size(krrt_ctx* ctx, int* n);
 int krrt_iteration(krrt_ctx* ctx, int64_t* iter);
 int krrt_last_sample(krrt_ctx* ctx, double out[4]);

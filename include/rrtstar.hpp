@@ -144,11 +144,19 @@ class RRTStar {
     } else {
       s.check(krrt_grow(c, xg ? g : nullptr, n_iter, samples, &solved, &gi));
     }
-    iteration_ += n_iter;
+    {  // the iterations the device really ran (a tree that reached `capacity` stops early: full() tells)
+      int64_t done = 0;
+      int full = 0;
+      s.check(krrt_grow_done(c, &done, &full));
+      iteration_ += (samples && n_iter > 1) ? done + 1 : done;
+      full_ = full != 0;
+    }
     s.touch();
     goal_index_ = gi;
     return solved != 0;
   }
+  // the tree holds Tree::capacity nodes: the last grow call stopped before its iterations were used up
+  bool full() const { return full_; }
 
   // == rrt.goalIndex(): index of the goal node, > 0 iff a solution exists (robosoccer_visual.hpp:19)
   int goalIndex() const { return goal_index_; }
@@ -175,6 +183,7 @@ class RRTStar {
   Connector& connector_;
   int goal_index_ = -1;
   long iteration_ = 0;
+  bool full_ = false;
 };
 
 #endif  // KRRT_RRTSTAR_HPP

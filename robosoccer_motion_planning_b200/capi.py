@@ -25,7 +25,7 @@ I = ctypes.POINTER(ctypes.c_int32)
 
 # every symbol include/krrt.h declares (tests check the library exports all of them)
 EXPORTS = (
-    "krrt_default_config", "krrt_create", "krrt_destroy", "krrt_last_error", "krrt_device_count",
+    "krrt_default_config", "krrt_grow_done", "krrt_create", "krrt_destroy", "krrt_last_error", "krrt_device_count",
     "krrt_set_obstacles", "krrt_set_start", "krrt_grow", "krrt_tree_size", "krrt_iteration", "krrt_last_sample",
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
@@ -105,6 +105,7 @@ def lib():
     L.krrt_set_start.argtypes = [P, D]
     L.krrt_grow.argtypes = [P, D, ctypes.c_int, D, I, I]
     L.krrt_tree_size.argtypes = [P, I]
+    L.krrt_grow_done.argtypes = [P, ctypes.POINTER(ctypes.c_int64), I]
     L.krrt_iteration.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_last_sample.argtypes = [P, D]
     L.krrt_get_stats.argtypes = [P, ctypes.POINTER(KrrtStats)]
@@ -261,6 +262,12 @@ class Planner:
         gi = ctypes.c_int32(-1)
         self._ck(lib().krrt_grow(self.h, g, int(n_iter), s, ctypes.byref(solved), ctypes.byref(gi)))
         return bool(solved.value), gi.value
+
+    def grow_done(self):
+        """(iterations the last grow call really ran, whether it stopped because the tree is full)"""
+        it, full = ctypes.c_int64(0), ctypes.c_int32(0)
+        self._ck(lib().krrt_grow_done(self.h, ctypes.byref(it), ctypes.byref(full)))
+        return it.value, bool(full.value)
 
     @property
     def size(self):

@@ -81,6 +81,8 @@ struct krrt_ctx {
   double last_total_ms = 0.0, last_scan_ms = 0.0;
   int64_t last_scan_launches = 0;
   double last_scan_node_samples = 0.0;
+  int64_t last_grow_iters = 0;  // iterations the last krrt_grow call really ran (fewer than asked when the tree filled up)
+  int last_grow_full = 0;
 };
 
 #define CK(call)                                                                                   \
@@ -589,6 +591,8 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->last_total_ms = ms;
+  ctx->last_grow_iters = h.iter - h.iter_begin;
+  ctx->last_grow_full = h.full ? 1 : 0;
   ctx->last_scan_node_samples = h.scan_pairs;
   {
     // phase clocks of the kernel's last CTA -> shares of the call's device time
@@ -608,6 +612,16 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   }
   if (solved) *solved = h.goal_index >= 0;
   if (goal_index) *goal_index = h.goal_index;
+  return KRRT_OK;
+}
+
+// how the last krrt_grow call ended: RRTStar::grow advances its iteration counter by n_iter whatever happens
+// (include/rrtstar.hpp mirrors that from here); a tree that reached `capacity` stops early and says so
+int krrt_grow_done(krrt_ctx* ctx, int64_t* iterations_done, int* full) {
+  if (!ctx) return KRRT_ERR_INVALID;
+  F64_ONLY();
+  if (iterations_done) *iterations_done = ctx->last_grow_iters;
+  if (full) *full = ctx->last_grow_full;
   return KRRT_OK;
 }
 

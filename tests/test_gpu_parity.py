@@ -192,7 +192,11 @@ def test_capacity_full(gpu_required):
     G, O = make_pair(gpu_required, dynamic=1, capacity=300, batch=64)
     for P in (G, O):
         P.grow(scenes.GOAL, 500)
+    done, full = G.grow_done()               # the call returns KRRT_OK; how it ended is on record
+    assert full and done < 500 and done == O.iteration
+    for P in (G, O):
         P.grow(scenes.GOAL, 3)
+    assert G.grow_done() == (0, True)
     assert G.size == O.size == 300
     assert_same_tree(G, O)
 
