@@ -158,8 +158,19 @@ class TreeInt2D {
 
   size_t node_count() const {
     if (!session_->started) return 0;
+    // tree.tree.size() right after a grow(xg) that was answered from the run-ahead records: the record has it (rrtstar.hpp)
+    const krrt::RunAhead& ra = session_->run_ahead();
+    if (ra.served > 0 && (size_t)ra.served <= ra.log.size() && ra.log[(size_t)ra.served - 1].n_nodes >= 0)
+      return (size_t)ra.log[(size_t)ra.served - 1].n_nodes;
+    return device_size();
+  }
+  // the device's own count, with the device tree settled at the caller's iteration
+  size_t device_size() const {
+    if (!session_->started) return 0;
+    krrt_ctx* c = session_->ctx();
+    session_->sync_tree();
     int n = 0;
-    session_->check(krrt_tree_size(session_->ctx(), &n));
+    session_->check(krrt_tree_size(c, &n));
     return (size_t)n;
   }
   State operator()(size_t i) const { return tree.cloud.states.at(i); }
@@ -177,6 +188,7 @@ class TreeInt2D {
     if (idx < 0 || !session_->started) return out;
     int len = 0;
     krrt_ctx* c = session_->ctx();
+    session_->sync_tree();
     session_->check(krrt_path(c, idx, nullptr, nullptr, 0, &len));
     out.resize(len);
     if (len > 0) session_->check(krrt_path(c, idx, out[0].data(), nullptr, len, &len));
@@ -195,6 +207,7 @@ class TreeInt2D {
     if (seen_ == session_->version() || !session_->started) return;
     auto* self = const_cast<TreeInt2D*>(this);
     krrt_ctx* c = session_->ctx();
+    session_->sync_tree();  // (iterations run ahead of the caller are taken back first: rrtstar.hpp)
     int n = 0, gi = -1;
     session_->check(krrt_tree_size(c, &n));
     session_->check(krrt_goal_index(c, &gi));
@@ -306,7 +319,15 @@ class SamplerInt2D {
   // the sample the last expansion used (…node.cpp:178)
   State last_sample() const {
     State s{};
-    if (session_->started) session_->check(krrt_last_sample(session_->ctx(), s.data()));
+    if (!session_->started) return s;
+    const krrt::RunAhead& ra = session_->run_ahead();
+    if (ra.served > 0 && (size_t)ra.served <= ra.log.size() && ra.log[(size_t)ra.served - 1].n_nodes >= 0) {
+      for (int k = 0; k < 4; ++k) s[k] = ra.log[(size_t)ra.served - 1].sample[k];
+      return s;
+    }
+    krrt_ctx* c = session_->ctx();
+    session_->sync_tree();
+    session_->check(krrt_last_sample(c, s.data()));
     return s;
   }
   void configure(krrt_config& c) const {
@@ -366,6 +387,8 @@ class SoccerEnv {
     return hit != 0;
   }
   void configure(krrt_config& c) const { c.R = collision_radius; }
+  // the discs resident on the device are not (the current version of) this environment's
+  bool stale(const krrt::Session& s) const { return !(s.obstacle_owner == this && s.obstacle_version == version_); }
   // make this environment's discs the ones resident on the device (two environments share one tree/session)
   void upload(krrt::Session& s) {
     static_assert(sizeof(std::array<double, 4>) == 4 * sizeof(double), "obstacle layout");

@@ -119,6 +119,21 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]);
  * host doubles; a row whose first entry is NaN means "draw from the internal Philox sampler". */
 int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved,
               int* goal_index);
+/* The caller's loop `for (i < iteration) solved = rrt.grow(xg)` (…node.cpp:176-185) as ONE device call: the tree after the
+ * call is the tree n_iter single krrt_grow(ctx, goal, 1, row i) calls leave, and records[i] holds what call i would have
+ * returned and what the getters the loop reads after it would have said (tree size, last sample).  include/rrtstar.hpp
+ * serves the unchanged per-iteration loop from such a record.  1 <= n_iter <= 256, tree size after the call <= 1024,
+ * else KRRT_ERR_UNSUPPORTED (use krrt_grow).  An iteration the tree had no room for repeats the previous record. */
+typedef struct krrt_iter_record {
+  int32_t n_nodes;     /* tree.tree.size() after the iteration                       (…node.cpp:179-180) */
+  int32_t solved;      /* what rrt.grow(xg) returns                                  (…node.cpp:177)     */
+  int32_t goal_index;  /* rrt.goalIndex() at that point, -1 when not solved                               */
+  int32_t inserted;    /* the iteration added a node ("ok" / "failed" of …node.cpp:179)                   */
+  double sample[4];    /* sampler.last_sample()                                      (…node.cpp:178)     */
+  double goal_cost;    /* cost-to-come of the goal node when solved                                       */
+} krrt_iter_record;
+int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, krrt_iter_record* records,
+                     int* solved, int* goal_index);
 /* how the last krrt_grow call ended: the iterations it really ran and whether it stopped because the tree had reached
  * `capacity` (the call itself returns KRRT_OK: the tree is valid, only shorter than asked for) */
 int krrt_grow_done(krrt_ctx* ctx, int64_t* iterations_done, int* full);

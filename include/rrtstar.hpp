@@ -15,11 +15,14 @@
 #ifndef KRRT_RRTSTAR_HPP
 #define KRRT_RRTSTAR_HPP
 
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <vector>
 
 #include "krrt.h"
 
@@ -33,9 +36,57 @@ struct Error : std::runtime_error {
 // One device context shared by the components of a planner (and by the static / dynamic planner pair, which
 // share one tree in the reference: …node.cpp:60-61).  Created lazily so that constructing the singletons
 // does not touch the GPU; re-created only when a create-time field (capacity, device) changes.
+// Run-ahead of the caller's per-iteration loop.  The node calls rrt.grow(xg) once per iteration (…node.cpp:176-185) and
+// reads tree.tree.size() and sampler.last_sample() after every call; one device call per iteration costs ~60 us of launch
+// and read-back latency.  The planner is deterministic (counter-based samples), so the first grow(xg) of a cycle runs the
+// iterations that are LIKELY to follow — as many as the cycle before had, with the goal forced as the sample where the
+// caller forced it last time (…node.cpp:183-184) — in ONE logged device call (krrt_grow_logged), and the following
+// calls are answered from its per-iteration records.  Every call is checked against what was assumed (same goal, same forced
+// sample or none); on a mismatch, or when the tree is read while the device is ahead of the caller, the device tree is
+// rebuilt at the caller's iteration by replaying the cycle from its start (same samples -> the same tree, bit for bit).
+// What the caller sees is therefore exactly what one device call per iteration gives (tests/native/host_surface_check.cpp
+// runs the node's loop against the CPU checker call by call).  KRRT_RUN_AHEAD=0 in the environment switches it off.
+struct RunAhead {
+  struct Forced { long at; double x[4]; };
+  struct GoalSeg { long from; bool has; double g[4]; };
+  bool enabled = true;
+  std::vector<krrt_iter_record> log;  // record of iteration i of the current cycle (n_nodes < 0: not recorded)
+  long served = 0;                    // iterations handed to the caller since setStart
+  long ahead = 0;                     // iterations the device tree has run since setStart (>= served)
+  double start[4] = {0, 0, 0, 0};
+  std::vector<Forced> forced;         // explicit sample rows the device used in [0, ahead): the caller's and the assumed ones
+  std::vector<GoalSeg> goals;         // goal handed to grow() from iteration `from` on
+  long last_len = 0;                  // iterations of the cycle before
+  std::vector<long> last_goal_forced_at, goal_forced_at;  // where the caller forced the goal as the sample (before / now)
+  long replays = 0, device_calls = 0;  // diagnostics
+
+  const Forced* forced_at(long i) const {
+    for (const Forced& f : forced)
+      if (f.at == i) return &f;
+    return nullptr;
+  }
+  const GoalSeg* goal_at(long i) const {
+    const GoalSeg* r = nullptr;
+    for (const GoalSeg& g : goals)
+      if (g.from <= i) r = &g;
+    return r;
+  }
+  static bool same4(const double* a, const double* b) { return a[0] == b[0] && a[1] == b[1] && a[2] == b[2] && a[3] == b[3]; }
+  void note_goal(long i, bool has, const double* g) {
+    const GoalSeg* cur = goal_at(i);
+    if (cur && cur->has == has && (!has || same4(cur->g, g))) return;
+    GoalSeg n{i, has, {0, 0, 0, 0}};
+    if (has) std::memcpy(n.g, g, sizeof(n.g));
+    goals.push_back(n);
+  }
+};
+
 class Session {
  public:
-  Session() { krrt_default_config(&cfg_); }
+  Session() {
+    krrt_default_config(&cfg_);
+    if (const char* e = std::getenv("KRRT_RUN_AHEAD")) ra_.enabled = std::atoi(e) != 0;
+  }
   ~Session() { krrt_destroy(ctx_); }
   Session(const Session&) = delete;
   Session& operator=(const Session&) = delete;
@@ -59,10 +110,57 @@ class Session {
       live_ = cfg_;
       ++epoch_;
     } else if (std::memcmp(&cfg_, &live_, sizeof(cfg_)) != 0) {
+      sync_tree();  // iterations run ahead were run with the settings that are live now: settle the tree before they change
       check(krrt_set_params(ctx_, &cfg_));
       live_ = cfg_;
     }
     return ctx_;
+  }
+  RunAhead& run_ahead() { return ra_; }
+  // a new cycle (rrt.setStart): remember how the last one went, forget its records
+  void begin_cycle(const double x0[4]) {
+    if (ra_.served > 0) {
+      ra_.last_len = ra_.served;
+      ra_.last_goal_forced_at = ra_.goal_forced_at;
+    }
+    ra_.log.clear();
+    ra_.forced.clear();
+    ra_.goals.clear();
+    ra_.goal_forced_at.clear();
+    ra_.served = ra_.ahead = 0;
+    std::memcpy(ra_.start, x0, sizeof(ra_.start));
+  }
+  // the device tree at the caller's iteration: anything that reads the tree, or changes what it is grown with, calls this first
+  void sync_tree() {
+    if (ctx_ && started && ra_.ahead > ra_.served) rewind_to(ra_.served);
+  }
+  // rebuild the device tree as it stood after iteration i - 1 of the cycle: restart + replay (same samples, same tree)
+  void rewind_to(long i) {
+    check(krrt_set_start(ctx_, ra_.start));
+    std::vector<double> rows;
+    for (size_t k = 0; k < ra_.goals.size() && ra_.goals[k].from < i; ++k) {
+      const RunAhead::GoalSeg& seg = ra_.goals[k];
+      const long lo = seg.from, hi = (k + 1 < ra_.goals.size() && ra_.goals[k + 1].from < i) ? ra_.goals[k + 1].from : i;
+      if (hi <= lo) continue;
+      rows.assign((size_t)(hi - lo) * 4, std::nan(""));
+      bool any = false;
+      for (const RunAhead::Forced& f : ra_.forced)
+        if (f.at >= lo && f.at < hi) {
+          std::memcpy(&rows[(size_t)(f.at - lo) * 4], f.x, sizeof(f.x));
+          any = true;
+        }
+      int solved = 0, gi = -1;
+      check(krrt_grow(ctx_, seg.has ? seg.g : nullptr, (int)(hi - lo), any ? rows.data() : nullptr, &solved, &gi));
+      ++ra_.device_calls;
+    }
+    ra_.ahead = i;
+    if ((long)ra_.log.size() > i) ra_.log.resize((size_t)i);
+    for (size_t k = ra_.forced.size(); k-- > 0;)
+      if (ra_.forced[k].at >= i) ra_.forced.erase(ra_.forced.begin() + (long)k);
+    while (!ra_.goals.empty() && ra_.goals.back().from >= i && i > 0) ra_.goals.pop_back();
+    if (i == 0) ra_.goals.clear();
+    ++ra_.replays;
+    touch();
   }
   void check(int rc) const {
     if (rc != KRRT_OK) throw Error(rc, krrt_last_error(ctx_));
@@ -76,6 +174,7 @@ class Session {
 
  private:
   krrt_config cfg_{}, live_{};
+  RunAhead ra_;
   krrt_ctx* ctx_ = nullptr;
   unsigned long version_ = 1, epoch_ = 0;
 };
@@ -108,6 +207,7 @@ class RRTStar {
     krrt::Session& s = tree_.session();
     push_config(s);
     const double x0[4] = {xs(0), xs(1), xs(2), xs(3)};
+    s.begin_cycle(x0);  // (first: whatever was run ahead of the last cycle is dropped, not replayed)
     s.check(krrt_set_start(s.ctx(), x0));
     s.started = true;
     s.touch();
@@ -121,14 +221,98 @@ class RRTStar {
     iteration_ = 0;
   }
 
-  // == solved = rrt.grow(xg) (…node.cpp:177): ONE exact RRT* expansion
-  bool grow(State* xg) { return grow(xg, 1); }
+  // == solved = rrt.grow(xg) (…node.cpp:177): ONE exact RRT* expansion — answered from the run-ahead records when the
+  // call is the one that was assumed (krrt::RunAhead above), by a device call otherwise
+  bool grow(State* xg) {
+    krrt::Session& s = tree_.session();
+    if (!s.started) throw krrt::Error(KRRT_ERR_STATE, "grow before setStart");
+    krrt::RunAhead& ra = s.run_ahead();
+    if (!ra.enabled) return grow(xg, 1);
+    push_config(s);
+    krrt_ctx* c = s.ctx();
+    if (env_.stale(s)) {
+      s.sync_tree();  // (the iterations run ahead saw the discs that are resident now)
+      env_.upload(s);
+    }
+    double g[4] = {0, 0, 0, 0};
+    const bool has = xg != nullptr;
+    if (has)
+      for (int k = 0; k < 4; ++k) g[k] = (*xg)(k);
+    double fr[4];
+    const bool has_forced = sampler_.take_next_sample(fr);  // sampler.set_next_sample(x) (…node.cpp:184)
+    const long i = ra.served;
+    if (i < ra.ahead) {  // this iteration has been run ahead: was it run with what the caller hands over now?
+      const krrt::RunAhead::GoalSeg* gs = ra.goal_at(i);
+      const krrt::RunAhead::Forced* f = ra.forced_at(i);
+      const bool ok = gs && gs->has == has && (!has || krrt::RunAhead::same4(gs->g, g)) && ((f != nullptr) == has_forced) &&
+                      (!f || krrt::RunAhead::same4(f->x, fr)) && ra.log[(size_t)i].n_nodes >= 0;
+      if (!ok) s.rewind_to(i);
+    }
+    if (i == ra.ahead) {  // run this iteration and the ones that are likely to follow
+      ra.note_goal(i, has, g);
+      const int n_now = i > 0 && ra.log[(size_t)i - 1].n_nodes >= 0 ? ra.log[(size_t)i - 1].n_nodes : (i > 0 ? (int)tree_.device_size() : 1);
+      long L = ra.last_len > i ? ra.last_len - i : (i < 1 ? 1 : (i < 64 ? i : 64));
+      if (L > 256) L = 256;
+      if (n_now + L > 1024) L = 1024 - n_now;
+      std::vector<krrt_iter_record> recs;
+      int solved = 0, gi = -1, rc = KRRT_ERR_UNSUPPORTED;
+      if (L >= 1) {
+        std::vector<double> rows((size_t)L * 4, std::nan(""));
+        std::vector<krrt::RunAhead::Forced> assumed;
+        if (has_forced) {
+          krrt::RunAhead::Forced f{i, {fr[0], fr[1], fr[2], fr[3]}};
+          assumed.push_back(f);
+        }
+        if (has)
+          for (long p : ra.last_goal_forced_at)
+            if (p > i && p < i + L) {
+              krrt::RunAhead::Forced f{p, {g[0], g[1], g[2], g[3]}};
+              assumed.push_back(f);
+            }
+        for (const auto& f : assumed) std::memcpy(&rows[(size_t)(f.at - i) * 4], f.x, sizeof(f.x));
+        recs.resize((size_t)L);
+        rc = krrt_grow_logged(c, has ? g : nullptr, (int)L, assumed.empty() ? nullptr : rows.data(), recs.data(), &solved, &gi);
+        if (rc == KRRT_OK) ra.forced.insert(ra.forced.end(), assumed.begin(), assumed.end());
+      }
+      if (rc == KRRT_ERR_UNSUPPORTED) {  // a tree too large for per-iteration records: one plain device call for this iteration
+        s.check(krrt_grow(c, has ? g : nullptr, 1, has_forced ? fr : nullptr, &solved, &gi));
+        if (has_forced) {
+          krrt::RunAhead::Forced f{i, {fr[0], fr[1], fr[2], fr[3]}};
+          ra.forced.push_back(f);
+        }
+        krrt_iter_record r{};
+        int n = 0;
+        s.check(krrt_tree_size(c, &n));
+        s.check(krrt_last_sample(c, r.sample));
+        r.inserted = n > n_now ? 1 : 0;
+        r.n_nodes = n;
+        r.solved = solved;
+        r.goal_index = gi;
+        recs.assign(1, r);
+        L = 1;
+      } else {
+        s.check(rc);
+      }
+      ++ra.device_calls;
+      ra.log.resize((size_t)i);
+      ra.log.insert(ra.log.end(), recs.begin(), recs.end());
+      ra.ahead = i + L;
+    }
+    const krrt_iter_record& r = ra.log[(size_t)i];
+    if (has_forced && has && krrt::RunAhead::same4(fr, g)) ra.goal_forced_at.push_back(i);
+    ra.served = i + 1;
+    ++iteration_;
+    s.touch();
+    goal_index_ = r.goal_index;
+    return r.solved != 0;
+  }
   // extension: n_iter expansions in one device call (identical tree to n_iter single calls)
   bool grow(State* xg, int n_iter) {
     krrt::Session& s = tree_.session();
     if (!s.started) throw krrt::Error(KRRT_ERR_STATE, "grow before setStart");
     push_config(s);
     krrt_ctx* c = s.ctx();
+    s.sync_tree();
     env_.upload(s);
     double g[4] = {0, 0, 0, 0};
     if (xg) {
@@ -150,6 +334,20 @@ class RRTStar {
       s.check(krrt_grow_done(c, &done, &full));
       iteration_ += (samples && n_iter > 1) ? done + 1 : done;
       full_ = full != 0;
+    }
+    {  // the cycle's history, should a replay be needed later: this call's goal and explicit first sample
+      krrt::RunAhead& ra = s.run_ahead();
+      ra.note_goal(ra.served, xg != nullptr, g);
+      if (samples) {
+        krrt::RunAhead::Forced f{ra.served, {forced[0], forced[1], forced[2], forced[3]}};
+        ra.forced.push_back(f);
+      }
+      krrt_iter_record none{};
+      none.n_nodes = -1;  // no per-iteration record: the getters ask the device
+      ra.log.resize((size_t)ra.served);
+      ra.log.resize((size_t)(ra.served + n_iter), none);
+      ra.served += n_iter;
+      ra.ahead = ra.served;
     }
     s.touch();
     goal_index_ = gi;

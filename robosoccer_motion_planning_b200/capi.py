@@ -25,7 +25,7 @@ I = ctypes.POINTER(ctypes.c_int32)
 
 # every symbol include/krrt.h declares (tests check the library exports all of them)
 EXPORTS = (
-    "krrt_default_config", "krrt_grow_done", "krrt_create", "krrt_destroy", "krrt_last_error", "krrt_device_count",
+    "krrt_default_config", "krrt_grow_done", "krrt_grow_logged", "krrt_create", "krrt_destroy", "krrt_last_error", "krrt_device_count",
     "krrt_set_obstacles", "krrt_set_start", "krrt_grow", "krrt_tree_size", "krrt_iteration", "krrt_last_sample",
     "krrt_get_stats", "krrt_tree_download", "krrt_path", "krrt_result_of", "krrt_trajectory", "krrt_steer_cost",
     "krrt_solve", "krrt_edge_collide", "krrt_near", "krrt_plan_batch", "krrt_plan_batch_device",
@@ -61,6 +61,10 @@ class KrrtStats(ctypes.Structure):
 RESULT_DTYPE = np.dtype([
     ("solved", "<i4"), ("goal_index", "<i4"), ("n_nodes", "<i4"), ("path_len", "<i4"),
     ("cost", "<f8"), ("time", "<f8"), ("waypoints", "<f8", (KRRT_MAX_WAYPOINTS, 5))])
+
+
+ITER_RECORD_DTYPE = np.dtype([("n_nodes", "<i4"), ("solved", "<i4"), ("goal_index", "<i4"), ("inserted", "<i4"),
+                              ("sample", "<f8", (4,)), ("goal_cost", "<f8")])   # == krrt_iter_record
 
 
 class KrrtError(RuntimeError):
@@ -106,6 +110,7 @@ def lib():
     L.krrt_grow.argtypes = [P, D, ctypes.c_int, D, I, I]
     L.krrt_tree_size.argtypes = [P, I]
     L.krrt_grow_done.argtypes = [P, ctypes.POINTER(ctypes.c_int64), I]
+    L.krrt_grow_logged.argtypes = [P, D, ctypes.c_int, D, ctypes.c_void_p, I, I]
     L.krrt_iteration.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
     L.krrt_last_sample.argtypes = [P, D]
     L.krrt_get_stats.argtypes = [P, ctypes.POINTER(KrrtStats)]
@@ -262,6 +267,22 @@ class Planner:
         gi = ctypes.c_int32(-1)
         self._ck(lib().krrt_grow(self.h, g, int(n_iter), s, ctypes.byref(solved), ctypes.byref(gi)))
         return bool(solved.value), gi.value
+
+    # the caller's `for(i<iteration) rrt.grow(xg)` loop as ONE device call (…node.cpp:176-185): per-iteration records
+    def grow_logged(self, goal, n_iter, samples=None):
+        g = None
+        if goal is not None:
+            goal = _f64(goal, (4,))
+            g = _d(goal)
+        s = None
+        if samples is not None:
+            samples = _f64(samples, (n_iter, 4))
+            s = _d(samples)
+        rec = np.zeros(n_iter, dtype=ITER_RECORD_DTYPE)
+        solved = ctypes.c_int32(0)
+        gi = ctypes.c_int32(-1)
+        self._ck(lib().krrt_grow_logged(self.h, g, int(n_iter), s, rec.ctypes.data, ctypes.byref(solved), ctypes.byref(gi)))
+        return rec, bool(solved.value), gi.value
 
     def grow_done(self):
         """(iterations the last grow call really ran, whether it stopped because the tree is full)"""

@@ -81,6 +81,9 @@ struct krrt_ctx {
   double last_total_ms = 0.0, last_scan_ms = 0.0;
   int64_t last_scan_launches = 0;
   double last_scan_node_samples = 0.0;
+  unsigned char* d_iterlog = nullptr;  // krrt_grow_logged: one allocation behind the IterLog views + the records
+  IterLog ilog = {nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  IterRec* d_iterrec = nullptr;
   int64_t last_grow_iters = 0;  // iterations the last krrt_grow call really ran (fewer than asked when the tree filled up)
   int last_grow_full = 0;
 };
@@ -182,6 +185,7 @@ void krrt_destroy(krrt_ctx* ctx) {
   for (void* p : ctx->d_scratch)
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
+  if (ctx->d_iterlog) cudaFree(ctx->d_iterlog);
   if (ctx->d_flush) cudaFree(ctx->d_flush);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
   if (ctx->d_redo) cudaFree(ctx->d_redo);
@@ -461,10 +465,17 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
 
 // before every k_grow launch: barrier counter, empty candidate lists, armed prefix slots; `first`: a new krrt_grow call
 __global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, GridBar* bar,
-                             int reset_round) {
+                             int reset_round, TreeView T, IterLog Lg) {
   for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {
     Bt.count[b] = 0;
     Bt.dup[b] = 0;
+  }
+  if (first && Lg.n_after) {  // logged call: row 0 of the snapshots is the tree before the call
+    const int n = ctl->n;
+    for (int j = threadIdx.x; j < n && j < Lg.stride; j += blockDim.x) {
+      Lg.snap_ctc[j] = T.ctc[j];
+      Lg.snap_tim[j] = T.tim[j];
+    }
   }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   bar[0].arrive = 0ull;
@@ -502,7 +513,31 @@ static int fetch_ctl(krrt_ctx* ctx, Ctl* h) {
   return KRRT_OK;
 }
 
+constexpr int ITERLOG_MAX_ITERS = 256;   // iterations one logged call can record
+constexpr int ITERLOG_STRIDE = 1024;     // nodes a snapshot row holds
+
+static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index,
+                     krrt_iter_record* records);
+
 int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index) {
+  return grow_impl(ctx, goal, n_iter, samples, solved, goal_index, nullptr);
+}
+
+// The caller's own loop `for(i<iteration) solved = rrt.grow(xg)` (robosoccer_motion_planning_node.cpp:176-185) in ONE device
+// call: the same tree as n_iter single calls, plus what each of those calls would have returned (include/krrt.h)
+int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, krrt_iter_record* records,
+                     int* solved, int* goal_index) {
+  if (!ctx || !records) return KRRT_ERR_INVALID;
+  F64_ONLY();
+  REQUIRE(n_iter >= 1 && n_iter <= ITERLOG_MAX_ITERS, KRRT_ERR_UNSUPPORTED, "krrt_grow_logged: 1 <= n_iter <= 256");
+  REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow_logged before krrt_set_start");
+  REQUIRE(ctx->n_upper + n_iter <= ITERLOG_STRIDE, KRRT_ERR_UNSUPPORTED,
+          "krrt_grow_logged: the tree would outgrow the 1024 nodes a logged call can record; use krrt_grow");
+  return grow_impl(ctx, goal, n_iter, samples, solved, goal_index, records);
+}
+
+static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index,
+                     krrt_iter_record* records) {
   if (!ctx) return KRRT_ERR_INVALID;
   F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
@@ -529,6 +564,27 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
   gcfg.user_samples = samples ? ctx->d_user : nullptr;
   gcfg.bar = ctx->d_bar;
   gcfg.gi = ctx->gi;
+  gcfg.log = IterLog{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  const int n_before = ctx->n_upper;  // (exact: every grow call ends with a read-back of the control block)
+  if (records) {
+    if (!ctx->d_iterlog) {
+      const size_t rows = ITERLOG_MAX_ITERS + 1, it = ITERLOG_MAX_ITERS;
+      const size_t b_snap = rows * ITERLOG_STRIDE * sizeof(double), b_smp = it * 4 * sizeof(double), b_int = it * sizeof(int),
+                   b_rec = it * sizeof(IterRec);
+      CK(cudaMalloc((void**)&ctx->d_iterlog, 2 * b_snap + b_smp + b_rec + 2 * b_int));
+      unsigned char* q = ctx->d_iterlog;
+      ctx->ilog.snap_ctc = (double*)q; q += b_snap;
+      ctx->ilog.snap_tim = (double*)q; q += b_snap;
+      ctx->ilog.sample = (double*)q; q += b_smp;
+      ctx->d_iterrec = (IterRec*)q; q += b_rec;
+      ctx->ilog.n_after = (int*)q; q += b_int;
+      ctx->ilog.snap_of = (int*)q;
+      ctx->ilog.stride = ITERLOG_STRIDE;
+      ctx->ilog.rows = (int)rows;
+    }
+    gcfg.log = ctx->ilog;
+    gcfg.wave_enabled = 0;  // every iteration goes through the in-order commit, which keeps the records
+  }
   {  // sub-round sizing (profiles/r1_param_sweep.txt); the environment overrides are for sweeps
     auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
     gcfg.pend_resolve = envi("KRRT_PEND", 1);
@@ -556,13 +612,17 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       CK(cudaMemsetAsync(ctx->W.ok, 0, sizeof(unsigned) * 1024, st));
     }
     ctx->ctl_valid = false;
-    k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0);
+    k_begin_grow<<<1, 32, 0, st>>>(ctx->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, ctx->Bt, ctx->d_bar, wrap ? 1 : 0, ctx->T,
+                                   gcfg.log);
     void* args[] = {(void*)&ctx->d_ctl, (void*)&ctx->P, (void*)&ctx->T, (void*)&ctx->Bt, (void*)&ctx->W, (void*)&gcfg};
     // A call of a few expansions that leaves the tree below the size where sub-rounds start (the node's own pattern:
     // one grow(xg) per iteration on 75-200-node trees, config/config.yaml:3) is committed in order by one warp whatever
     // the grid: it gets ONE CTA and a plain launch — no co-residency check, no grid-wide barriers (85 -> 58 us per call).
     // Longer calls keep the full grid: their windows of 32 samples are scanned and steered by all SMs.
-    const bool small = n_iter <= 4 && ctx->n_upper + n_iter < ctx->small_max_n && !std::getenv("KRRT_NO_SMALL");
+    // (a logged call of up to 256 iterations on a tree that stays below 512 nodes likewise: its windows of 64 samples are a
+    // few thousand pairs, and the in-order commit is one warp anyway)
+    const bool small = ((n_iter <= 4 && ctx->n_upper + n_iter < ctx->small_max_n) || (records && ctx->n_upper + n_iter <= 512)) &&
+                       !std::getenv("KRRT_NO_SMALL");
     if (small) {
       GrowCfg one = gcfg;
       one.wave_enabled = 0;  // a single CTA cannot run sub-rounds; in order is what a sequential planner does anyway
@@ -579,6 +639,12 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
       const int ctas = (int)std::max<long long>(1, std::min<long long>(std::min(GOAL_MAX_CTAS, 4 * ctx->prop.multiProcessorCount),
                                                                        (n_max + GOAL_THREADS - 1) / GOAL_THREADS));
       k_goal_connect<<<ctas, GOAL_THREADS, 0, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->goal_scr);
+    }
+    if (records) {
+      static_assert(sizeof(IterRec) == sizeof(krrt_iter_record), "IterRec mirrors krrt_iter_record");
+      k_goal_log<<<n_iter, GLOG_THREADS, 0, st>>>(ctx->d_ctl, ctx->P, ctx->T, gcfg.log, n_iter, n_before, ctx->d_iterrec);
+      CK(cudaMemcpyAsync(records, ctx->d_iterrec, sizeof(IterRec) * (size_t)n_iter, cudaMemcpyDeviceToHost, st));
+      ctx->launches += 1;
     }
     CK(cudaEventRecord(ctx->ev1, st));
     ctx->launches += 3;

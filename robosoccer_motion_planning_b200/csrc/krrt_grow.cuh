@@ -101,6 +101,7 @@ struct GrowCfg {
   int prop_forward;            // a near node whose cost an earlier sample's PROPAGATION changes: re-check with the new cost
   int intra_fix;               // a rewire candidate that is a CHILD of a node the same sample rewires is settled in decide (0: in-order path)
   int tail_seq;                // a sample that needs the in-order path right behind the prefix is committed in the same sub-round
+  IterLog log;                 // krrt_grow_logged: per-iteration records of the in-order commit (n_after == nullptr: off)
   int nb_mul, nb_add, nb_min;  // samples decided per sub-round = max(nb_min, nb_mul x mean prefix + nb_add)
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
 };
@@ -253,7 +254,7 @@ __device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm,
 // when it needs the sequential path).  smem: obstacles + near list (commit_smem_bytes).
 // nn_idx >= 0: the nearest node of sample b0 over the whole tree (found by a grid-wide scan), used if its near set is empty.
 __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
-                                        unsigned char* smem, int b0, int b1, int nn_idx, double nn_d2) {
+                                        unsigned char* smem, int b0, int b1, int nn_idx, double nn_d2, const IterLog& Lg) {
   const int lane = lane_id();
   const int cap = Bt.near_cap;
   double4* s_obs = reinterpret_cast<double4*>(smem);
@@ -273,16 +274,39 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
   long long iter = __ldcg(&ctl->iter);
   int full = 0, error = 0;
   State4 s = {0, 0, 0, 0};
+  // logged call: what iteration `iter` left behind (the tree's costs are copied only when the tree changed)
+  const long long iter_begin = Lg.n_after ? __ldcg(&ctl->iter_begin) : 0;
+  auto log_iter = [&](bool changed) {
+    if (!Lg.n_after) return;
+    const long long i = iter - iter_begin - 1;
+    if (i < 0 || i >= Lg.rows - 1) return;
+    __syncwarp();
+    const int row = changed ? (int)i + 1 : (i > 0 ? Lg.snap_of[i - 1] : 0);
+    if (changed) {
+      for (int j = lane; j < n && j < Lg.stride; j += 32) {
+        Lg.snap_ctc[(size_t)row * Lg.stride + j] = __ldcg(&T.ctc[j]);
+        Lg.snap_tim[(size_t)row * Lg.stride + j] = __ldcg(&T.tim[j]);
+      }
+    }
+    if (lane == 0) {
+      Lg.n_after[i] = n;
+      Lg.snap_of[i] = row;
+      Lg.sample[4 * i + 0] = s.x; Lg.sample[4 * i + 1] = s.y; Lg.sample[4 * i + 2] = s.vx; Lg.sample[4 * i + 3] = s.vy;
+    }
+    __syncwarp();
+  };
   for (int b = b0; b < b1; ++b) {
     s = Bt.samples[b];
     ++iter;
     st.iters++;
     if (!P.dynamic && __ldcg(&Bt.reject[b])) {
       st.fail_reject++;
+      log_iter(false);
       continue;
     }
     if (n >= P.capacity) {
       full = 1;
+      log_iter(false);
       break;
     }
     const int cnt = __ldcg(&Bt.count[b]);
@@ -320,6 +344,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
     }
     if (__any_sync(FULL, dup)) {
       st.fail_dup++;
+      log_iter(false);
       continue;
     }
     if (K == 0) {  // empty near set: exact nearest over the whole tree (rare once the tree is dense)
@@ -328,6 +353,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
       if (ni < 0 || b != b0) warp_nearest(T, n, s, ni, nd2);
       if (nd2 == 0.0) {
         st.fail_dup++;
+        log_iter(false);
         continue;
       }
       if (lane == 0) {
@@ -349,6 +375,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
       n = nw + 1;
     }
     __syncwarp();
+    log_iter(nw >= 0);
   }
   if (lane == 0) {
     ctl->n = n;
@@ -686,7 +713,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
 
     if (!wave) {  // small tree: the whole window in order, one warp
       if (last && t < 32) {
-        seq_commit(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0);
+        seq_commit(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0, cfg.log);
         __syncwarp();
         clear_window(Bt);
         if (t == 0) ctl->rounds_seq += 1;
@@ -1509,7 +1536,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           int ni = -1;
           double nd2 = 0.0;
           if (need_nn) nn_fold(ni, nd2);
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2);
+          seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2, cfg.log);
           if (lane == 0) {
             ctl->ema16 = (3 * ema_sub + 16) / 4;
             sm.fin[11] += 1;  // rounds_seq
@@ -1526,7 +1553,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           int ni = -1;
           double nd2 = 0.0;
           if (tail_nn) nn_fold(ni, nd2);
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2);
+          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2, cfg.log);
           if (t == 0) sm.fin[18] += 1;  // tail commits
         }
         __syncwarp();

@@ -88,6 +88,25 @@ struct Batch {
   int near_cap;
 };
 
+// Per-iteration record of a logged call (krrt_grow_logged: the caller's own `for(i<iteration) rrt.grow(xg)` loop,
+// robosoccer_motion_planning_node.cpp:176-185, served from ONE device call).  The in-order commit leaves, per iteration, the
+// tree size, the sample, and — whenever the tree changed — a snapshot of every node's cost-to-come and arrival time
+// (row 0: the tree before the call); k_goal_log then works out what grow(xg) would have returned after each iteration.
+struct IterLog {
+  int* n_after;      // [rows - 1] tree size after iteration i of the call (nullptr: logging off)
+  int* snap_of;      // [rows - 1] snapshot row that holds the tree's costs after iteration i
+  double* sample;    // [rows - 1][4]
+  double* snap_ctc;  // [rows][stride]
+  double* snap_tim;
+  int stride;        // nodes a snapshot row holds
+  int rows;          // 1 + iterations the buffers hold
+};
+struct IterRec {     // layout == krrt_iter_record (include/krrt.h)
+  int n_nodes, solved, goal_index, inserted;
+  double sample[4];
+  double goal_cost;
+};
+
 // ---------------------------------------------------------------------------------------------------
 // Per-sample decision of a sub-round (krrt_grow.cuh) and the conflict marks it is validated with.
 enum { OUT_REJECT = 0, OUT_DUP = 1, OUT_NOFREE = 2, OUT_INSERT = 3, OUT_COMPLEX = 4, OUT_CONFLICT = 5,
@@ -290,6 +309,86 @@ __global__ void __launch_bounds__(GOAL_THREADS) k_goal_connect(Ctl* ctl, Params 
       }
     }
     ctl->goal_index = gi;
+  }
+}
+
+// grow(xg)'s answer after EVERY iteration of a logged call: block i redoes the goal connection (k_goal_connect's rule) on
+// the tree as it stood after iteration i — node states never change, costs and arrival times come from the snapshot row.
+constexpr int GLOG_THREADS = 128;
+__global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Params P, TreeView T, IterLog L, int n_iter,
+                                                           int n_before, IterRec* out) {
+  __shared__ double4 s_obs[KRRT_MAX_OBS_DEV];
+  __shared__ double s_c[GLOG_THREADS / 32];
+  __shared__ int s_i[GLOG_THREADS / 32];
+  const int t = threadIdx.x, it = blockIdx.x;
+  if (it >= n_iter) return;
+  const int n = L.n_after[it];
+  const int row = L.snap_of[it];
+  const int n_prev = it > 0 ? L.n_after[it - 1] : n_before;
+  const double* ctc = L.snap_ctc + (size_t)row * L.stride;
+  const double* tim = L.snap_tim + (size_t)row * L.stride;
+  for (int j = t; j < P.m; j += GLOG_THREADS) s_obs[j] = P.obs[j];
+  __syncthreads();
+  double bc = INFINITY;
+  int bi = -1, aux = 0;
+  const bool has_goal = ctl->has_goal != 0;
+  const State4 g = {ctl->goal[0], ctl->goal[1], ctl->goal[2], ctl->goal[3]};
+  if (has_goal && P.goal_mode == GOAL_MODE_TOLERANCE) {
+    for (int i = t; i < n; i += GLOG_THREADS)
+      if (dist2(load_state(T, i), g) <= P.goal_tol2) {
+        const double c = ctc[i];
+        if (c < bc) {
+          bc = c;
+          bi = i;
+        }
+      }
+  } else if (has_goal) {
+    for (int i = 1 + t; i < n; i += GLOG_THREADS) {
+      const State4 x = load_state(T, i);
+      const bool same = dist2(x, g) == 0.0;
+      double tg = 0.0, cg = 0.0;
+      if (!same) steer(x, g, P.r, tg, cg);
+      const double cand = ctc[i] + cg;
+      if (bi >= 0 && cand >= bc) continue;
+      bool hit = false;
+      if (!same && P.m > 0) {
+        const Edge e = make_edge(x, g, tg, tim[i]);
+        for (int k = 0; k < P.S && !hit; ++k) {
+          const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : 0.0;
+          hit = edge_point_hits_any(e, h, s_obs, P.m, P.dynamic, P.R2);
+        }
+      }
+      if (!hit) {
+        bc = cand;
+        bi = i;
+      }
+    }
+  }
+  warp_argmin(bc, bi, aux);
+  if ((t & 31) == 0) {
+    s_c[t >> 5] = bc;
+    s_i[t >> 5] = bi;
+  }
+  __syncthreads();
+  if (t < 32) {
+    bc = t < GLOG_THREADS / 32 ? s_c[t] : INFINITY;
+    bi = t < GLOG_THREADS / 32 ? s_i[t] : -1;
+    warp_argmin(bc, bi, aux);
+    if (t == 0) {
+      IterRec r;
+      r.n_nodes = n;
+      r.inserted = n > n_prev ? 1 : 0;
+      r.solved = bi >= 0 ? 1 : 0;
+      r.goal_index = -1;
+      r.goal_cost = 0.0;
+      if (bi >= 0) {
+        const bool node_is_goal = P.goal_mode == GOAL_MODE_TOLERANCE || dist2(load_state(T, bi), g) == 0.0;
+        r.goal_index = node_is_goal ? bi : n;
+        r.goal_cost = bc;
+      }
+      for (int k = 0; k < 4; ++k) r.sample[k] = L.sample[4 * (size_t)it + k];
+      out[it] = r;
+    }
   }
 }
 

@@ -7,6 +7,7 @@
 // TEST ONLY: also links oracle/_build/libkrrt_oracle.so and checks the tree grown through the C++ surface
 // bit-for-bit against the CPU oracle fed the same calls.  Usage: host_surface_check [static|dynamic] [iterations]
 // Exit 0 = identical; 3 = no GPU (the surface threw krrt::Error with KRRT_ERR_NO_DEVICE, as it must).
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -207,6 +208,73 @@ int main(int argc, char** argv) {
       EXPECT((int)tree.tree.size() == ko_size(oracle) && rr.goalIndex() == ogi);
       const std::vector<int>& p2 = tree.parent;
       for (size_t i = 0; i < p2.size(); ++i) EXPECT(p2[i] == ko_parents(oracle)[i]);
+    }
+    // The run-ahead of the per-iteration loop (krrt::RunAhead, include/rrtstar.hpp): whatever the caller does — the same
+    // cycle again, a longer one, a shorter one, a tree read-out in the middle of the loop, another goal from some
+    // iteration on, a forced sample where none was the cycle before — every single call answers as the CPU checker does.
+    if (target_size >= 60) {
+      auto& rr = Kinodynamic::Wrapper::get_rrtstar_int2d();
+      krrt::RunAhead& ra = Kinodynamic::Wrapper::get_session().run_ahead();
+      auto run_cycle = [&](int iters, int read_at, int goal_change_at, int force_at) {
+        rr.setStart(start);
+        rr.setIteration(0);
+        env.setObstacles(obstacles);
+        ko_set_obstacles(oracle, obstacles[0].data(), 9, 0);
+        ko_set_start(oracle, start.data());
+        auto g = xg;
+        bool forced = false;
+        Kinodynamic::TreeInt2D::State frow = g;
+        for (int i = 0; i < iters; ++i) {
+          if (i == goal_change_at) {
+            g(0) = 6.0;
+            g(1) = 2.5;
+          }
+          if (i == force_at) {
+            Kinodynamic::TreeInt2D::State x;
+            x(0) = 1.0; x(1) = -2.0; x(2) = 0.5; x(3) = 0.25;
+            sampler.set_next_sample(x);
+            forced = true;
+            frow = x;
+          }
+          const bool sv = rr.grow(&g);
+          const double nan_row[4] = {std::nan(""), 0, 0, 0};
+          const int osv = ko_grow(oracle, g.data(), 1, forced ? frow.data() : nan_row, &ogi);
+          forced = false;
+          EXPECT(sv == (osv != 0));
+          EXPECT(rr.goalIndex() == ogi);
+          const auto ls = sampler.last_sample();
+          const double* os = ko_last_sample(oracle);
+          EXPECT(ls(0) == os[0] && ls(1) == os[1] && ls(2) == os[2] && ls(3) == os[3]);
+          EXPECT((int)tree.tree.size() == ko_size(oracle));
+          if (i == read_at) {
+            const std::vector<int>& pp = tree.parent;
+            for (size_t k = 0; k < (size_t)ko_size(oracle) && k < pp.size(); ++k) EXPECT(pp[k] == ko_parents(oracle)[k]);
+          }
+          if (i == iters - 2 || i == iters / 2) {
+            sampler.set_next_sample(g);
+            forced = true;
+            frow = g;
+          }
+        }
+        double dummy[4];
+        sampler.take_next_sample(dummy);  // (a sample forced behind the last iteration is not carried into the next cycle)
+        const std::vector<int>& pp = tree.parent;
+        EXPECT((int)tree.tree.size() == ko_size(oracle));
+        for (size_t k = 0; k < (size_t)ko_size(oracle) && k < pp.size(); ++k) {
+          EXPECT(pp[k] == ko_parents(oracle)[k]);
+          EXPECT(tree.cost()[k] == ko_ctc(oracle)[k]);
+        }
+      };
+      const int N = (int)target_size - 13;
+      run_cycle(N, -1, -1, -1);
+      const long c0 = ra.device_calls, r0 = ra.replays;
+      run_cycle(N, -1, -1, -1);
+      // the steady state: ONE device call per cycle (per 256 iterations: what one logged call records), nothing replayed
+      if (ra.enabled) EXPECT(ra.device_calls - c0 == (N + 255) / 256 && ra.replays == r0);
+      run_cycle((int)target_size, 7, 20, 31);
+      run_cycle(N / 2, -1, -1, -1);
+      run_cycle(N / 2, 3, -1, 5);
+      std::printf("run-ahead: %ld device calls, %ld replays over 5 cycles\n", ra.device_calls, ra.replays);
     }
     ko_destroy(oracle);
     std::printf("%s: %s, %zu nodes, goalIndex %d, %d check failure(s)\n", dynamic ? "dynamic" : "static",

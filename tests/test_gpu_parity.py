@@ -194,9 +194,10 @@ def test_capacity_full(gpu_required):
         P.grow(scenes.GOAL, 500)
     done, full = G.grow_done()               # the call returns KRRT_OK; how it ended is on record
     assert full and done < 500 and done == O.iteration
+    it0 = O.iteration
     for P in (G, O):
         P.grow(scenes.GOAL, 3)
-    assert G.grow_done() == (0, True)
+    assert G.grow_done() == (O.iteration - it0, True)   # (the iteration that finds the tree full is consumed, on both sides)
     assert G.size == O.size == 300
     assert_same_tree(G, O)
 
@@ -673,3 +674,36 @@ def test_plan_batch_goal_rule(gpu_required, goal_mode, dynamic, p_direct):
     finally:
         del os.environ["KRRT_BATCH_V1"]
     assert out1.tobytes() == ref.tobytes()
+
+
+@pytest.mark.parametrize("dynamic,p_direct,goal_mode,n_iter", [(1, 0.1, 0, 75), (0, 0.0, 0, 100), (1, 0.2, 1, 200), (1, 0.1, 0, 256)])
+def test_grow_logged_equals_single_calls(gpu_required, dynamic, p_direct, goal_mode, n_iter):
+    """krrt_grow_logged: ONE device call for the caller's `for(i<iteration) rrt.grow(xg)` loop (…node.cpp:176-185).  Record i is
+    what single call i returns (solved, goalIndex) and what the loop reads after it (tree size, last sample); the tree after the
+    call is the tree of the single calls.  Forced goal samples (…node.cpp:183-184) ride along as explicit rows."""
+    kw = dict(goal_mode=goal_mode, goal_tol=0.8 if goal_mode else 0.0)
+    G, O = make_pair(gpu_required, dynamic=dynamic, capacity=2048, p_direct=p_direct, **kw)
+    rows = np.full((n_iter, 4), np.nan)
+    rows[n_iter // 2 + 1] = scenes.GOAL
+    rows[n_iter - 1] = scenes.GOAL
+    rec, solved, gi = G.grow_logged(scenes.GOAL, n_iter, rows)
+    n_prev = 1
+    for i in range(n_iter):
+        so, go = O.grow(scenes.GOAL, 1, samples=rows[i:i + 1])
+        assert (bool(rec["solved"][i]), int(rec["goal_index"][i])) == (so, go), i
+        assert rec["n_nodes"][i] == O.size and bool(rec["inserted"][i]) == (O.size > n_prev), i
+        assert np.array_equal(rec["sample"][i], O.last_sample()), i
+        if so:
+            assert rec["goal_cost"][i] == O.result(so, go)["cost"], i
+        n_prev = O.size
+    assert (solved, gi) == (so, go)
+    assert_same_tree(G, O)
+    # a second logged call continues the same tree
+    rec2, solved2, gi2 = G.grow_logged(scenes.GOAL, 40)
+    for i in range(40):
+        so, go = O.grow(scenes.GOAL, 1)
+        assert (bool(rec2["solved"][i]), int(rec2["goal_index"][i]), int(rec2["n_nodes"][i])) == (so, go, O.size), i
+    assert_same_tree(G, O)
+    with pytest.raises(capi.KrrtError) as e:
+        G.grow_logged(scenes.GOAL, 257)
+    assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
