@@ -40,6 +40,22 @@
 
 namespace krrt {
 
+// -DKRRT_CHECK (lib/libkrrt_check.so, `make check`; tests/test_switch_matrix.py runs the GPU suite's hardest plans on it):
+// every capacity the parallel commit relies on is asserted where it is used; a violation prints its code and traps, so the
+// host sees KRRT_ERR_CUDA with a message instead of a silently corrupted tree or an undiagnosed `illegal instruction`.
+#ifdef KRRT_CHECK
+#define KRRT_DCHECK(cond, code)                                                                                      \
+  do {                                                                                                               \
+    if (!(cond)) {                                                                                                   \
+      printf("krrt check %d failed: %s (cta %d thread %d, %s:%d)\n", (int)(code), #cond, (int)blockIdx.x, (int)threadIdx.x, \
+             __FILE__, __LINE__);                                                                                    \
+      __trap();                                                                                                      \
+    }                                                                                                                \
+  } while (0)
+#else
+#define KRRT_DCHECK(cond, code) do { } while (0)
+#endif
+
 constexpr int GROW_THREADS = 256;
 #ifndef KRRT_GROW_MINB
 #define KRRT_GROW_MINB 1   // CTAs of k_grow per SM the register allocation is held to.  2 (128 registers, 264 B of spills, 295 samples per
@@ -238,6 +254,7 @@ __device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm,
     const int2 lk = __ldcg(&T.link[c]);
     const double ec = __ldcg(&T.ecost[c]), et = __ldcg(&T.etime[c]);
     const int pos = atomicAdd(&sm.tail, 1);
+    KRRT_DCHECK(c >= 0 && c < T.cap, 101);  // a child link that leaves the tree
     if (pos < GROW_QCAP) {
       sm.u.d.wl[pos] = c;
       sm.u.d.wl_head[pos] = lk.x;
@@ -368,6 +385,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
       K = 1;
     }
     __syncwarp();
+    KRRT_DCHECK(K >= 1 && K <= cap && n >= 1 && n < P.capacity, 111);
     st.sum_near += K;
     int nw = warp_commit(T, N, K, n, s, E, st);
     if (nw >= 0) {
@@ -551,6 +569,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           const int cx = min(gw - 1, max(0, (int)floor((p.x - g_lox) * g_invx)));
           const int cy = min(gh - 1, max(0, (int)floor((p.y - g_loy) * g_invy)));
           const int slot = __ldcg(&cfg.gi.cell[cy * gw + cx]) + cfg.gi.off[i];
+          KRRT_DCHECK(slot >= 0 && slot < n0 && gw * gh <= GRID_CELLS_MAX, 112);
           cfg.gi.pos[slot] = p;
           cfg.gi.vel[slot] = __ldcg(&T.vel[i]);
           cfg.gi.id[slot] = i;
@@ -783,6 +802,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
         bool earlier_ins = false;
         if (t < cta) earlier_ins = sample_insertable(Bt, P, F0 + t);
         const bool rejected = !P.dynamic && rej_b;
+        KRRT_DCHECK(nb >= 1 && nb < GROW_THREADS && cta < 512, 106);  // one thread per earlier sample; 9-bit sample id of the marks
         if (t <= nb) sm.rho[t] = P.rho2[min(nsub + t, P.capacity)];
         s = Bt.samples[b];
         if (t == 0) {
@@ -833,6 +853,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
         State4 x = {0, 0, 0, 0};
         double my_tim = 0.0;
         int my_head = -1, my_par0 = -1;
+        KRRT_DCHECK(my_node < T.cap, 107);  // a candidate reference that leaves the tree
         if (my_node >= 0) {
           x = load_state_cg(T, my_node);
           my_ctc = __ldcg(&T.ctc[my_node]);
@@ -960,6 +981,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
         my_tried = tried;
         my_cand = cand;
         if (cand) {
+          KRRT_DCHECK(sm.ncand < GROW_THREADS && 2 * GROW_THREADS <= GROW_HASH, 102);  // candidate list / hash load <= 1/2
           sm.u.d.cand[atomicAdd(&sm.ncand, 1)] = t;
           // membership table of the REWIRE CANDIDATES (cleared before the barrier above): a candidate below another rewired
           // node would be tested against a cost that the first rewire has just lowered (rewires go in ascending index,
@@ -988,6 +1010,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
         DBG_STAMP(6);
         if (cand && !(sm.u.d.flag[t] & 8)) {  // candidate and free: rewired.  Its children seed the write list
           my_q = atomicAdd(&sm.nrew, 1);
+          KRRT_DCHECK(my_q >= 0 && my_q < GROW_THREADS && my_node >= 0 && my_node < T.cap, 103);
           sm.u.d.rewn[my_q] = my_node;
           sm.u.d.rslot[my_q] = t;
           sm.u.d.rpar[my_q] = my_par0;
@@ -1017,8 +1040,10 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           }
           ++nlvl;
           __syncthreads();  // every thread has read sm.tail before the next level pushes
+          KRRT_DCHECK(level1 <= GROW_QCAP && nlvl <= GROW_LEVELS + 1 && cta < 1024, 104);  // write list, level table, wlc row
           for (int q = level0 + t; q < level1; q += GROW_THREADS) {
             const int d = sm.u.d.wl[q];
+            KRRT_DCHECK(d >= 0 && d < T.cap, 105);
             atomicMax(&W.wmin[d], key);
             bool dead = false;
             for (unsigned hsl = near_hash(d);; hsl = (hsl + 1) & (GROW_HASH - 1)) {
@@ -1250,6 +1275,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
             int my_x = -1;
             if (need_a || need_b) {
               my_x = atomicAdd(&sm.nxe, 1);
+              KRRT_DCHECK(my_x >= 0 && pend_e >= F0 && pend_e < F0 + cta, 110);  // a newcomer is an EARLIER sample of this sub-round
               if (my_x < GROW_XE) {
                 sm.xe_a[my_x] = need_a ? xe_p : s;
                 sm.xe_b[my_x] = need_a ? s : xe_p;
@@ -1435,6 +1461,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
       DBG_START();
       if (active && cta < F && outcome == OUT_INSERT) {
         const int nw = n_true;
+        KRRT_DCHECK(nw > 0 && nw < P.capacity && par >= 0 && par < nw && park >= 0 && park < GROW_THREADS, 108);
         // the descendants' new cost-to-come / arrival time were worked out on the way down (decide)
         for (int q = t; q < nwl; q += GROW_THREADS) {
           if (sm.u.d.wl_par[q] == WL_DEAD) continue;
@@ -1464,6 +1491,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
             for (int q = (t >> 5) - 1; q < nrew; q += GROW_THREADS / 32 - 1) {
               const int j = sm.u.d.rewn[q];
               const int old = sm.u.d.rpar[q];  // (nobody else of the prefix has rewired j: that would be a conflict)
+              KRRT_DCHECK(old >= 0 && old < T.cap && j > 0 && j < T.cap && __ldcg(&T.parent[j]) == old, 109);
               list_lock(W.lock, old);
               unlink_child_cg(T, old, j);
               list_unlock(W.lock, old);
