@@ -299,6 +299,8 @@ static int create_impl(krrt_ctx* ctx) {
   ctx->gi.min_n = 8192;
   if (const char* e = std::getenv("KRRT_GRID_INDEX")) ctx->gi.enabled = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_GRID_MIN_N")) ctx->gi.min_n = std::max(2, std::atoi(e));
+  ctx->gi.tail_max = 8192;  // measured 2048 .. unbounded on the 1 M-iteration tree: 392 / 383 / 381 / 384 / 392 / 393 ms (profiles/r2_grid_tail_s9.txt)
+  if (const char* e = std::getenv("KRRT_GRID_TAIL")) ctx->gi.tail_max = std::max(1024, std::atoi(e));
   CK(dev_alloc(ctx, &W.nn_d2, (size_t)1024));
   CK(dev_alloc(ctx, &W.nn_idx, (size_t)1024));
 #ifdef KRRT_DEBUG_CLK
@@ -316,6 +318,7 @@ static int create_impl(krrt_ctx* ctx) {
   {
     const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));
     CK(cudaFuncSetAttribute(k_grow, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+    CK(cudaFuncSetAttribute(k_grow_logged, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
     int per_sm = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow, GROW_THREADS, dyn));
     int coop = 0;
@@ -626,9 +629,11 @@ static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double
     if (small) {
       GrowCfg one = gcfg;
       one.wave_enabled = 0;  // a single CTA cannot run sub-rounds; in order is what a sequential planner does anyway
-      k_grow<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, one);
+      if (records) k_grow_logged<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, one);
+      else k_grow<<<1, GROW_THREADS, (size_t)dyn, st>>>(ctx->d_ctl, ctx->P, ctx->T, ctx->Bt, ctx->W, one);
     } else {
-      CK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(ctx->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
+      CK(cudaLaunchCooperativeKernel(records ? (const void*)k_grow_logged : (const void*)k_grow, dim3(ctx->grow_grid),
+                                     dim3(GROW_THREADS), args, (size_t)dyn, st));
     }
     // the goal lookup and the end-of-call event follow at once: ONE read-back per launch (when the kernel came back early
     // to have its conflict marks cleared, the lookup and the event are simply repeated after the next launch)

@@ -270,6 +270,9 @@ __device__ __forceinline__ void push_children(const TreeView& T, GrowShared& sm,
 // In-order commit of window samples [b0, b1) by ONE warp (the whole window while the tree is small; a single sample
 // when it needs the sequential path).  smem: obstacles + near list (commit_smem_bytes).
 // nn_idx >= 0: the nearest node of sample b0 over the whole tree (found by a grid-wide scan), used if its near set is empty.
+// kLog: the variant behind krrt_grow_logged, which also leaves a record per iteration (krrt_kernels.cuh: IterLog); the
+// planner proper is the kLog = false instantiation and carries none of it.
+template <bool kLog>
 __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt,
                                         unsigned char* smem, int b0, int b1, int nn_idx, double nn_d2, const IterLog& Lg) {
   const int lane = lane_id();
@@ -292,9 +295,9 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
   int full = 0, error = 0;
   State4 s = {0, 0, 0, 0};
   // logged call: what iteration `iter` left behind (the tree's costs are copied only when the tree changed)
-  const long long iter_begin = Lg.n_after ? __ldcg(&ctl->iter_begin) : 0;
+  const long long iter_begin = kLog ? __ldcg(&ctl->iter_begin) : 0;
   auto log_iter = [&](bool changed) {
-    if (!Lg.n_after) return;
+    if (!kLog) return;
     const long long i = iter - iter_begin - 1;
     if (i < 0 || i >= Lg.rows - 1) return;
     __syncwarp();
@@ -415,8 +418,9 @@ __device__ __forceinline__ void clear_window(const Batch& Bt) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,
-                                                            GrowCfg cfg) {
+template <bool kLog>
+__device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeView& T, const Batch& Bt, const Wave& W,
+                                          const GrowCfg& cfg) {
   extern __shared__ __align__(16) unsigned char dyn_raw[];
   GrowShared& sm = *reinterpret_cast<GrowShared*>(dyn_raw);
   unsigned char* dyn_smem = dyn_raw + grow_shared_bytes();  // in-order commit scratch (last CTA only)
@@ -515,7 +519,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
     if (cfg.gi.enabled && n0 >= cfg.gi.min_n) {
       gn = __ldcg(&ctl->grid_n);
       const double gcs = __ldcg(&ctl->grid_cs);
-      const bool stale = gn == 0 || n0 - gn > max(2048, n0 >> 4) || !(gcs * gcs >= 1.001 * rmax);
+      const bool stale = gn == 0 || n0 - gn > max(2048, min(n0 >> 4, cfg.gi.tail_max)) || !(gcs * gcs >= 1.001 * rmax);
       if (stale) {
         // geometry: cells at least 1.001 x the near radius wide (the margin dwarfs the rounding of the cell arithmetic,
         // so two points closer than the radius on an axis are never more than one cell apart on it)
@@ -732,7 +736,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
 
     if (!wave) {  // small tree: the whole window in order, one warp
       if (last && t < 32) {
-        seq_commit(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0, cfg.log);
+        seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0, cfg.log);
         __syncwarp();
         clear_window(Bt);
         if (t == 0) ctl->rounds_seq += 1;
@@ -1564,7 +1568,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           int ni = -1;
           double nd2 = 0.0;
           if (need_nn) nn_fold(ni, nd2);
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2, cfg.log);
+          seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2, cfg.log);
           if (lane == 0) {
             ctl->ema16 = (3 * ema_sub + 16) / 4;
             sm.fin[11] += 1;  // rounds_seq
@@ -1581,7 +1585,7 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
           int ni = -1;
           double nd2 = 0.0;
           if (tail_nn) nn_fold(ni, nd2);
-          seq_commit(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2, cfg.log);
+          seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2, cfg.log);
           if (t == 0) sm.fin[18] += 1;  // tail commits
         }
         __syncwarp();
@@ -1620,6 +1624,15 @@ __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl,
     ctl->dbg_cta[2][cta] += cta_app;
   }
 #endif
+}
+
+__global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,
+                                                            GrowCfg cfg) {
+  grow_body<false>(ctl, P, T, Bt, W, cfg);
+}
+// krrt_grow_logged: the same kernel with the in-order commit keeping per-iteration records (cfg.wave_enabled == 0)
+__global__ void __launch_bounds__(GROW_THREADS, 1) k_grow_logged(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W, GrowCfg cfg) {
+  grow_body<true>(ctl, P, T, Bt, W, cfg);
 }
 
 }  // namespace krrt

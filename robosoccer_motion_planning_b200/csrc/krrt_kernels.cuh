@@ -155,6 +155,7 @@ struct GridIndex {
   int* cell;      // [GRID_CELLS_MAX + 1] rebuild: counts; afterwards exclusive starts, cell[cells] = grid_n
   int enabled;    // KRRT_GRID_INDEX=0 in the environment: every window scans the whole tree
   int min_n;      // smallest tree that gets an index
+  int tail_max;   // most nodes left outside the index (scanned directly) before it is rebuilt: min(n / 16, tail_max)
 };
 
 // marks carry the round id, so they never need clearing: (round << 9) | (511 - sample), combined with atomicMax
