@@ -377,6 +377,19 @@ def test_large_tree_100k_properties_and_parity(gpu_required):
     assert_same_tree(G, O)
 
 
+@pytest.mark.slow
+def test_large_tree_1m_iterations_parity(gpu_required):
+    """BASELINE config 3 at its upper end: 1 M iterations (737 k nodes; grid index rebuilt ~60 times, windows of 1024 samples,
+    2 700 samples on the in-order path because they rewire nodes above > 1024 descendants).  Full bit parity: states, parents, costs,
+    times, all ten counters.  The oracle's kd-tree needs about half a minute for this plan."""
+    n_iter = 1_000_000
+    G, O = make_pair(gpu_required, dynamic=0, capacity=n_iter + 2)
+    G.grow(None, n_iter)
+    O.grow(None, n_iter)
+    assert G.size > 700_000
+    assert_same_tree(G, O)
+
+
 def test_edge_samples_and_tree_edges(gpu_required):
     """Connector slot: S samples per optimal edge, and tree.trajectories (robosoccer_visual.hpp:18)."""
     rng = np.random.default_rng(9)
