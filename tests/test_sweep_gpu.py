@@ -109,3 +109,23 @@ def test_mgpu_all_gpus_of_the_box(one_shot):
         assert S.max_over_ranks(3.5) == 3.5
         S.barrier()
         S.close()
+
+
+@pytest.mark.gpu
+def test_single_process_over_all_gpus_equals_one_gpu(gpu_required):
+    """krrt_mgpu_create: ONE process drives every GPU of the box (a host thread + context + stream per GPU, ncclCommInitAll),
+    the way a C++ caller without a launcher does; records byte-equal to the sweep on one GPU.  Skipped on a one-GPU box."""
+    n = capi.lib().krrt_device_count()
+    if n < 2:
+        pytest.skip("one GPU visible")
+    q = 4096 + 37
+    s, g, o = scenes.batch_queries(q, 9, seed=4)
+    S1 = sweep.Sweep.single_process(1, p_direct=0.1)
+    ref = S1.sweep(s, g, o, 1, 120)
+    S1.close()
+    Sn = sweep.Sweep.single_process(n, p_direct=0.1)
+    out = Sn.sweep(s, g, o, 1, 120)
+    info = Sn.info()
+    Sn.close()
+    assert info["world"] == n and info["nccl"] == 1
+    assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
