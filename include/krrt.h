@@ -64,8 +64,9 @@ enum { KRRT_GOAL_CONNECT = 0, KRRT_GOAL_TOLERANCE = 1 };
 typedef struct krrt_config {
   int32_t device;     /* CUDA device ordinal                                                 */
   int32_t precision;  /* KRRT_F64: binary64 throughout, as the reference (robotsubscriber.h:14), bit-exact with the CPU checker.
-                         KRRT_F32: binary32 states, steering and collision tests for krrt_plan_batch*, krrt_steer_cost and
-                         krrt_edge_collide (the same kernels compiled in float, bit-exact with the checker's float build; costs and
+                         KRRT_F32: binary32 states, steering and collision tests for krrt_plan_batch* and the stateless
+                         operators krrt_steer_cost, krrt_solve, krrt_solve_inputs, krrt_edge_samples, krrt_edge_collide
+                         (the same kernels compiled in float, bit-exact with the checker's float build; costs and
                          times within 1e-4 of binary64 on the same edge); arrays at this interface stay binary64.  The single-tree
                          planner (krrt_set_start / krrt_grow / tree read-outs) is binary64 only: KRRT_ERR_UNSUPPORTED on such a context */
   int32_t capacity;   /* max tree nodes                                                      */

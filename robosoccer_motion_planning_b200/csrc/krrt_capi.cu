@@ -108,8 +108,8 @@ struct krrt_ctx {
 // serves the batched planner and the stateless Cost / Environment operators, krrt_f32.cu)
 #define F64_ONLY()                                                                                                    \
   REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
-          "KRRT_F32 contexts serve krrt_plan_batch* / krrt_steer_cost / krrt_edge_collide; the single-tree planner and its " \
-          "read-outs are binary64 only")
+          "KRRT_F32 contexts serve krrt_plan_batch* and the stateless Cost / Connector / Environment operators; the "        \
+          "single-tree planner and its read-outs are binary64 only")
 
 // Everything a context owns on the device comes out of ONE allocation: the sub-rounds of k_grow are chains of
 // dependent gathers over ~25 arrays, and one arena keeps them inside a handful of 2 MB pages (TLB reach).

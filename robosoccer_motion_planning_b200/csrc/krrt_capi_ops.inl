@@ -145,7 +145,9 @@ static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const doub
   double* d_tau = (double*)ctx->d_scratch[3];
   int* d_rows = (int*)ctx->d_scratch[4];
   int* d_offs = d_rows + ne;
-  k_traj_count<<<(ne + 127) / 128, 128, 0, st>>>(d_states, ne, ctx->cfg.r, dt, d_tau, d_rows);
+  const bool f32 = ctx->cfg.precision == KRRT_F32;  // the Connector kernels of krrt_f32.cu (rows stay binary64 arrays)
+  if (f32) CK((cudaError_t)krrt_f32_api::traj_count(d_states, ne, ctx->cfg.r, dt, d_tau, d_rows, st));
+  else k_traj_count<<<(ne + 127) / 128, 128, 0, st>>>(d_states, ne, ctx->cfg.r, dt, d_tau, d_rows);
   k_traj_offsets<<<1, 32, 0, st>>>(d_rows, ne, d_offs);
   ctx->launches += 2;
   int total = 0;
@@ -157,7 +159,8 @@ static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const doub
   if ((rc = ensure_scratch(ctx, 5, sizeof(double) * 7 * (size_t)got)) != KRRT_OK) return rc;
   double* d_out = (double*)ctx->d_scratch[5];
   double* d_inp = inputs ? d_out + 5 * (size_t)got : nullptr;
-  k_traj_fill<<<ne, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, dt, d_out, got, d_inp);
+  if (f32) CK((cudaError_t)krrt_f32_api::traj_fill(d_states, d_t0, d_tau, d_offs, ne, dt, d_out, got, d_inp, st));
+  else k_traj_fill<<<ne, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, dt, d_out, got, d_inp);
   ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(rows, d_out, sizeof(double) * 5 * (size_t)got, cudaMemcpyDeviceToHost, st));
@@ -195,7 +198,6 @@ int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_row
 int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                int cap_rows, int* n_rows) {
   if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
-  F64_ONLY();
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   CK(cudaSetDevice(ctx->cfg.device));
   int rc;
@@ -212,7 +214,6 @@ int krrt_solve(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt,
 int krrt_solve_inputs(krrt_ctx* ctx, const double xi[4], const double xf[4], double dt, double t0, double* rows,
                       double* inputs, int cap_rows, int* n_rows) {
   if (!ctx || !xi || !xf || !n_rows) return KRRT_ERR_INVALID;
-  F64_ONLY();
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   REQUIRE(cap_rows == 0 || (rows && inputs), KRRT_ERR_INVALID, "null buffer");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -573,7 +574,6 @@ int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
 
 int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const double* t0, int n, int S, double* rows) {
   if (!ctx) return KRRT_ERR_INVALID;
-  F64_ONLY();
   REQUIRE(n >= 0 && S >= 1 && (n == 0 || (xi && xf && t0 && rows)), KRRT_ERR_INVALID, "null buffer / S < 1");
   if (n == 0) return KRRT_OK;
   CK(cudaSetDevice(ctx->cfg.device));
@@ -589,10 +589,14 @@ int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const d
   CK(cudaMemcpyAsync(ctx->d_scratch[1], xf, sb, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(ctx->d_scratch[3], t0, ob, cudaMemcpyHostToDevice, st));
   const long long total = (long long)n * S;
-  k_edge_samples<<<(unsigned)((total + 127) / 128), 128, 0, st>>>((const double*)ctx->d_scratch[0],
-                                                                  (const double*)ctx->d_scratch[1],
-                                                                  (const double*)ctx->d_scratch[3], n, S, ctx->cfg.r,
-                                                                  (double*)ctx->d_scratch[7]);
+  if (ctx->cfg.precision == KRRT_F32)
+    CK((cudaError_t)krrt_f32_api::edge_samples((const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1],
+                                               (const double*)ctx->d_scratch[3], n, S, ctx->cfg.r, (double*)ctx->d_scratch[7], st));
+  else
+    k_edge_samples<<<(unsigned)((total + 127) / 128), 128, 0, st>>>((const double*)ctx->d_scratch[0],
+                                                                    (const double*)ctx->d_scratch[1],
+                                                                    (const double*)ctx->d_scratch[3], n, S, ctx->cfg.r,
+                                                                    (double*)ctx->d_scratch[7]);
   ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(rows, ctx->d_scratch[7], rb, cudaMemcpyDeviceToHost, st));

@@ -66,6 +66,72 @@ __global__ void __launch_bounds__(128) k_edge_collide_batch(const krrt_io_real* 
   if (lane_id() == 0) hit[e] = h ? 1 : 0;
 }
 
+// ---- Connector slot in binary32 (the kernels of krrt_ops.cuh with the I/O arrays kept binary64)
+__device__ __forceinline__ int solve_last_row(double tau, double dt) {
+  int k = (int)floor(tau / dt);
+  if (k < 0) k = 0;
+  while ((double)k * dt < tau) ++k;
+  while (k > 0 && !((double)(k - 1) * dt < tau)) --k;
+  return k;
+}
+__device__ __forceinline__ State4 load_io_state(const krrt_io_real* p) {
+  const State4 s = {(double)p[0], (double)p[1], (double)p[2], (double)p[3]};
+  return s;
+}
+__global__ void k_traj_count(const krrt_io_real* __restrict__ states, int n_edges, double r, double dt,
+                             krrt_io_real* tau, int* rows) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  double t, c;
+  steer(load_io_state(states + 4 * (size_t)e), load_io_state(states + 4 * (size_t)(e + 1)), r, t, c);
+  tau[e] = t;
+  rows[e] = solve_last_row(t, dt) + 1;
+}
+__global__ void __launch_bounds__(128) k_traj_fill(const krrt_io_real* __restrict__ states, const krrt_io_real* __restrict__ t0s,
+                                                     const krrt_io_real* __restrict__ tau, const int* __restrict__ offs,
+                                                     double dt, krrt_io_real* out, int cap_rows,
+                                                     krrt_io_real* __restrict__ inputs) {
+  const int e = blockIdx.x;
+  const State4 x0 = load_io_state(states + 4 * (size_t)e), x1 = load_io_state(states + 4 * (size_t)(e + 1));
+  const double T = (double)tau[e], t0 = (double)t0s[e];
+  const int o = offs[e], cnt = offs[e + 1] - o;
+  const Edge ed = make_edge(x0, x1, T, t0);
+  for (int k = threadIdx.x; k < cnt; k += blockDim.x) {
+    if (o + k >= cap_rows) break;
+    const double t = (k == cnt - 1) ? T : (double)k * dt;
+    const double h = (T == KR(0.0)) ? KR(0.0) : t / T;
+    krrt_io_real* row = out + 5 * (size_t)(o + k);
+    row[0] = axis_pos(ed.kx, h);
+    row[1] = axis_pos(ed.ky, h);
+    row[2] = axis_vel(ed.kx, h, x0.vx, T);
+    row[3] = axis_vel(ed.ky, h, x0.vy, T);
+    row[4] = t0 + t;
+    if (inputs) {
+      inputs[2 * (size_t)(o + k) + 0] = axis_acc(ed.kx, h, T);
+      inputs[2 * (size_t)(o + k) + 1] = axis_acc(ed.ky, h, T);
+    }
+  }
+}
+__global__ void __launch_bounds__(128) k_edge_samples(const krrt_io_real* __restrict__ xi, const krrt_io_real* __restrict__ xf,
+                                                        const krrt_io_real* __restrict__ t0, int n, int S, double r,
+                                                        krrt_io_real* __restrict__ rows) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long long)n * S) return;
+  const int e = (int)(g / S), k = (int)(g - (long long)e * S);
+  const State4 x0 = load_io_state(xi + 4 * (size_t)e), x1 = load_io_state(xf + 4 * (size_t)e);
+  double tau, c;
+  steer(x0, x1, r, tau, c);
+  const double h = (S > 1) ? (double)k / (double)(S - 1) : KR(0.0);
+  const double t0e = (double)t0[e];
+  const Edge ed = make_edge(x0, x1, tau, t0e);
+  krrt_io_real* row = rows + 5 * g;
+  row[0] = axis_pos(ed.kx, h);
+  row[1] = axis_pos(ed.ky, h);
+  row[2] = axis_vel(ed.kx, h, x0.vx, tau);
+  row[3] = axis_vel(ed.ky, h, x0.vy, tau);
+  row[4] = t0e + tau * h;
+}
+
 static BatchJob make_job(const krrt_f32_api::BatchArgs& a) {
   BatchJob J;
   J.starts = a.starts; J.goals = a.goals; J.obstacles = a.obstacles;
@@ -138,6 +204,26 @@ int edge_collide_batch(const krrt_io_real* d_xi, const krrt_io_real* d_xf, const
   const double Rf = (double)R;
   krrt_f32::k_edge_collide_batch<<<(n * 32 + 127) / 128, 128, 0, st>>>(d_xi, d_xf, d_tau, d_t0, n, d_obs, m, dynamic, Rf * Rf, S,
                                                                       d_hit);
+  return (int)cudaGetLastError();
+}
+
+int traj_count(const krrt_io_real* d_states, int n_edges, krrt_io_real r, krrt_io_real dt, krrt_io_real* d_tau, int* d_rows,
+               cudaStream_t st) {
+  if (n_edges <= 0) return 0;
+  krrt_f32::k_traj_count<<<(n_edges + 127) / 128, 128, 0, st>>>(d_states, n_edges, (double)r, (double)dt, d_tau, d_rows);
+  return (int)cudaGetLastError();
+}
+int traj_fill(const krrt_io_real* d_states, const krrt_io_real* d_t0, const krrt_io_real* d_tau, const int* d_offs, int n_edges,
+              krrt_io_real dt, krrt_io_real* d_out, int cap_rows, krrt_io_real* d_inputs, cudaStream_t st) {
+  if (n_edges <= 0) return 0;
+  krrt_f32::k_traj_fill<<<n_edges, 128, 0, st>>>(d_states, d_t0, d_tau, d_offs, (double)dt, d_out, cap_rows, d_inputs);
+  return (int)cudaGetLastError();
+}
+int edge_samples(const krrt_io_real* d_xi, const krrt_io_real* d_xf, const krrt_io_real* d_t0, int n, int S, krrt_io_real r,
+                 krrt_io_real* d_rows, cudaStream_t st) {
+  if (n <= 0) return 0;
+  const long long threads = (long long)n * S;
+  krrt_f32::k_edge_samples<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(d_xi, d_xf, d_t0, n, S, (double)r, d_rows);
   return (int)cudaGetLastError();
 }
 

@@ -43,4 +43,11 @@ int edge_collide_batch(const double* d_xi, const double* d_xf, const double* d_t
                        const double* d_obs /* m x 4 */, int m, int dynamic, double R, int S, unsigned char* d_hit,
                        cudaStream_t st);
 
+// Connector slot (solver.solve(xi, xf, dt), the stored edge samples): rows of the edges states[e] -> states[e + 1]
+int traj_count(const double* d_states, int n_edges, double r, double dt, double* d_tau, int* d_rows, cudaStream_t st);
+int traj_fill(const double* d_states, const double* d_t0, const double* d_tau, const int* d_offs, int n_edges, double dt,
+              double* d_out, int cap_rows, double* d_inputs /* nullable */, cudaStream_t st);
+int edge_samples(const double* d_xi, const double* d_xf, const double* d_t0, int n, int S, double r, double* d_rows,
+                 cudaStream_t st);
+
 }  // namespace krrt_f32_api

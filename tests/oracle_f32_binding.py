@@ -43,6 +43,11 @@ def lib():
     L.ko_edge_collide.argtypes = [F, F, ctypes.c_float, ctypes.c_float, F, ctypes.c_int, ctypes.c_int, ctypes.c_float,
                                   ctypes.c_int]
     L.ko_edge_collide.restype = ctypes.c_int
+    L.ko_solve.argtypes = [F, F, ctypes.c_float, ctypes.c_float, ctypes.c_float, F, ctypes.c_int]
+    L.ko_solve.restype = ctypes.c_int
+    L.ko_solve_inputs.argtypes = [F, F, ctypes.c_float, ctypes.c_float, F, ctypes.c_int]
+    L.ko_solve_inputs.restype = ctypes.c_int
+    L.ko_edge_state.argtypes = [F, F, ctypes.c_float, ctypes.c_float, F]
     L.ko_rho2.argtypes = [ctypes.POINTER(KoConfigF), ctypes.c_int]
     L.ko_rho2.restype = ctypes.c_float
     L.ko_sample.argtypes = [ctypes.POINTER(KoConfigF), ctypes.c_uint64, F, F]
@@ -84,6 +89,28 @@ def edge_collide(x0, x1, tau, t0, obs, dynamic, R=1.35, S=10):
     obs = _f32(obs).reshape(-1, 4)
     return lib().ko_edge_collide(_f(x0), _f(x1), float(np.float32(tau)), float(np.float32(t0)), _f(obs), obs.shape[0],
                                  int(dynamic), float(R), int(S))
+
+
+def solve(x0, x1, r=0.5, dt=0.1, t0=0.0, cap=4096):
+    """rows (x, y, vx, vy, t0 + t) of solver.solve(x0, x1, dt) in binary32, widened"""
+    x0, x1 = _f32(x0), _f32(x1)
+    rows = np.empty((cap, 5), dtype=np.float32)
+    n = lib().ko_solve(_f(x0), _f(x1), float(r), float(np.float32(dt)), float(np.float32(t0)), _f(rows), cap)
+    return rows[:min(n, cap)].astype(np.float64)
+
+
+def solve_inputs(x0, x1, r=0.5, dt=0.1, cap=4096):
+    x0, x1 = _f32(x0), _f32(x1)
+    rows = np.empty((cap, 2), dtype=np.float32)
+    n = lib().ko_solve_inputs(_f(x0), _f(x1), float(r), float(np.float32(dt)), _f(rows), cap)
+    return rows[:min(n, cap)].astype(np.float64)
+
+
+def edge_state(x0, x1, tau, h):
+    x0, x1 = _f32(x0), _f32(x1)
+    out = np.empty(4, dtype=np.float32)
+    lib().ko_edge_state(_f(x0), _f(x1), float(np.float32(tau)), float(np.float32(h)), _f(out))
+    return out.astype(np.float64)
 
 
 def rho2(cfg, n):

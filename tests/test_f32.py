@@ -132,6 +132,32 @@ def test_f32_plan_batch_bit_exact(gpu_required, dynamic, p_direct, n_iter, goal_
 
 
 @pytest.mark.gpu
+def test_f32_connector_bit_exact(gpu_required):
+    """Connector slot on a KRRT_F32 context: solver.solve rows, control inputs and the S stored samples of an edge."""
+    from robosoccer_motion_planning_b200 import capi
+    G = capi.Planner(precision=capi.KRRT_F32)
+    x0, x1 = _pairs(300, seed=8)
+    t, c = of.steer(x0, x1)
+    for i in range(0, 300, 7):
+        rows = G.solve(x0[i], x1[i], dt=0.1, t0=1.5)
+        ref = of.solve(x0[i], x1[i], 0.5, 0.1, 1.5)
+        assert rows.shape == ref.shape and np.array_equal(rows, ref), i
+        rows2, inp = G.solve_inputs(x0[i], x1[i], dt=0.1)
+        assert np.array_equal(inp, of.solve_inputs(x0[i], x1[i], 0.5, 0.1)), i
+        assert np.array_equal(rows2, of.solve(x0[i], x1[i], 0.5, 0.1, 0.0))
+    S = 10
+    t0 = np.linspace(0.0, 3.0, 300)
+    E = G.edge_samples(x0, x1, t0, S)
+    for i in range(0, 300, 11):
+        for k in range(S):
+            h = np.float32(k) / np.float32(S - 1)
+            st = of.edge_state(x0[i], x1[i], t[i], h)
+            assert np.array_equal(E[i, k, :4], st), (i, k)
+            assert E[i, k, 4] == float(np.float32(t0[i]) + np.float32(t[i]) * h)
+    G.close()
+
+
+@pytest.mark.gpu
 def test_f32_near_overflow_takes_the_redo_pass(gpu_required):
     """A near radius that covers the whole field: every near set outgrows k_plan_batch2's 64 registers, the float k_plan_batch
     plans those queries, the result is the checker's."""
