@@ -71,7 +71,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -80,11 +80,20 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.monotonic(), ln.strip()))
+
+    def mark(self):
+        """start of the timed region (the sampler itself is started before the warm-up: nvidia-smi needs ~0.1 s to come up)"""
+        self.t0 = time.monotonic()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t1 = time.monotonic()
+        t0 = getattr(self, "t0", 0.0)
+        time.sleep(0.03)    # (a sample that was being taken when the region ended)
+        inside = [ln for (ts, ln) in self.lines if t0 <= ts <= t1 + 0.03]
+        self.lines = inside if inside else [ln for (_, ln) in self.lines[-3:]]
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -217,13 +226,14 @@ def run_ours(args, rank, world, local_rank):
         res = G.result(*r)
         return G.timer_end(), res
 
-    for _ in range(max(args.warmup, 3)):
-        plan_device_timed()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        plan_device_timed()
     # ---- value: device time of the grow call, K steps
     barrier()
+    sampler.mark()
     l0 = G.launch_count
     tot_ms = 0.0
     for _ in range(args.steps):
