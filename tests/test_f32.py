@@ -179,3 +179,31 @@ def test_f32_context_refuses_the_single_tree_planner(gpu_required):
         G.set_start(scenes.START)
     assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
     G.close()
+
+
+@pytest.mark.gpu
+def test_f32_edge_cases(gpu_required):
+    """Empty and ragged inputs on a KRRT_F32 context: no queries, one query, one iteration, no obstacles, a start that coincides
+    with the goal, the largest obstacle count — every record equals the float checker's."""
+    from robosoccer_motion_planning_b200 import capi, scenes
+    G = capi.Planner(precision=capi.KRRT_F32, p_direct=0.25)
+    cfg = of.default_config(p_direct=0.25)
+    starts, goals, obs = scenes.batch_queries(33, 9, seed=21)
+    assert len(G.plan_batch(starts[:0], goals[:0], obs[:0], 1, 50)) == 0
+    for q, m, n_iter, dyn in ((1, 9, 1, 1), (1, 9, 200, 0), (33, 0, 40, 1), (7, 3, 2, 1)):
+        o = obs[:q, :m]
+        out = G.plan_batch(starts[:q], goals[:q], o, dyn, n_iter, query_base=5)
+        ref = of.plan_batch(cfg, starts[:q], goals[:q], o, dyn, n_iter, query_base=5, nthreads=4)
+        assert np.array_equal(out.view(np.uint8), ref.view(np.uint8)), (q, m, n_iter, dyn)
+    same = goals[:4].copy()
+    out = G.plan_batch(same, same, obs[:4], 1, 30)              # start == goal: every sample that is the goal is a duplicate of the root
+    ref = of.plan_batch(cfg, same, same, obs[:4], 1, 30, nthreads=2)
+    assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
+    rng = np.random.default_rng(3)
+    big = np.concatenate([rng.uniform(-9, 9, (2, 64, 1)), rng.uniform(-6, 6, (2, 64, 1)), rng.uniform(-1, 1, (2, 64, 2))], axis=2)
+    big[:, :, :2] += 30.0                                       # 64 discs (KRRT_MAX_OBS) parked off the field
+    out = G.plan_batch(starts[:2], goals[:2], big, 1, 60)
+    ref = of.plan_batch(cfg, starts[:2], goals[:2], big, 1, 60, nthreads=2)
+    assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
+    assert G.steer_cost(starts[:0], goals[:0])[0].shape == (0,)
+    G.close()

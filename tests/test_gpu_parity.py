@@ -720,3 +720,29 @@ def test_grow_logged_equals_single_calls(gpu_required, dynamic, p_direct, goal_m
     with pytest.raises(capi.KrrtError) as e:
         G.grow_logged(scenes.GOAL, 257)
     assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
+
+
+def test_grow_logged_edge_cases(gpu_required):
+    """One iteration, no goal, a full tree, explicit rows only, and a logged call after plain ones: records against single calls."""
+    G, O = make_pair(gpu_required, dynamic=1, capacity=40, p_direct=0.3)
+    G.grow(scenes.GOAL, 7)
+    O.grow(scenes.GOAL, 7)
+    rec, solved, gi = G.grow_logged(None, 1)                    # no goal: never solved
+    so, go = O.grow(None, 1)
+    assert (bool(rec["solved"][0]), int(rec["goal_index"][0]), int(rec["n_nodes"][0])) == (so, go, O.size) == (False, -1, O.size)
+    rows = np.array([[1.0, 2.0, 0.5, -0.5], [1.0, 2.0, 0.5, -0.5], [-3.0, 1.0, 0.0, 0.25]])   # the second one is a duplicate
+    rec, solved, gi = G.grow_logged(scenes.GOAL, 3, rows)
+    for i in range(3):
+        so, go = O.grow(scenes.GOAL, 1, samples=rows[i:i + 1])
+        assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i])) == (so, go, O.size), i
+        assert np.array_equal(rec["sample"][i], rows[i])
+    assert not rec["inserted"][1]
+    rec, solved, gi = G.grow_logged(scenes.GOAL, 120)           # the tree fills up (capacity 40) on the way
+    n_prev = O.size
+    for i in range(120):
+        so, go = O.grow(scenes.GOAL, 1)
+        if O.size == 40 and n_prev == 40:
+            break                                                # from here on single calls find the tree full
+        assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i])) == (so, go, O.size), i
+        n_prev = O.size
+    assert G.size == 40 and G.grow_done()[1]
