@@ -139,7 +139,9 @@ class TreeInt2D {
   void configure(krrt_config& c) const {
     c.capacity = capacity;
     c.S = edge_samples;
+    c.precision = precision;
   }
+  int precision = KRRT_F64;  // KRRT_F32: the whole planner in binary32 (krrt.h); the reference is double throughout
   int capacity = 1 << 16;
   int edge_samples = 10;
 

@@ -64,11 +64,13 @@ enum { KRRT_GOAL_CONNECT = 0, KRRT_GOAL_TOLERANCE = 1 };
 typedef struct krrt_config {
   int32_t device;     /* CUDA device ordinal                                                 */
   int32_t precision;  /* KRRT_F64: binary64 throughout, as the reference (robotsubscriber.h:14), bit-exact with the CPU checker.
-                         KRRT_F32: binary32 states, steering and collision tests for krrt_plan_batch* and the stateless
-                         operators krrt_steer_cost, krrt_solve, krrt_solve_inputs, krrt_edge_samples, krrt_edge_collide
-                         (the same kernels compiled in float, bit-exact with the checker's float build; costs and
-                         times within 1e-4 of binary64 on the same edge); arrays at this interface stay binary64.  The single-tree
-                         planner (krrt_set_start / krrt_grow / tree read-outs) is binary64 only: KRRT_ERR_UNSUPPORTED on such a context */
+                         KRRT_F32: binary32 throughout (8-byte position / velocity pairs, fp32 steering, scans and collision
+                         tests): the planner proper (krrt_set_start, krrt_grow, krrt_tree_*, krrt_path, krrt_result_of, ...),
+                         krrt_plan_batch* and the stateless operators — the SAME kernels compiled in float, bit-exact with the
+                         checker's float build; costs and times within 1e-4 of binary64 on the same edge.  Arrays at this
+                         interface stay binary64 (rounded on the way in, widened on the way out).  krrt_grow_logged,
+                         krrt_trajectory, krrt_near, krrt_tree_edges and the diagnostics are binary64 only
+                         (KRRT_ERR_UNSUPPORTED on such a context) */
   int32_t capacity;   /* max tree nodes                                                      */
   int32_t S;          /* samples per edge for collision checks, both end points included     */
   double r;           /* input weight of J = int (1 + r|u|^2) dt; solver.set_weight(r) (…node.cpp:91-92) */

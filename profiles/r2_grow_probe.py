@@ -13,7 +13,12 @@ import numpy as np  # noqa: E402
 from robosoccer_motion_planning_b200 import capi, scenes  # noqa: E402
 
 
+F32 = "--f32" in sys.argv
+
+
 def run(label, iters, obs, dynamic, goal, p_direct, reps, parity):
+    if F32:
+        return run_f32(label, iters, obs, dynamic, goal, p_direct, reps, parity)
     G = capi.Planner(capacity=iters + 2, p_direct=p_direct)
     G.set_obstacles(obs, dynamic)
     G.set_start(scenes.START)
@@ -42,6 +47,31 @@ def run(label, iters, obs, dynamic, goal, p_direct, reps, parity):
         dt = time.perf_counter() - t0
         same = all(np.array_equal(a, b) for a, b in zip(G.tree(), O.tree())) and G.stats() == O.stats()
         print(f"   oracle {iters / dt / 1e3:.1f} k exp/s -> x{(iters / (best * 1e-3)) / (iters / dt):.1f}  parity {'bit-exact' if same else 'MISMATCH'}")
+    G.close()
+
+
+def run_f32(label, iters, obs, dynamic, goal, p_direct, reps, parity):
+    """the same plan on a KRRT_F32 context (wall clock around the call: the diagnostics are binary64 only)"""
+    G = capi.Planner(capacity=iters + 2, p_direct=p_direct, precision=capi.KRRT_F32)
+    G.set_obstacles(obs, dynamic)
+    G.set_start(scenes.START)
+    G.grow(goal, min(iters, 20000))
+    best = None
+    for _ in range(reps):
+        G.set_start(scenes.START)
+        t0 = time.perf_counter()
+        G.grow(goal, iters)
+        t = 1e3 * (time.perf_counter() - t0)
+        best = t if best is None else min(best, t)
+    print(f"{label} (f32): {best:9.3f} ms wall  {iters / best / 1e3:7.3f} M exp/s  nodes {G.size}")
+    if parity:
+        import oracle_f32_binding as of
+        O = of.OraclePlannerF32(capacity=iters + 2, p_direct=p_direct)
+        O.set_obstacles(obs, dynamic)
+        O.set_start(scenes.START)
+        O.grow(goal, iters)
+        same = all(np.array_equal(a, b) for a, b in zip(G.tree(), O.tree())) and G.stats() == O.stats()
+        print(f"   parity with the float checker: {'bit-exact' if same else 'MISMATCH'}")
     G.close()
 
 

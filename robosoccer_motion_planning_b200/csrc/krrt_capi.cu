@@ -84,6 +84,7 @@ struct krrt_ctx {
   unsigned char* d_iterlog = nullptr;  // krrt_grow_logged: one allocation behind the IterLog views + the records
   IterLog ilog = {nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
   IterRec* d_iterrec = nullptr;
+  krrt_f32_api::Tree* f32 = nullptr;  // KRRT_F32 contexts: the single-tree planner in binary32 (krrt_f32.cu)
   int64_t last_grow_iters = 0;  // iterations the last krrt_grow call really ran (fewer than asked when the tree filled up)
   int last_grow_full = 0;
 };
@@ -104,12 +105,22 @@ struct krrt_ctx {
       return (code);             \
     }                            \
   } while (0)
-// entry points of the single-tree planner and of the Tree / Connector read-outs: binary64 contexts only (a KRRT_F32 context
-// serves the batched planner and the stateless Cost / Environment operators, krrt_f32.cu)
+// entry points that exist in binary64 only: the logged call, the tree-walking read-outs beyond states / path, the diagnostics
+// (a KRRT_F32 context serves the planner proper, the batched planner and the stateless operators: krrt_f32.cu)
 #define F64_ONLY()                                                                                                    \
   REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
-          "KRRT_F32 contexts serve krrt_plan_batch* and the stateless Cost / Connector / Environment operators; the "        \
-          "single-tree planner and its read-outs are binary64 only")
+          "not available on a KRRT_F32 context (krrt_grow_logged, krrt_trajectory, krrt_near, krrt_tree_edges and the "      \
+          "diagnostics are binary64 only)")
+
+// KRRT_F32 contexts: the call goes to the binary32 planner; its error text becomes the context's
+#define F32_FORWARD(expr)                                                \
+  do {                                                                   \
+    if (ctx->cfg.precision == KRRT_F32) {                                \
+      const int rc_ = (expr);                                            \
+      if (rc_ != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32); \
+      return rc_;                                                        \
+    }                                                                    \
+  } while (0)
 
 // Everything a context owns on the device comes out of ONE allocation: the sub-rounds of k_grow are chains of
 // dependent gathers over ~25 arrays, and one arena keeps them inside a handful of 2 MB pages (TLB reach).
@@ -186,6 +197,7 @@ void krrt_destroy(krrt_ctx* ctx) {
     if (p) cudaFree(p);
   if (ctx->d_user) cudaFree(ctx->d_user);
   if (ctx->d_iterlog) cudaFree(ctx->d_iterlog);
+  if (ctx->f32) krrt_f32_api::tree_destroy(ctx->f32);
   if (ctx->d_flush) cudaFree(ctx->d_flush);
   if (ctx->d_rho2_batch) cudaFree(ctx->d_rho2_batch);
   if (ctx->d_redo) cudaFree(ctx->d_redo);
@@ -349,6 +361,14 @@ static int create_impl(krrt_ctx* ctx) {
   P.goal_mode = c.goal_mode;
   P.rho2 = ctx->d_rho2;
   P.obs = ctx->d_obs;
+  if (c.precision == KRRT_F32) {
+    char msg[512] = {0};
+    const int rc = krrt_f32_api::tree_create(&ctx->cfg, &ctx->f32, msg, sizeof(msg));
+    if (rc != KRRT_OK) {
+      ctx->err = msg;
+      return rc;
+    }
+  }
   return KRRT_OK;
 }
 
@@ -434,27 +454,17 @@ int krrt_set_obstacles(krrt_ctx* ctx, const double* o, int m, int dynamic) {
   }
   ctx->P.m = m;
   ctx->P.dynamic = dynamic ? 1 : 0;
+  if (ctx->f32) {  // (the binary64 copy above serves krrt_edge_collide's float kernel, which rounds on load)
+    const int rc = krrt_f32_api::tree_set_obstacles(ctx->f32, o, m, dynamic);
+    if (rc != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
+    return rc;
+  }
   return KRRT_OK;
-}
-
-__global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  T.pos[0] = make_double2(x0.x, x0.y);
-  T.vel[0] = make_double2(x0.vx, x0.vy);
-  T.parent[0] = -1;
-  T.ctc[0] = 0.0; T.tim[0] = 0.0; T.ecost[0] = 0.0; T.etime[0] = 0.0;
-  T.link[0] = make_int2(-1, -1); T.prev[0] = -1;
-  Ctl z;
-  memset(&z, 0, sizeof(z));
-  z.n = 1;
-  z.goal_index = -1;
-  z.round = ctl->round;  // the epoch of the conflict marks survives a restart (marks are never cleared)
-  *ctl = z;
 }
 
 int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   if (!ctx || !x0) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_set_start(ctx->f32, x0));
   CK(cudaSetDevice(ctx->cfg.device));
   State4 s = {x0[0], x0[1], x0[2], x0[3]};
   ctx->ctl_valid = false;
@@ -464,42 +474,6 @@ int krrt_set_start(krrt_ctx* ctx, const double x0[4]) {
   ctx->started = true;
   ctx->n_upper = 1;
   return KRRT_OK;
-}
-
-// before every k_grow launch: barrier counter, empty candidate lists, armed prefix slots; `first`: a new krrt_grow call
-__global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, GridBar* bar,
-                             int reset_round, TreeView T, IterLog Lg) {
-  for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {
-    Bt.count[b] = 0;
-    Bt.dup[b] = 0;
-  }
-  if (first && Lg.n_after) {  // logged call: row 0 of the snapshots is the tree before the call
-    const int n = ctl->n;
-    for (int j = threadIdx.x; j < n && j < Lg.stride; j += blockDim.x) {
-      Lg.snap_ctc[j] = T.ctc[j];
-      Lg.snap_tim[j] = T.tim[j];
-    }
-  }
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  bar[0].arrive = 0ull;
-  bar[1].arrive = 0ull;
-  ctl->wave_Fs[0] = 0x7fffffff;
-  ctl->wave_Fs[1] = 0x7fffffff;
-  if (reset_round) ctl->round = 0;
-  if (!first) return;
-  ctl->iter_begin = ctl->iter;
-  ctl->iter_target = ctl->iter + n_iter;
-  if (ctl->ema16 <= 0) ctl->ema16 = 16 * 16;
-  ctl->full = 0;
-  ctl->scan_pairs = 0.0;
-  ctl->scan_nodes = 0.0;
-  ctl->scan_visited = 0.0;
-  ctl->windows = 0;
-  for (int k = 0; k < 8; ++k) ctl->phase_clk[k] = 0;
-  for (int k = 0; k < 16; ++k) ctl->dbg_clk[k] = 0;
-  for (int k = 0; k < 3 * 160; ++k) (&ctl->dbg_cta[0][0])[k] = 0;
-  ctl->has_goal = has_goal;
-  ctl->goal[0] = g.x; ctl->goal[1] = g.y; ctl->goal[2] = g.vx; ctl->goal[3] = g.vy;
 }
 
 static int fetch_ctl(krrt_ctx* ctx, Ctl* h) {
@@ -542,6 +516,7 @@ int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double
 static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index,
                      krrt_iter_record* records) {
   if (!ctx) return KRRT_ERR_INVALID;
+  if (!records) F32_FORWARD(krrt_f32_api::tree_grow(ctx->f32, goal, n_iter, samples, solved, goal_index));
   F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
   REQUIRE(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
@@ -690,7 +665,7 @@ static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double
 // (include/rrtstar.hpp mirrors that from here); a tree that reached `capacity` stops early and says so
 int krrt_grow_done(krrt_ctx* ctx, int64_t* iterations_done, int* full) {
   if (!ctx) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_grow_done(ctx->f32, iterations_done, full, nullptr));
   if (iterations_done) *iterations_done = ctx->last_grow_iters;
   if (full) *full = ctx->last_grow_full;
   return KRRT_OK;
@@ -698,7 +673,7 @@ int krrt_grow_done(krrt_ctx* ctx, int64_t* iterations_done, int* full) {
 
 int krrt_tree_size(krrt_ctx* ctx, int* n) {
   if (!ctx || !n) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_info(ctx->f32, n, nullptr, nullptr, nullptr, nullptr));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -710,7 +685,7 @@ int krrt_tree_size(krrt_ctx* ctx, int* n) {
 
 int krrt_iteration(krrt_ctx* ctx, int64_t* iter) {
   if (!ctx || !iter) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_info(ctx->f32, nullptr, iter, nullptr, nullptr, nullptr));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -722,7 +697,7 @@ int krrt_iteration(krrt_ctx* ctx, int64_t* iter) {
 
 int krrt_last_sample(krrt_ctx* ctx, double out[4]) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_info(ctx->f32, nullptr, nullptr, out, nullptr, nullptr));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -734,7 +709,7 @@ int krrt_last_sample(krrt_ctx* ctx, double out[4]) {
 
 int krrt_get_stats(krrt_ctx* ctx, krrt_stats* out) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_info(ctx->f32, nullptr, nullptr, nullptr, out, nullptr));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;

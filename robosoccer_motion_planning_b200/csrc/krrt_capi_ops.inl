@@ -15,7 +15,13 @@ extern "C" {
 
 int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* cost, double* time) {
   if (!ctx) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  if (ctx->cfg.precision == KRRT_F32) {
+    int n32 = 0;
+    int rc32 = krrt_f32_api::tree_info(ctx->f32, &n32, nullptr, nullptr, nullptr, nullptr);
+    if (rc32 == KRRT_OK) rc32 = krrt_f32_api::tree_read(ctx->f32, 0, n32, states, parent, cost, time);
+    if (rc32 != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
+    return rc32;
+  }
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   int n = 0;
@@ -36,7 +42,7 @@ int krrt_tree_download(krrt_ctx* ctx, double* states, int32_t* parent, double* c
 
 int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t* parent, double* cost, double* time) {
   if (!ctx) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_read(ctx->f32, first, count, states, parent, cost, time));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   int n = 0, ng = 0;
@@ -58,7 +64,7 @@ int krrt_tree_read(krrt_ctx* ctx, int first, int count, double* states, int32_t*
 
 int krrt_goal_index(krrt_ctx* ctx, int* goal_index) {
   if (!ctx || !goal_index) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_info(ctx->f32, nullptr, nullptr, nullptr, nullptr, goal_index));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   CK(cudaSetDevice(ctx->cfg.device));
   Ctl h;
@@ -70,7 +76,7 @@ int krrt_goal_index(krrt_ctx* ctx, int* goal_index) {
 
 int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, int* len) {
   if (!ctx || !len) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_path(ctx->f32, idx, states, times, cap, len));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(cap >= 0, KRRT_ERR_INVALID, "cap < 0");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -103,7 +109,25 @@ int krrt_path(krrt_ctx* ctx, int idx, double* states, double* times, int cap, in
 
 int krrt_result_of(krrt_ctx* ctx, int solved, int goal_index, krrt_result* out) {
   if (!ctx || !out) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  if (ctx->cfg.precision == KRRT_F32) {  // the same record from the binary32 tree (path + the goal node's cost and arrival time)
+    std::memset(out, 0, sizeof(*out));
+    int n32 = 0;
+    int rc32 = krrt_tree_size(ctx, &n32);
+    if (rc32 != KRRT_OK) return rc32;
+    out->solved = solved;
+    out->goal_index = goal_index;
+    out->n_nodes = n32;
+    if (!solved) return KRRT_OK;
+    double st4[KRRT_MAX_WAYPOINTS][4], tm[KRRT_MAX_WAYPOINTS];
+    int len = 0;
+    if ((rc32 = krrt_path(ctx, goal_index, &st4[0][0], tm, KRRT_MAX_WAYPOINTS, &len)) != KRRT_OK) return rc32;
+    out->path_len = len;
+    for (int k = 0; k < std::min(len, (int)KRRT_MAX_WAYPOINTS); ++k) {
+      for (int d = 0; d < 4; ++d) out->waypoints[k][d] = st4[k][d];
+      out->waypoints[k][4] = tm[k];
+    }
+    return krrt_tree_read(ctx, goal_index, 1, nullptr, nullptr, &out->cost, &out->time);
+  }
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   std::memset(out, 0, sizeof(*out));
   int n = 0;
@@ -569,6 +593,11 @@ int krrt_set_params(krrt_ctx* ctx, const krrt_config* nc) {
   P.query_id = c.query_id;
   P.goal_tol2 = c.goal_tol * c.goal_tol;
   P.goal_mode = c.goal_mode;
+  if (ctx->f32) {
+    const int rc = krrt_f32_api::tree_set_params(ctx->f32, &ctx->cfg);
+    if (rc != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
+    return rc;
+  }
   return KRRT_OK;
 }
 

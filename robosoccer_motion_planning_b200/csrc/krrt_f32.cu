@@ -10,8 +10,14 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
+#include <string.h>
 
 #include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <string>
+#include <vector>
 
 #include "krrt_f32_api.h"
 #include "krrt_real.cuh"
@@ -26,6 +32,8 @@
 #define make_double2 make_float2
 #define make_double4 make_float4
 #include "krrt_batch2.cuh"
+#include "krrt_kernels.cuh"
+#include "krrt_grow.cuh"
 
 namespace krrt_f32 {
 
@@ -225,6 +233,487 @@ int edge_samples(const krrt_io_real* d_xi, const krrt_io_real* d_xf, const krrt_
   const long long threads = (long long)n * S;
   krrt_f32::k_edge_samples<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(d_xi, d_xf, d_t0, n, S, (double)r, d_rows);
   return (int)cudaGetLastError();
+}
+
+}  // namespace krrt_f32_api
+
+// =====================================================================================================================
+// The single-tree planner in binary32: k_set_start / k_begin_grow / k_grow / k_goal_connect of namespace krrt_f32 (the
+// binary64 sources compiled in float, as everything above) behind a small runtime of their own.  It mirrors what
+// krrt_capi.cu does for a binary64 context — one arena, one stream, one cooperative launch per grow call, one read-back of
+// the control block — without the diagnostics, the logged call and the single-CTA launch of tiny calls.
+// (`double` is `float` in this file: the C ABI's arrays are krrt_io_real.)
+namespace krrt_f32 {
+
+__global__ void k_path_extract(TreeView T, int n, int idx, double* states, double* times, int cap, int* out_len) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (idx < 0 || idx >= n) {
+    *out_len = 0;
+    return;
+  }
+  int len = 0;
+  for (int i = idx; i >= 0 && len < n; i = T.parent[i]) ++len;
+  int p = len - 1;
+  for (int i = idx; i >= 0 && p >= 0; i = T.parent[i], --p) {
+    if (p < cap) {
+      const double2 a = T.pos[i], v = T.vel[i];
+      states[4 * p + 0] = a.x; states[4 * p + 1] = a.y; states[4 * p + 2] = v.x; states[4 * p + 3] = v.y;
+      times[p] = T.tim[i];
+    }
+  }
+  *out_len = len;
+}
+
+}  // namespace krrt_f32
+
+namespace krrt_f32_api {
+
+using namespace krrt_f32;
+
+struct Tree {
+  krrt_config cfg;
+  cudaStream_t st = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int sms = 0, grow_grid = 0;
+  unsigned char* arena = nullptr;
+  size_t arena_bytes = 0, arena_used = 0;
+  TreeView T{};
+  double* d_rho2 = nullptr;
+  double4* d_obs = nullptr;
+  Ctl* d_ctl = nullptr;
+  Ctl* h_ctl = nullptr;
+  bool ctl_valid = false, started = false;
+  int n_upper = 0;
+  Batch Bt{};
+  Wave W{};
+  Params P{};
+  GridBar* d_bar = nullptr;
+  GridIndex gi{};
+  GoalScratch goal_scr{};
+  double* d_user = nullptr;
+  size_t user_cap = 0;
+  double* d_scr = nullptr;   // path read-out
+  int* d_len = nullptr;
+  size_t scr_cap = 0;
+  int wave_min_n = 32;
+  int64_t launches = 0, last_iters = 0;
+  int last_full = 0;
+  float last_ms = 0.f;
+  std::string err;
+};
+
+#define TCK(call)                                                             \
+  do {                                                                        \
+    cudaError_t e_ = (call);                                                  \
+    if (e_ != cudaSuccess) {                                                  \
+      t->err = std::string(#call) + ": " + cudaGetErrorString(e_);            \
+      return KRRT_ERR_CUDA;                                                   \
+    }                                                                         \
+  } while (0)
+#define TREQ(cond, code, msg) \
+  do {                        \
+    if (!(cond)) {            \
+      t->err = (msg);         \
+      return (code);          \
+    }                         \
+  } while (0)
+
+template <typename Tp>
+static cudaError_t talloc(Tree* t, Tp** p, size_t count) {
+  const size_t bytes = (sizeof(Tp) * std::max<size_t>(count, 1) + 255) / 256 * 256;
+  if (t->arena_used + bytes > t->arena_bytes) return cudaErrorMemoryAllocation;
+  *p = reinterpret_cast<Tp*>(t->arena + t->arena_used);
+  t->arena_used += bytes;
+  return cudaSuccess;
+}
+
+static void fill_params(Tree* t) {
+  const krrt_config& c = t->cfg;
+  Params& P = t->P;
+  const double R = (double)c.R, tol = (double)c.goal_tol;
+  P.r = (double)c.r;
+  P.R2 = R * R;
+  P.S = c.S;
+  P.capacity = c.capacity;
+  for (int k = 0; k < 4; ++k) {
+    P.sp.lo[k] = (double)c.lo[k];
+    P.sp.hi[k] = (double)c.hi[k];
+  }
+  P.sp.p_direct = (double)c.p_direct;
+  P.sp.seed = c.seed;
+  P.query_id = c.query_id;
+  P.goal_tol2 = tol * tol;
+  P.goal_mode = c.goal_mode;
+  P.rho2 = t->d_rho2;
+  P.obs = t->d_obs;
+}
+
+static int upload_radius_table(Tree* t) {
+  const size_t cap = (size_t)t->cfg.capacity;
+  std::vector<double> rho2(cap + 1);
+  for (size_t n = 0; n <= cap; ++n) rho2[n] = (double)near_radius2(t->cfg.gamma, t->cfg.rho_max, (int)n);
+  TCK(cudaMemcpyAsync(t->d_rho2, rho2.data(), sizeof(double) * (cap + 1), cudaMemcpyHostToDevice, t->st));
+  TCK(cudaStreamSynchronize(t->st));
+  return KRRT_OK;
+}
+
+static int create_body(Tree* t) {
+  const krrt_config& c = t->cfg;
+  TCK(cudaSetDevice(c.device));
+  cudaDeviceProp prop;
+  TCK(cudaGetDeviceProperties(&prop, c.device));
+  t->sms = prop.multiProcessorCount;
+  TCK(cudaStreamCreateWithFlags(&t->st, cudaStreamNonBlocking));
+  TCK(cudaEventCreate(&t->ev0));
+  TCK(cudaEventCreate(&t->ev1));
+  const size_t cap = (size_t)c.capacity;
+  const size_t bcn = (size_t)c.batch * c.near_cap;
+  const size_t need = cap * (8 * 2 + 4 * 4 + 8 + 4 * 3 + 4 * 3) + cap * (8 * 2 + 4 * 2) + cap * 8 + (GRID_CELLS_MAX + 1) * 4 +
+                      (cap + 1) * 4 + bcn * (4 + 4 * 5) + (size_t)1024 * GROW_QCAP * 4 + 2 * 1024 * 4 + 512 +
+                      (size_t)c.batch * (16 + 1 + 1 + 4 + 4 + sizeof(WaveRec)) + sizeof(Ctl) + GOAL_MAX_CTAS * 12 + (64 << 10);
+  TCK(cudaMalloc((void**)&t->arena, need));
+  t->arena_bytes = need;
+  TreeView& T = t->T;
+  TCK(talloc(t, &T.pos, cap + 1));
+  TCK(talloc(t, &T.vel, cap + 1));
+  TCK(talloc(t, &T.ctc, cap + 1));
+  TCK(talloc(t, &T.tim, cap + 1));
+  TCK(talloc(t, &T.ecost, cap + 1));
+  TCK(talloc(t, &T.etime, cap + 1));
+  TCK(talloc(t, &T.parent, cap + 1));
+  TCK(talloc(t, &T.link, cap));
+  TCK(talloc(t, &T.prev, cap));
+  TCK(talloc(t, &T.queue, cap));
+  T.cap = c.capacity;
+  TCK(talloc(t, &t->d_rho2, cap + 1));
+  TCK(talloc(t, &t->d_obs, (size_t)KRRT_MAX_OBS));
+  TCK(talloc(t, &t->d_ctl, (size_t)1));
+  TCK(talloc(t, &t->goal_scr.part_c, (size_t)GOAL_MAX_CTAS));
+  TCK(talloc(t, &t->goal_scr.part_i, (size_t)GOAL_MAX_CTAS));
+  TCK(talloc(t, &t->goal_scr.ticket, (size_t)1));
+  TCK(cudaMemsetAsync(t->goal_scr.ticket, 0, sizeof(unsigned), t->st));
+  TCK(cudaMemsetAsync(t->d_ctl, 0, sizeof(Ctl), t->st));
+  TCK(cudaMemsetAsync(t->d_obs, 0, sizeof(double4) * KRRT_MAX_OBS, t->st));
+  Batch& B = t->Bt;
+  B.B = c.batch;
+  B.near_cap = c.near_cap;
+  TCK(talloc(t, &B.samples, (size_t)B.B));
+  TCK(talloc(t, &B.reject, (size_t)B.B));
+  TCK(talloc(t, &B.dup, (size_t)B.B));
+  TCK(talloc(t, &B.map, (size_t)B.B));
+  TCK(talloc(t, &B.count, (size_t)B.B));
+  TCK(talloc(t, &B.ref, bcn));
+  TCK(talloc(t, &B.d2, bcn));
+  TCK(talloc(t, &B.tf, bcn));
+  TCK(talloc(t, &B.cf, bcn));
+  TCK(talloc(t, &B.tb, bcn));
+  TCK(talloc(t, &B.cb, bcn));
+  Wave& W = t->W;
+  TCK(talloc(t, &W.rec, (size_t)B.B));
+  TCK(talloc(t, &W.wmin, cap));
+  TCK(talloc(t, &W.amin, cap));
+  TCK(talloc(t, &W.rmin, cap));
+  TCK(talloc(t, &W.lock, cap));
+  TCK(talloc(t, &W.wlc, (size_t)1024 * GROW_QCAP));
+  TCK(talloc(t, &W.done, (size_t)1024));
+  TCK(talloc(t, &W.ok, (size_t)1024));
+  TCK(talloc(t, &W.nn_d2, (size_t)1024));
+  TCK(talloc(t, &W.nn_idx, (size_t)1024));
+  W.dbg_log = nullptr;
+  TCK(cudaMemsetAsync(W.done, 0, sizeof(unsigned) * 1024, t->st));
+  TCK(cudaMemsetAsync(W.ok, 0, sizeof(unsigned) * 1024, t->st));
+  TCK(cudaMemsetAsync(W.wmin, 0, sizeof(unsigned) * cap, t->st));
+  TCK(cudaMemsetAsync(W.amin, 0, sizeof(unsigned) * cap, t->st));
+  TCK(cudaMemsetAsync(W.rmin, 0, sizeof(unsigned long long) * cap, t->st));
+  TCK(cudaMemsetAsync(W.lock, 0, sizeof(int) * cap, t->st));
+  TCK(talloc(t, &t->gi.pos, cap));
+  TCK(talloc(t, &t->gi.vel, cap));
+  TCK(talloc(t, &t->gi.id, cap));
+  TCK(talloc(t, &t->gi.off, cap));
+  TCK(talloc(t, &t->gi.cell, (size_t)GRID_CELLS_MAX + 1));
+  t->gi.enabled = 1;
+  t->gi.min_n = 8192;
+  t->gi.tail_max = 8192;
+  if (const char* e = std::getenv("KRRT_GRID_INDEX")) t->gi.enabled = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) t->wave_min_n = std::max(2, std::atoi(e));
+  TCK(talloc(t, &t->d_bar, (size_t)2));
+  {
+    const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));
+    TCK(cudaFuncSetAttribute(k_grow, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+    int per_sm = 0, coop = 0;
+    TCK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow, GROW_THREADS, dyn));
+    TCK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c.device));
+    TREQ(per_sm >= 1 && coop, KRRT_ERR_UNSUPPORTED, "k_grow (binary32) does not fit one CTA per SM / no cooperative launch");
+    t->grow_grid = t->sms;
+  }
+  TCK(cudaHostAlloc((void**)&t->h_ctl, sizeof(Ctl), cudaHostAllocDefault));
+  int rc = upload_radius_table(t);
+  if (rc != KRRT_OK) return rc;
+  fill_params(t);
+  t->P.m = 0;
+  t->P.dynamic = 0;
+  return KRRT_OK;
+}
+
+int tree_create(const krrt_config* cfg, Tree** out, char* err, size_t err_len) {
+  Tree* t = new Tree();
+  t->cfg = *cfg;
+  const int rc = create_body(t);
+  if (rc != KRRT_OK) {
+    if (err && err_len) snprintf(err, err_len, "%s", t->err.c_str());
+    tree_destroy(t);
+    return rc;
+  }
+  *out = t;
+  return KRRT_OK;
+}
+
+void tree_destroy(Tree* t) {
+  if (!t) return;
+  cudaSetDevice(t->cfg.device);
+  if (t->st) cudaStreamSynchronize(t->st);
+  if (t->arena) cudaFree(t->arena);
+  if (t->d_user) cudaFree(t->d_user);
+  if (t->d_scr) cudaFree(t->d_scr);
+  if (t->h_ctl) cudaFreeHost(t->h_ctl);
+  if (t->ev0) cudaEventDestroy(t->ev0);
+  if (t->ev1) cudaEventDestroy(t->ev1);
+  if (t->st) cudaStreamDestroy(t->st);
+  delete t;
+}
+
+const char* tree_error(const Tree* t) { return t ? t->err.c_str() : ""; }
+int64_t tree_launches(const Tree* t) { return t ? t->launches : 0; }
+
+int tree_set_params(Tree* t, const krrt_config* cfg) {
+  TCK(cudaSetDevice(t->cfg.device));
+  const bool radius = cfg->gamma != t->cfg.gamma || cfg->rho_max != t->cfg.rho_max;
+  t->cfg = *cfg;
+  if (radius) {
+    const int rc = upload_radius_table(t);
+    if (rc != KRRT_OK) return rc;
+  }
+  const int m = t->P.m, dyn = t->P.dynamic;
+  fill_params(t);
+  t->P.m = m;
+  t->P.dynamic = dyn;
+  return KRRT_OK;
+}
+
+int tree_set_obstacles(Tree* t, const krrt_io_real* o, int m, int dynamic) {
+  TCK(cudaSetDevice(t->cfg.device));
+  if (m > 0) {
+    std::vector<double> h(4 * (size_t)m);
+    for (size_t k = 0; k < h.size(); ++k) h[k] = (double)o[k];
+    TCK(cudaMemcpyAsync(t->d_obs, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice, t->st));
+    TCK(cudaStreamSynchronize(t->st));
+  }
+  t->P.m = m;
+  t->P.dynamic = dynamic ? 1 : 0;
+  return KRRT_OK;
+}
+
+int tree_set_start(Tree* t, const krrt_io_real x0[4]) {
+  TCK(cudaSetDevice(t->cfg.device));
+  const State4 s = {(double)x0[0], (double)x0[1], (double)x0[2], (double)x0[3]};
+  k_set_start<<<1, 32, 0, t->st>>>(t->d_ctl, t->T, s);
+  t->launches++;
+  TCK(cudaGetLastError());
+  t->started = true;
+  t->ctl_valid = false;
+  t->n_upper = 1;
+  return KRRT_OK;
+}
+
+static int fetch(Tree* t, Ctl* h) {
+  if (!t->ctl_valid) {
+    TCK(cudaMemcpyAsync(t->h_ctl, t->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, t->st));
+    TCK(cudaStreamSynchronize(t->st));
+    t->ctl_valid = true;
+  }
+  *h = *t->h_ctl;
+  t->n_upper = h->n;
+  return KRRT_OK;
+}
+
+int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real* samples, int* solved, int* goal_index) {
+  TREQ(t->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
+  TREQ(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
+  TCK(cudaSetDevice(t->cfg.device));
+  cudaStream_t st = t->st;
+  if (samples && n_iter > 0) {  // explicit rows, rounded to binary32 (a NaN row stays one: "draw it yourself")
+    const size_t cnt = 4 * (size_t)n_iter, need = sizeof(double) * cnt;
+    if (t->user_cap < need) {
+      if (t->d_user) TCK(cudaFree(t->d_user));
+      t->d_user = nullptr;
+      t->user_cap = 0;
+      TCK(cudaMalloc((void**)&t->d_user, need));
+      t->user_cap = need;
+    }
+    std::vector<double> h(cnt);
+    for (size_t k = 0; k < cnt; ++k) h[k] = (double)samples[k];
+    TCK(cudaMemcpyAsync(t->d_user, h.data(), need, cudaMemcpyHostToDevice, st));
+    TCK(cudaStreamSynchronize(st));
+  }
+  State4 g = {0, 0, 0, 0};
+  if (goal) g = State4{(double)goal[0], (double)goal[1], (double)goal[2], (double)goal[3]};
+  TCK(cudaEventRecord(t->ev0, st));
+  GrowCfg gcfg;
+  gcfg.wave_enabled = 1;
+  if (const char* e = std::getenv("KRRT_WAVE")) gcfg.wave_enabled = std::atoi(e) != 0;
+  gcfg.wave_min_n = t->wave_min_n;
+  gcfg.user_samples = samples ? t->d_user : nullptr;
+  gcfg.bar = t->d_bar;
+  gcfg.gi = t->gi;
+  gcfg.log = IterLog{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  {
+    auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
+    gcfg.pend_resolve = envi("KRRT_PEND", 1);
+    gcfg.raw_forward = envi("KRRT_RAW_FORWARD", 1);
+    gcfg.tail_seq = envi("KRRT_TAIL_SEQ", 1);
+    gcfg.intra_fix = envi("KRRT_INTRA_FIX", 1);
+    gcfg.prop_forward = envi("KRRT_PROP_FORWARD", 1);
+    gcfg.join_test = envi("KRRT_JOIN_TEST", 1);
+    gcfg.flow = envi("KRRT_FLOW", 0);
+    gcfg.nb_mul = envi("KRRT_NB_MUL", 2); gcfg.nb_add = envi("KRRT_NB_ADD", 8); gcfg.nb_min = envi("KRRT_NB_MIN", 16);
+    gcfg.pn_mul = envi("KRRT_PN_MUL", 3); gcfg.pn_add = envi("KRRT_PN_ADD", 16); gcfg.pn_min = envi("KRRT_PN_MIN", 48);
+  }
+  const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(t->Bt.near_cap));
+  Ctl h;
+  for (int launch = 0;; ++launch) {
+    const bool wrap = launch > 0;
+    if (wrap) {
+      const size_t cap = (size_t)t->cfg.capacity;
+      TCK(cudaMemsetAsync(t->W.wmin, 0, sizeof(unsigned) * cap, st));
+      TCK(cudaMemsetAsync(t->W.amin, 0, sizeof(unsigned) * cap, st));
+      TCK(cudaMemsetAsync(t->W.rmin, 0, sizeof(unsigned long long) * cap, st));
+      TCK(cudaMemsetAsync(t->W.done, 0, sizeof(unsigned) * 1024, st));
+      TCK(cudaMemsetAsync(t->W.ok, 0, sizeof(unsigned) * 1024, st));
+    }
+    t->ctl_valid = false;
+    k_begin_grow<<<1, 32, 0, st>>>(t->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, t->Bt, t->d_bar, wrap ? 1 : 0, t->T, gcfg.log);
+    void* args[] = {(void*)&t->d_ctl, (void*)&t->P, (void*)&t->T, (void*)&t->Bt, (void*)&t->W, (void*)&gcfg};
+    TCK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(t->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
+    if (t->P.goal_mode == KRRT_GOAL_TOLERANCE) {
+      k_find_goal<<<1, 1024, 0, st>>>(t->d_ctl, t->T, t->P.goal_tol2);
+    } else {
+      const long long n_max = (long long)t->n_upper + n_iter;
+      const int ctas = (int)std::max<long long>(1, std::min<long long>(std::min(GOAL_MAX_CTAS, 4 * t->sms),
+                                                                       (n_max + GOAL_THREADS - 1) / GOAL_THREADS));
+      k_goal_connect<<<ctas, GOAL_THREADS, 0, st>>>(t->d_ctl, t->P, t->T, t->goal_scr);
+    }
+    TCK(cudaEventRecord(t->ev1, st));
+    t->launches += 3;
+    TCK(cudaGetLastError());
+    const int rc = fetch(t, &h);
+    if (rc != KRRT_OK) return rc;
+    if (h.full || h.error || h.iter >= h.iter_target) break;
+    TREQ(h.round >= (1u << 23) - 2, KRRT_ERR_CUDA, "k_grow (binary32) returned before its target");
+  }
+  TCK(cudaEventElapsedTime(&t->last_ms, t->ev0, t->ev1));
+  t->last_iters = h.iter - h.iter_begin;
+  t->last_full = h.full ? 1 : 0;
+  if (h.error) {
+    t->err = h.error == KRRT_ERR_NEAR_OVERFLOW ? "near set exceeded near_cap; raise krrt_config.near_cap" : "device error";
+    return h.error;
+  }
+  if (solved) *solved = h.goal_index >= 0;
+  if (goal_index) *goal_index = h.goal_index;
+  return KRRT_OK;
+}
+
+int tree_grow_done(Tree* t, int64_t* iterations_done, int* full, krrt_io_real* ms) {
+  if (iterations_done) *iterations_done = t->last_iters;
+  if (full) *full = t->last_full;
+  if (ms) *ms = t->last_ms;
+  return KRRT_OK;
+}
+
+int tree_info(Tree* t, int* n, int64_t* iteration, krrt_io_real last_sample[4], krrt_stats* stats, int* goal_index) {
+  TREQ(t->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  TCK(cudaSetDevice(t->cfg.device));
+  Ctl h;
+  const int rc = fetch(t, &h);
+  if (rc != KRRT_OK) return rc;
+  if (n) *n = h.n;
+  if (iteration) *iteration = h.iter;
+  if (last_sample)
+    for (int k = 0; k < 4; ++k) last_sample[k] = h.last_sample[k];
+  if (stats) {
+    static_assert(sizeof(krrt_stats) == 10 * sizeof(long long), "stats layout");
+    memcpy(stats, h.stats, sizeof(krrt_stats));
+  }
+  if (goal_index) *goal_index = h.goal_index;
+  return KRRT_OK;
+}
+
+int tree_read(Tree* t, int first, int count, krrt_io_real* states, int32_t* parent, krrt_io_real* cost, krrt_io_real* time) {
+  TREQ(t->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  TCK(cudaSetDevice(t->cfg.device));
+  Ctl h;
+  int rc = fetch(t, &h);
+  if (rc != KRRT_OK) return rc;
+  const int ng = h.n + (h.goal_index == h.n ? 1 : 0);
+  TREQ(first >= 0 && count >= 0 && first + count <= ng, KRRT_ERR_INVALID, "node range out of bounds");
+  if (count == 0) return KRRT_OK;
+  const size_t c = (size_t)count;
+  std::vector<double2> p(states ? c : 0), v(states ? c : 0);
+  std::vector<double> cc(cost ? c : 0), tt(time ? c : 0);
+  if (states) {
+    TCK(cudaMemcpyAsync(p.data(), t->T.pos + first, sizeof(double2) * c, cudaMemcpyDeviceToHost, t->st));
+    TCK(cudaMemcpyAsync(v.data(), t->T.vel + first, sizeof(double2) * c, cudaMemcpyDeviceToHost, t->st));
+  }
+  if (parent) TCK(cudaMemcpyAsync(parent, t->T.parent + first, sizeof(int) * c, cudaMemcpyDeviceToHost, t->st));
+  if (cost) TCK(cudaMemcpyAsync(cc.data(), t->T.ctc + first, sizeof(double) * c, cudaMemcpyDeviceToHost, t->st));
+  if (time) TCK(cudaMemcpyAsync(tt.data(), t->T.tim + first, sizeof(double) * c, cudaMemcpyDeviceToHost, t->st));
+  TCK(cudaStreamSynchronize(t->st));
+  for (size_t i = 0; i < c; ++i) {
+    if (states) {
+      states[4 * i + 0] = p[i].x; states[4 * i + 1] = p[i].y; states[4 * i + 2] = v[i].x; states[4 * i + 3] = v[i].y;
+    }
+    if (cost) cost[i] = cc[i];
+    if (time) time[i] = tt[i];
+  }
+  return KRRT_OK;
+}
+
+int tree_path(Tree* t, int idx, krrt_io_real* states, krrt_io_real* times, int cap, int* len) {
+  TREQ(t->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  TCK(cudaSetDevice(t->cfg.device));
+  Ctl h;
+  int rc = fetch(t, &h);
+  if (rc != KRRT_OK) return rc;
+  const int ng = h.n + (h.goal_index == h.n ? 1 : 0);
+  TREQ(idx >= 0 && idx < ng, KRRT_ERR_INVALID, "node index out of range");
+  const size_t need = sizeof(double) * 5 * (size_t)ng + 16;
+  if (t->scr_cap < need) {
+    if (t->d_scr) TCK(cudaFree(t->d_scr));
+    t->d_scr = nullptr;
+    t->scr_cap = 0;
+    TCK(cudaMalloc((void**)&t->d_scr, need));
+    t->scr_cap = need;
+  }
+  double* d_states = t->d_scr;
+  double* d_times = d_states + 4 * (size_t)ng;
+  int* d_len = reinterpret_cast<int*>(d_times + ng);
+  k_path_extract<<<1, 32, 0, t->st>>>(t->T, ng, idx, d_states, d_times, ng, d_len);
+  t->launches++;
+  int hl = 0;
+  TCK(cudaMemcpyAsync(&hl, d_len, sizeof(int), cudaMemcpyDeviceToHost, t->st));
+  TCK(cudaStreamSynchronize(t->st));
+  *len = hl;
+  const int got = std::min(hl, cap);
+  if (got > 0 && (states || times)) {
+    std::vector<double> hs(4 * (size_t)got), ht((size_t)got);
+    TCK(cudaMemcpyAsync(hs.data(), d_states, sizeof(double) * 4 * got, cudaMemcpyDeviceToHost, t->st));
+    TCK(cudaMemcpyAsync(ht.data(), d_times, sizeof(double) * got, cudaMemcpyDeviceToHost, t->st));
+    TCK(cudaStreamSynchronize(t->st));
+    if (states)
+      for (size_t k = 0; k < hs.size(); ++k) states[k] = hs[k];
+    if (times)
+      for (size_t k = 0; k < ht.size(); ++k) times[k] = ht[k];
+  }
+  return KRRT_OK;
 }
 
 }  // namespace krrt_f32_api

@@ -6,6 +6,8 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include "../../include/krrt.h"
+
 namespace krrt_f32_api {
 
 struct BatchArgs {              // one batched plan: device buffers of the C ABI (binary64) + the context's scratch
@@ -49,5 +51,22 @@ int traj_fill(const double* d_states, const double* d_t0, const double* d_tau, c
               double* d_out, int cap_rows, double* d_inputs /* nullable */, cudaStream_t st);
 int edge_samples(const double* d_xi, const double* d_xf, const double* d_t0, int n, int S, double r, double* d_rows,
                  cudaStream_t st);
+
+// ---- the single-tree planner in binary32 (k_grow and the kernels around it compiled in float; krrt_f32.cu).  One Tree per
+// KRRT_F32 context: krrt_capi.cu forwards the planner's entry points here.  Arrays are the C ABI's (binary64): rounded on the
+// way in, widened on the way out.  Every function returns a KRRT_* status; tree_error() gives the text.
+struct Tree;
+int tree_create(const krrt_config* cfg, Tree** out, char* err, size_t err_len);
+void tree_destroy(Tree* t);
+const char* tree_error(const Tree* t);
+int tree_set_params(Tree* t, const krrt_config* cfg);
+int tree_set_obstacles(Tree* t, const double* xyvxvy, int m, int dynamic);
+int tree_set_start(Tree* t, const double x0[4]);
+int tree_grow(Tree* t, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index);
+int tree_grow_done(Tree* t, int64_t* iterations_done, int* full, double* ms);
+int tree_info(Tree* t, int* n, int64_t* iteration, double last_sample[4], krrt_stats* stats, int* goal_index);
+int tree_read(Tree* t, int first, int count, double* states, int32_t* parent, double* cost, double* time);
+int tree_path(Tree* t, int idx, double* states, double* times, int cap, int* len);
+int64_t tree_launches(const Tree* t);
 
 }  // namespace krrt_f32_api

@@ -122,6 +122,15 @@ struct GrowCfg {
   int pn_mul, pn_add, pn_min;  // CTAs that take part in a window's sub-rounds, likewise
 };
 
+// a non-negative cost / squared distance as an unsigned key that orders the same way (arg-min by REDUX on its two words)
+#ifdef KRRT_F32_BUILD
+__device__ __forceinline__ unsigned long long real_key(double x) { return (unsigned long long)__float_as_uint(x) << 32; }
+__device__ __forceinline__ double key_real(unsigned long long k) { return __uint_as_float((unsigned)(k >> 32)); }
+#else
+__device__ __forceinline__ unsigned long long real_key(double x) { return (unsigned long long)__double_as_longlong(x); }
+__device__ __forceinline__ double key_real(unsigned long long k) { return __longlong_as_double((long long)k); }
+#endif
+
 __device__ __forceinline__ void grid_barrier(GridBar* bar, BarState& st, int n, bool relaxed) {
   __syncthreads();
   st.arrived += (unsigned long long)n;
@@ -349,7 +358,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
         const double d = __ldcg(&Bt.d2[o]);
         node = (ref & IN_BATCH) ? __ldcg(&Bt.map[ref & ~IN_BATCH]) : ref;
         valid = node >= 0 && d <= rho2n;
-        dup |= valid && d == 0.0;
+        dup |= valid && d == KR(0.0);
       }
       unsigned mk = __ballot_sync(FULL, valid);
       if (valid) {
@@ -371,7 +380,7 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
       int ni = nn_idx;
       double nd2 = nn_d2;
       if (ni < 0 || b != b0) warp_nearest(T, n, s, ni, nd2);
-      if (nd2 == 0.0) {
+      if (nd2 == KR(0.0)) {
         st.fail_dup++;
         log_iter(false);
         continue;
@@ -382,8 +391,8 @@ __device__ __noinline__ void seq_commit(Ctl* ctl, const Params& P, const TreeVie
         N.idx[0] = ni;
         N.cf[0] = c;
         N.tf[0] = t;
-        N.cb[0] = 0.0;
-        N.tb[0] = 0.0;
+        N.cb[0] = KR(0.0);
+        N.tb[0] = KR(0.0);
       }
       K = 1;
     }
@@ -432,7 +441,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
   const int S = P.S;
   BarState bs_all = {0ull}, bs_sub = {0ull};
   if (t < 20) sm.fin[t] = 0;
-  if (t < GROW_SMAX) sm.hS[t] = (S > 1) ? (double)t / (double)(S - 1) : 0.0;
+  if (t < GROW_SMAX) sm.hS[t] = (S > 1) ? (double)t / (double)(S - 1) : KR(0.0);
   long long clk_mark = clock64();
   auto phase_done = [&](int which) {  // phase clocks of the last CTA (it waits at every barrier like the others)
     if (last && t == 0) {
@@ -465,7 +474,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
     const int user_off = (int)(iter0 - __ldcg(&ctl->iter_begin));
 
     // squared radius that covers every tree size this window can see
-    double rmax = 0.0;
+    double rmax = KR(0.0);
     for (int k = t; k <= Wn; k += GROW_THREADS) rmax = fmax(rmax, P.rho2[min(n0 + k, P.capacity)]);
     for (int off = 16; off > 0; off >>= 1) rmax = fmax(rmax, __shfl_xor_sync(FULL, rmax, off));
     if ((t & 31) == 0) sm.red_c[t >> 5] = rmax;
@@ -515,23 +524,23 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
     // cells are too small for this window's radius (krrt_set_params raised it).  Every CTA takes the same decision from the
     // same values (read after the previous window's end barrier; written below by one thread, a barrier before any use).
     int gn = 0, gw = 1, gh = 1;
-    double g_lox = 0.0, g_loy = 0.0, g_invx = 0.0, g_invy = 0.0;
+    double g_lox = KR(0.0), g_loy = KR(0.0), g_invx = KR(0.0), g_invy = KR(0.0);
     if (cfg.gi.enabled && n0 >= cfg.gi.min_n) {
       gn = __ldcg(&ctl->grid_n);
       const double gcs = __ldcg(&ctl->grid_cs);
-      const bool stale = gn == 0 || n0 - gn > max(2048, min(n0 >> 4, cfg.gi.tail_max)) || !(gcs * gcs >= 1.001 * rmax);
+      const bool stale = gn == 0 || n0 - gn > max(2048, min(n0 >> 4, cfg.gi.tail_max)) || !(gcs * gcs >= KR(1.001) * rmax);
       if (stale) {
         // geometry: cells at least 1.001 x the near radius wide (the margin dwarfs the rounding of the cell arithmetic,
         // so two points closer than the radius on an axis are never more than one cell apart on it)
         const double rad = sqrt(rmax);
-        const double cs = 1.001 * rad;
+        const double cs = KR(1.001) * rad;
         g_lox = P.sp.lo[0];
         g_loy = P.sp.lo[1];
         const double wx = P.sp.hi[0] - P.sp.lo[0], wy = P.sp.hi[1] - P.sp.lo[1];
-        gw = (cs > 0.0 && wx > 0.0) ? (int)fmin((double)GRID_W_MAX, fmax(1.0, floor(wx / cs))) : 1;
-        gh = (cs > 0.0 && wy > 0.0) ? (int)fmin((double)GRID_H_MAX, fmax(1.0, floor(wy / cs))) : 1;
-        g_invx = wx > 0.0 ? (double)gw / wx : 0.0;
-        g_invy = wy > 0.0 ? (double)gh / wy : 0.0;
+        gw = (cs > KR(0.0) && wx > KR(0.0)) ? (int)fmin((double)GRID_W_MAX, fmax(KR(1.0), floor(wx / cs))) : 1;
+        gh = (cs > KR(0.0) && wy > KR(0.0)) ? (int)fmin((double)GRID_H_MAX, fmax(KR(1.0), floor(wy / cs))) : 1;
+        g_invx = wx > KR(0.0) ? (double)gw / wx : KR(0.0);
+        g_invy = wy > KR(0.0) ? (double)gh / wy : KR(0.0);
         const int ncell = gw * gh;
         for (int c = cta * GROW_THREADS + t; c <= ncell; c += G * GROW_THREADS) cfg.gi.cell[c] = 0;
         grid_barrier(cfg.bar, bs_all, G, false);
@@ -624,7 +633,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
               const State4 a = {p[u].x, p[u].y, v[u].x, v[u].y};
               const double d = dist2(a, sb);
               if (d <= rmax) {
-                if (d == 0.0) Bt.dup[b] = 1;
+                if (d == KR(0.0)) Bt.dup[b] = 1;
                 append_candidate(Bt, b, __ldcg(&cfg.gi.id[slot]), d);
               }
             }
@@ -650,7 +659,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
           for (int b = c0; b < c1; ++b) {
             const double d = dist2(a, sm.u.ss[b]);
             if (d <= rmax) {
-              if (d == 0.0) Bt.dup[b] = 1;
+              if (d == KR(0.0)) Bt.dup[b] = 1;
               append_candidate(Bt, b, i, d);
             }
           }
@@ -736,7 +745,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
 
     if (!wave) {  // small tree: the whole window in order, one warp
       if (last && t < 32) {
-        seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, 0.0, cfg.log);
+        seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, 0, Wn, -1, KR(0.0), cfg.log);
         __syncwarp();
         clear_window(Bt);
         if (t == 0) ctl->rounds_seq += 1;
@@ -772,12 +781,12 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
       // what this CTA carries from decide to validate and apply
       int outcome = OUT_REJECT, n_b = 0, K = 0, par = -1, park = -1, nrew = 0, nwl = 0, nlvl = 0, nprop = 0;
       long long collide_calls = 0;
-      double ctc_new = 0.0, tim_new = 0.0, rho2n = 0.0;
+      double ctc_new = KR(0.0), tim_new = KR(0.0), rho2n = KR(0.0);
       int my_node = -1, my_q = -1;
       bool my_tried = false, my_cand = false;  // this thread's near node was tried as parent / is a rewire candidate
       int pend_e = -1;  // this thread's candidate is an earlier sample of the SAME sub-round (window index): see validate
-      double pend_tf = 0.0, pend_tb = 0.0;  // tau* of that candidate -> sample / sample -> candidate
-      double my_d = 0.0, my_cf = 0.0, my_cb = 0.0, my_ctc = 0.0;
+      double pend_tf = KR(0.0), pend_tb = KR(0.0);  // tau* of that candidate -> sample / sample -> candidate
+      double my_d = KR(0.0), my_cf = KR(0.0), my_cb = KR(0.0), my_ctc = KR(0.0);
       bool my_near = false;
       State4 s = {0, 0, 0, 0};
 
@@ -792,7 +801,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
         // but allocated data; they are ignored below.
         const bool spec = t < min(cap, 64);  // these slots are warm in L2 (every window uses them); the rest wait for the count
         int ref = 0;
-        double my_tf = 0.0, my_tb = 0.0;
+        double my_tf = KR(0.0), my_tb = KR(0.0);
         if (spec) {
           ref = __ldcg(&Bt.ref[base + t]);
           my_d = __ldcg(&Bt.d2[base + t]);
@@ -855,7 +864,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
           }
         }
         State4 x = {0, 0, 0, 0};
-        double my_tim = 0.0;
+        double my_tim = KR(0.0);
         int my_head = -1, my_par0 = -1;
         KRRT_DCHECK(my_node < T.cap, 107);  // a candidate reference that leaves the tree
         if (my_node >= 0) {
@@ -877,7 +886,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
         my_near = my_node >= 0 && my_d <= rho2n;
         {
           const unsigned nearb = __ballot_sync(FULL, my_near);
-          const unsigned dupb = __ballot_sync(FULL, my_near && my_d == 0.0);
+          const unsigned dupb = __ballot_sync(FULL, my_near && my_d == KR(0.0));
           const unsigned pendb = __ballot_sync(FULL, pend);
           if ((t & 31) == 0) {
             if (nearb) atomicAdd(&sm.K, __popc(nearb));
@@ -914,7 +923,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
             const int k = w / S, p = w - k * S;
             if (!(sm.u.d.flag[k] & 1)) continue;
             const Edge ed = make_edge(sm.u.d.st[k], s, sm.u.d.tf[k], sm.u.d.tim[k]);
-            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : KR(0.0));
             if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) atomicOr(&sm.u.d.flag[k], 2);
           }
           __syncthreads();
@@ -924,7 +933,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
         // order like unsigned integers: three REDUX per warp, then every thread folds the per-warp winners
         {
           const bool ok = my_near && !(sm.u.d.flag[t] & 2);
-          const unsigned long long kb = ok ? (unsigned long long)__double_as_longlong(my_ctc + my_cf) : ~0ull;
+          const unsigned long long kb = ok ? real_key(my_ctc + my_cf) : ~0ull;
           const unsigned hi = (unsigned)(kb >> 32), lo = (unsigned)kb;
           const unsigned mh = __reduce_min_sync(FULL, hi);
           const unsigned ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
@@ -1006,7 +1015,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
             const int q = w / S, p = w - q * S;
             const int k = sm.u.d.cand[q];
             const Edge ed = make_edge(s, sm.u.d.st[k], sm.u.d.tb[k], tim_new);
-            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+            const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : KR(0.0));
             if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) atomicOr(&sm.u.d.flag[k], 8);
           }
           __syncthreads();
@@ -1141,7 +1150,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
         r.pad = 0;
 #endif
         r.outcome = outcome; r.n_b = n_b; r.par = par; r.park = park; r.K = K; r.nrew = nrew; r.nwl = nprop;
-        r.ctc_new = ctc_new; r.tim_new = tim_new; r.collide_calls = collide_calls; r.d2_in_max = 0.0; r.d2_out_min = 0.0;
+        r.ctc_new = ctc_new; r.tim_new = tim_new; r.collide_calls = collide_calls; r.d2_in_max = KR(0.0); r.d2_out_min = KR(0.0);
         W.rec[b] = r;
       }
 #ifdef KRRT_DEBUG_CLK
@@ -1198,7 +1207,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
             mr = __ldcg(&W.rmin[my_node]);
           }
           int oe = -1;
-          double ce_p = 0.0, te_p = 0.0;
+          double ce_p = KR(0.0), te_p = KR(0.0);
           State4 xe_p = {0, 0, 0, 0};
           if (pend_e >= 0) {
             oe = __ldcg(&W.rec[pend_e].outcome);
@@ -1261,7 +1270,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
             const double ce = ce_p;
             if (oe == OUT_INSERT && my_d <= rt) {
               joins = true;
-              conf |= my_d == 0.0;
+              conf |= my_d == KR(0.0);
               // the newcomer would be tried as parent (all candidates are if none is free) / is a rewire candidate
               need_a = outcome == OUT_NOFREE || ce + my_cf < ctc_new;
               need_b = outcome == OUT_INSERT && ctc_new + my_cb < ce;
@@ -1269,7 +1278,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
                 conf |= need_a || need_b;
                 need_a = need_b = false;
               }
-              WHY(outcome == OUT_NOFREE, 4); WHY(my_d == 0.0, 8); WHY(ce + my_cf < ctc_new, 16); WHY(ctc_new + my_cb < ce, 32);
+              WHY(outcome == OUT_NOFREE, 4); WHY(my_d == KR(0.0), 8); WHY(ce + my_cf < ctc_new, 16); WHY(ctc_new + my_cb < ce, 32);
             }
           }
           const int n_join = __syncthreads_count(joins);
@@ -1295,7 +1304,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
             for (int w = t; w < ne * S; w += GROW_THREADS) {
               const int q = w / S, p = w - q * S;
               const Edge ed = make_edge(sm.xe_a[q], sm.xe_b[q], sm.xe_tau[q], sm.xe_t0[q]);
-              const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : 0.0);
+              const double h = S <= GROW_SMAX ? sm.hS[p] : ((S > 1) ? (double)p / (double)(S - 1) : KR(0.0));
               if (edge_point_hits_any(ed, h, sm.obs, P.m, P.dynamic, P.R2)) sm.xe_hit[q] = 1;
             }
             __syncthreads();
@@ -1414,13 +1423,13 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
           }
         }
         // (distance, index) arg-min: distances are >= 0, their bit patterns order like unsigned integers
-        const unsigned long long kb = (unsigned long long)__double_as_longlong(bd);
+        const unsigned long long kb = real_key(bd);
         const unsigned hi = (unsigned)(kb >> 32), lo = (unsigned)kb;
         const unsigned mh = __reduce_min_sync(FULL, hi);
         const unsigned ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
         const unsigned mn = __reduce_min_sync(FULL, (hi == mh && lo == ml) ? (unsigned)bi : 0xffffffffu);
         if ((t & 31) == 0) {
-          sm.red_c[t >> 5] = __longlong_as_double((long long)(((unsigned long long)mh << 32) | ml));
+          sm.red_c[t >> 5] = key_real(((unsigned long long)mh << 32) | ml);
           sm.red_i[t >> 5] = (int)mn;
         }
         __syncthreads();
@@ -1566,7 +1575,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
           }
         } else {  // the first sample needs the sequential path (empty near set, huge subtree, ...): commit it alone
           int ni = -1;
-          double nd2 = 0.0;
+          double nd2 = KR(0.0);
           if (need_nn) nn_fold(ni, nd2);
           seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, F0, F0 + 1, ni, nd2, cfg.log);
           if (lane == 0) {
@@ -1583,7 +1592,7 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
       if (last && t < 32) {
         if (tail_seq) {
           int ni = -1;
-          double nd2 = 0.0;
+          double nd2 = KR(0.0);
           if (tail_nn) nn_fold(ni, nd2);
           seq_commit<kLog>(ctl, P, T, Bt, dyn_smem, F0 + F, F0 + F + 1, ni, nd2, cfg.log);
           if (t == 0) sm.fin[18] += 1;  // tail commits
@@ -1624,6 +1633,58 @@ __device__ __forceinline__ void grow_body(Ctl* ctl, const Params& P, const TreeV
     ctl->dbg_cta[2][cta] += cta_app;
   }
 #endif
+}
+
+// a fresh tree holding only the root (rrt.setStart, robosoccer_motion_planning_node.cpp:135)
+__global__ void k_set_start(Ctl* ctl, TreeView T, State4 x0) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  T.pos[0] = make_double2(x0.x, x0.y);
+  T.vel[0] = make_double2(x0.vx, x0.vy);
+  T.parent[0] = -1;
+  T.ctc[0] = KR(0.0); T.tim[0] = KR(0.0); T.ecost[0] = KR(0.0); T.etime[0] = KR(0.0);
+  T.link[0] = make_int2(-1, -1); T.prev[0] = -1;
+  Ctl z;
+  memset(&z, 0, sizeof(z));
+  z.n = 1;
+  z.goal_index = -1;
+  z.round = ctl->round;  // the epoch of the conflict marks survives a restart (marks are never cleared)
+  *ctl = z;
+}
+
+// before every k_grow launch: barrier counter, empty candidate lists, armed prefix slots; `first`: a new krrt_grow call
+__global__ void k_begin_grow(Ctl* ctl, int first, int has_goal, State4 g, int n_iter, Batch Bt, GridBar* bar,
+                             int reset_round, TreeView T, IterLog Lg) {
+  for (int b = threadIdx.x; b < Bt.B; b += blockDim.x) {
+    Bt.count[b] = 0;
+    Bt.dup[b] = 0;
+  }
+  if (first && Lg.n_after) {  // logged call: row 0 of the snapshots is the tree before the call
+    const int n = ctl->n;
+    for (int j = threadIdx.x; j < n && j < Lg.stride; j += blockDim.x) {
+      Lg.snap_ctc[j] = T.ctc[j];
+      Lg.snap_tim[j] = T.tim[j];
+    }
+  }
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  bar[0].arrive = 0ull;
+  bar[1].arrive = 0ull;
+  ctl->wave_Fs[0] = 0x7fffffff;
+  ctl->wave_Fs[1] = 0x7fffffff;
+  if (reset_round) ctl->round = 0;
+  if (!first) return;
+  ctl->iter_begin = ctl->iter;
+  ctl->iter_target = ctl->iter + n_iter;
+  if (ctl->ema16 <= 0) ctl->ema16 = 16 * 16;
+  ctl->full = 0;
+  ctl->scan_pairs = KR(0.0);
+  ctl->scan_nodes = KR(0.0);
+  ctl->scan_visited = KR(0.0);
+  ctl->windows = 0;
+  for (int k = 0; k < 8; ++k) ctl->phase_clk[k] = 0;
+  for (int k = 0; k < 16; ++k) ctl->dbg_clk[k] = 0;
+  for (int k = 0; k < 3 * 160; ++k) (&ctl->dbg_cta[0][0])[k] = 0;
+  ctl->has_goal = has_goal;
+  ctl->goal[0] = g.x; ctl->goal[1] = g.y; ctl->goal[2] = g.vx; ctl->goal[3] = g.vy;
 }
 
 __global__ void __launch_bounds__(GROW_THREADS, KRRT_GROW_MINB) k_grow(Ctl* ctl, Params P, TreeView T, Batch Bt, Wave W,

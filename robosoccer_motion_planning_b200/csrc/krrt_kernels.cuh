@@ -240,8 +240,8 @@ __global__ void __launch_bounds__(GOAL_THREADS) k_goal_connect(Ctl* ctl, Params 
   int bi = -1, aux = 0;
   for (int i = 1 + blockIdx.x * GOAL_THREADS + t; i < n; i += gridDim.x * GOAL_THREADS) {
     const State4 x = load_state(T, i);
-    const bool same = dist2(x, g) == 0.0;
-    double tg = 0.0, cg = 0.0;
+    const bool same = dist2(x, g) == KR(0.0);
+    double tg = KR(0.0), cg = KR(0.0);
     if (!same) steer(x, g, P.r, tg, cg);
     const double cand = T.ctc[i] + cg;
     if (bi >= 0 && cand >= bc) continue;  // (i only grows: an equal offer loses on the index)
@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(GOAL_THREADS) k_goal_connect(Ctl* ctl, Params 
     if (!same && P.m > 0) {
       const Edge e = make_edge(x, g, tg, T.tim[i]);
       for (int k = 0; k < P.S && !hit; ++k) {
-        const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : 0.0;
+        const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : KR(0.0);
         hit = edge_point_hits_any(e, h, s_obs, P.m, P.dynamic, P.R2);
       }
     }
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(GOAL_THREADS) k_goal_connect(Ctl* ctl, Params 
     int gi = -1;
     if (bi >= 0) {
       const State4 x = load_state(T, bi);
-      if (dist2(x, g) == 0.0) {
+      if (dist2(x, g) == KR(0.0)) {
         gi = bi;
       } else {
         double tg, cg;
@@ -346,8 +346,8 @@ __global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Param
   } else if (has_goal) {
     for (int i = 1 + t; i < n; i += GLOG_THREADS) {
       const State4 x = load_state(T, i);
-      const bool same = dist2(x, g) == 0.0;
-      double tg = 0.0, cg = 0.0;
+      const bool same = dist2(x, g) == KR(0.0);
+      double tg = KR(0.0), cg = KR(0.0);
       if (!same) steer(x, g, P.r, tg, cg);
       const double cand = ctc[i] + cg;
       if (bi >= 0 && cand >= bc) continue;
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Param
       if (!same && P.m > 0) {
         const Edge e = make_edge(x, g, tg, tim[i]);
         for (int k = 0; k < P.S && !hit; ++k) {
-          const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : 0.0;
+          const double h = (P.S > 1) ? (double)k / (double)(P.S - 1) : KR(0.0);
           hit = edge_point_hits_any(e, h, s_obs, P.m, P.dynamic, P.R2);
         }
       }
@@ -381,9 +381,9 @@ __global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Param
       r.inserted = n > n_prev ? 1 : 0;
       r.solved = bi >= 0 ? 1 : 0;
       r.goal_index = -1;
-      r.goal_cost = 0.0;
+      r.goal_cost = KR(0.0);
       if (bi >= 0) {
-        const bool node_is_goal = P.goal_mode == GOAL_MODE_TOLERANCE || dist2(load_state(T, bi), g) == 0.0;
+        const bool node_is_goal = P.goal_mode == GOAL_MODE_TOLERANCE || dist2(load_state(T, bi), g) == KR(0.0);
         r.goal_index = node_is_goal ? bi : n;
         r.goal_cost = bc;
       }

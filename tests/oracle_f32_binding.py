@@ -53,6 +53,26 @@ def lib():
     L.ko_sample.argtypes = [ctypes.POINTER(KoConfigF), ctypes.c_uint64, F, F]
     L.ko_plan_batch.argtypes = [ctypes.POINTER(KoConfigF), F, F, F, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                 ctypes.c_uint32, ctypes.c_void_p, ctypes.c_int]
+    L.ko_create.argtypes = [ctypes.POINTER(KoConfigF)]
+    L.ko_create.restype = ctypes.c_void_p
+    L.ko_destroy.argtypes = [ctypes.c_void_p]
+    L.ko_set_obstacles.argtypes = [ctypes.c_void_p, F, ctypes.c_int, ctypes.c_int]
+    L.ko_set_start.argtypes = [ctypes.c_void_p, F]
+    L.ko_grow.argtypes = [ctypes.c_void_p, F, ctypes.c_int, F, I]
+    L.ko_grow.restype = ctypes.c_int
+    L.ko_size.argtypes = [ctypes.c_void_p]
+    L.ko_size.restype = ctypes.c_int
+    L.ko_iteration.argtypes = [ctypes.c_void_p]
+    L.ko_iteration.restype = ctypes.c_int64
+    for name, rt in (("ko_states", F), ("ko_ctc", F), ("ko_times", F), ("ko_last_sample", F), ("ko_parents", I)):
+        getattr(L, name).argtypes = [ctypes.c_void_p]
+        getattr(L, name).restype = rt
+    L.ko_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(ob.KoStats)]
+    L.ko_path.argtypes = [ctypes.c_void_p, ctypes.c_int, F, F, ctypes.c_int]
+    L.ko_path.restype = ctypes.c_int
+    L.ko_fill_result.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    L.ko_check_invariants.argtypes = [ctypes.c_void_p, ctypes.c_float]
+    L.ko_check_invariants.restype = ctypes.c_int
     _lib = L
     return L
 
@@ -141,3 +161,88 @@ def plan_batch(cfg, starts, goals, obstacles, dynamic, n_iter, query_base=0, nth
     for k in ("cost", "time", "waypoints"):
         out[k] = raw[k].astype(np.float64)
     return out
+
+
+def _widen_result(raw):
+    out = np.zeros(raw.shape, dtype=ob.RESULT_DTYPE)
+    for k in ("solved", "goal_index", "n_nodes", "path_len"):
+        out[k] = raw[k]
+    for k in ("cost", "time", "waypoints"):
+        out[k] = raw[k].astype(np.float64)
+    return out
+
+
+class OraclePlannerF32:
+    """The single-tree planner of the float build (mirror of oracle_binding.OraclePlanner; arrays in and out are binary64)."""
+
+    def __init__(self, **kw):
+        self.cfg = default_config(**kw)
+        self.h = lib().ko_create(ctypes.byref(self.cfg))
+
+    def close(self):
+        if self.h:
+            lib().ko_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def set_obstacles(self, obs, dynamic):
+        obs = _f32(obs).reshape(-1, 4)
+        lib().ko_set_obstacles(self.h, _f(obs), obs.shape[0], int(dynamic))
+
+    def set_start(self, x0):
+        x0 = _f32(x0)
+        lib().ko_set_start(self.h, _f(x0))
+
+    def grow(self, goal, n_iter, samples=None):
+        g = None
+        if goal is not None:
+            self._goal = _f32(goal)
+            g = _f(self._goal)
+        s = None
+        if samples is not None:
+            samples = _f32(samples).reshape(n_iter, 4)
+            s = _f(samples)
+        gi = ctypes.c_int32(-1)
+        solved = lib().ko_grow(self.h, g, int(n_iter), s, ctypes.byref(gi))
+        return bool(solved), gi.value
+
+    @property
+    def size(self):
+        return lib().ko_size(self.h)
+
+    @property
+    def iteration(self):
+        return lib().ko_iteration(self.h)
+
+    def tree(self):
+        n = self.size
+        L = lib()
+        states = np.ctypeslib.as_array(L.ko_states(self.h), shape=(n, 4)).astype(np.float64)
+        parent = np.ctypeslib.as_array(L.ko_parents(self.h), shape=(n,)).copy()
+        ctc = np.ctypeslib.as_array(L.ko_ctc(self.h), shape=(n,)).astype(np.float64)
+        tim = np.ctypeslib.as_array(L.ko_times(self.h), shape=(n,)).astype(np.float64)
+        return states, parent, ctc, tim
+
+    def last_sample(self):
+        return np.ctypeslib.as_array(lib().ko_last_sample(self.h), shape=(4,)).astype(np.float64)
+
+    def stats(self):
+        s = ob.KoStats()
+        lib().ko_get_stats(self.h, ctypes.byref(s))
+        return {n: getattr(s, n) for n, _ in ob.KoStats._fields_}
+
+    def path(self, idx, cap=4096):
+        st = np.empty((cap, 4), dtype=np.float32)
+        tm = np.empty(cap, dtype=np.float32)
+        n = lib().ko_path(self.h, int(idx), _f(st), _f(tm), cap)
+        return st[:n].astype(np.float64), tm[:n].astype(np.float64)
+
+    def result(self, solved, goal_index):
+        r = np.zeros(1, dtype=RESULT_F32)
+        lib().ko_fill_result(self.h, int(solved), int(goal_index), r.ctypes.data)
+        return _widen_result(r)[0]
+
+    def check_invariants(self, tol=1e-4):
+        return lib().ko_check_invariants(self.h, float(tol))

@@ -171,13 +171,107 @@ def test_f32_near_overflow_takes_the_redo_pass(gpu_required):
     G.close()
 
 
+def _pair32(dynamic, capacity, **kw):
+    from robosoccer_motion_planning_b200 import capi, scenes
+    G = capi.Planner(precision=capi.KRRT_F32, capacity=capacity, **kw)
+    O = of.OraclePlannerF32(capacity=capacity, **kw)
+    obs = scenes.dynamic_obstacles() if dynamic else scenes.static_obstacles()
+    for P in (G, O):
+        P.set_obstacles(obs, dynamic)
+        P.set_start(scenes.START)
+    return G, O
+
+
+def _same_tree32(G, O):
+    assert G.size == O.size and G.iteration == O.iteration
+    for a, b, what in zip(G.tree(), O.tree(), ("states", "parents", "cost-to-come", "times")):
+        assert np.array_equal(a, b), what
+    assert G.stats() == O.stats()
+
+
 @pytest.mark.gpu
-def test_f32_context_refuses_the_single_tree_planner(gpu_required):
+@pytest.mark.parametrize("dynamic,p_direct,n_iter,goal_mode", [(1, 0.1, 8000, 0), (0, 0.0, 6000, 0), (1, 0.2, 3000, 1)])
+def test_f32_single_tree_bit_exact(gpu_required, dynamic, p_direct, n_iter, goal_mode):
+    """The planner proper on a KRRT_F32 context: k_grow compiled in float against the float checker — states, parents, costs,
+    times, all ten counters, goal node, path and result record; in several calls, with explicit rows, after a restart."""
+    from robosoccer_motion_planning_b200 import scenes
+    kw = dict(p_direct=p_direct, goal_mode=goal_mode, goal_tol=1.0 if goal_mode else 0.0)
+    G, O = _pair32(dynamic, n_iter + 2, **kw)
+    rows = np.full((100, 4), np.nan)
+    rows[7] = scenes.GOAL
+    rows[50] = [1.0 + 1e-9, -2.0, 0.5, 0.25]            # (not float-representable: rounded on the way in, on both sides)
+    rg = G.grow(scenes.GOAL, 100, rows)
+    ro = O.grow(scenes.GOAL, 100, rows)
+    assert rg == ro
+    assert np.array_equal(G.last_sample(), O.last_sample())
+    rg = G.grow(scenes.GOAL, n_iter - 100)
+    ro = O.grow(scenes.GOAL, n_iter - 100)
+    assert rg == ro
+    _same_tree32(G, O)
+    if rg[0]:
+        ps, pt = G.path(rg[1])
+        qs, qt = O.path(ro[1])
+        assert np.array_equal(ps, qs) and np.array_equal(pt, qt)
+        assert G.result(*rg).tobytes() == O.result(*ro).tobytes()
+    for P in (G, O):                                       # restart on the same context
+        P.set_start(scenes.GOAL)
+        P.grow(scenes.START, 500)
+    _same_tree32(G, O)
+    G.close()
+
+
+@pytest.mark.gpu
+def test_f32_single_tree_large_and_full(gpu_required):
+    """30 000 iterations without a goal (grid index from 8192 nodes on, windows of 1024 samples), then a tree that fills up."""
+    G, O = _pair32(0, 30002)
+    G.grow(None, 30000)
+    O.grow(None, 30000)
+    _same_tree32(G, O)
+    assert G.size > 20000
+    G.close()
+    from robosoccer_motion_planning_b200 import scenes
+    G, O = _pair32(1, 300, p_direct=0.1)
+    for P in (G, O):
+        P.grow(scenes.GOAL, 600)
+    assert G.size == O.size == 300 and G.grow_done()[1]
+    _same_tree32(G, O)
+    G.close()
+
+
+@pytest.mark.gpu
+def test_f32_tree_close_to_the_binary64_tree(gpu_required):
+    """north_star's fp32 criterion on a single tree: the float tree has the binary64 tree's parents wherever no decision sat within
+    float rounding of a tie — here for the first few hundred expansions of a plan — and costs / times within 1e-4 there."""
+    from robosoccer_motion_planning_b200 import capi, scenes
+    G32 = capi.Planner(precision=capi.KRRT_F32, capacity=4096, p_direct=0.1)
+    G64 = capi.Planner(capacity=4096, p_direct=0.1)
+    for P in (G32, G64):
+        P.set_obstacles(scenes.dynamic_obstacles(), 1)
+        P.set_start(scenes.START)
+        P.grow(scenes.GOAL, 400)
+    s32, p32, c32, t32 = G32.tree()
+    s64, p64, c64, t64 = G64.tree()
+    n = min(len(p32), len(p64))
+    same = p32[:n] == p64[:n]
+    assert len(p32) == len(p64) and same.mean() >= 0.99
+    ok = same & (c64[:n] > 0)
+    assert (np.abs(c32[:n][ok] - c64[:n][ok]) <= RTOL_F32 * c64[:n][ok]).all()
+    assert (np.abs(t32[:n][ok] - t64[:n][ok]) <= RTOL_F32 * t64[:n][ok]).all()
+    G32.close()
+    G64.close()
+
+
+@pytest.mark.gpu
+def test_f32_context_refuses_what_is_binary64_only(gpu_required):
     from robosoccer_motion_planning_b200 import capi, scenes
     G = capi.Planner(precision=capi.KRRT_F32)
-    with pytest.raises(capi.KrrtError) as e:
-        G.set_start(scenes.START)
-    assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
+    G.set_start(scenes.START)
+    G.grow(scenes.GOAL, 50)
+    for call in (lambda: G.grow_logged(scenes.GOAL, 10), lambda: G.trajectory(1), lambda: G.near(scenes.GOAL, 1.0),
+                 lambda: G.tree_edges()):
+        with pytest.raises(capi.KrrtError) as e:
+            call()
+        assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
     G.close()
 
 
