@@ -511,6 +511,29 @@ def run_ours(args, rank, world, local_rank):
                          "peak": f32_peak, "unit": "TFLOP/s", "frac": f_tflops / f32_peak,
                          "peak_source": "measured (profiles/r1_fp_peak.json, FMA-chain microbenchmark)"}}
         S32.close()
+        # ... and the headline plan on a KRRT_F32 context (k_grow compiled in float), against the float checker
+        G32 = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, precision=capi.KRRT_F32)
+        O32 = of.OraclePlannerF32(capacity=N_ITER + 2, p_direct=P_DIRECT)
+        for P_ in (G32, O32):
+            P_.set_obstacles(obs, 1)
+            P_.set_start(start)
+        r32 = G32.grow(goal, N_ITER)
+        ro32 = O32.grow(goal, N_ITER)
+        same32 = r32 == ro32 and all(np.array_equal(a, b) for a, b in zip(G32.tree(), O32.tree())) and G32.stats() == O32.stats()
+        ms32 = 0.0
+        for _ in range(args.steps):
+            G32.set_start(start)
+            flush_l2()
+            G32.grow(goal, N_ITER)
+            ms32 += G32.last_timing()["total_ms"]
+        line["single_tree_f32"] = {"dtype": "f32", "workload": WORKLOAD.replace("fp64", "KRRT_F32 context"),
+                                   "expansions_per_sec": N_ITER * args.steps / (ms32 * 1e-3), "ms_per_step": ms32 / args.steps,
+                                   "speedup_over_f64": (tot_ms / args.steps) / (ms32 / args.steps),
+                                   "tree_nodes": int(G32.size), "cost": float(G32.result(*r32)["cost"]),
+                                   "cost_rel_diff_vs_f64": abs(float(G32.result(*r32)["cost"]) - float(res["cost"])) / float(res["cost"]),
+                                   "parity_vs_float_checker": "bit-exact" if same32 else "MISMATCH"}
+        G32.close()
+        O32.close()
         # config 0 (rrtstar_benchmark, C1): static obstacles, fixed seed, 10k iterations — GPU and the CPU port, same plan
         G1 = capi.Planner(device=local_rank, capacity=10002, batch=args.batch)
         O1 = ob.OraclePlanner(capacity=10002, query_id=0)

@@ -516,7 +516,15 @@ int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double
 static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index,
                      krrt_iter_record* records) {
   if (!ctx) return KRRT_ERR_INVALID;
-  if (!records) F32_FORWARD(krrt_f32_api::tree_grow(ctx->f32, goal, n_iter, samples, solved, goal_index));
+  if (!records && ctx->cfg.precision == KRRT_F32) {  // the binary32 planner (krrt_f32.cu); krrt_last_timing gives its device time
+    const int rc32 = krrt_f32_api::tree_grow(ctx->f32, goal, n_iter, samples, solved, goal_index);
+    double ms32 = 0.0;
+    krrt_f32_api::tree_grow_done(ctx->f32, nullptr, nullptr, &ms32);
+    ctx->last_total_ms = ms32;
+    ctx->launches += 3;
+    if (rc32 != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
+    return rc32;
+  }
   F64_ONLY();
   REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
   REQUIRE(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
