@@ -92,8 +92,9 @@ class ClockSampler:
         t1 = time.monotonic()
         t0 = getattr(self, "t0", 0.0)
         time.sleep(0.03)    # (a sample that was being taken when the region ended)
-        inside = [ln for (ts, ln) in self.lines if t0 <= ts <= t1 + 0.03]
-        self.lines = inside if inside else [ln for (_, ln) in self.lines[-3:]]
+        raw = list(self.lines)    # (the reader thread keeps appending until the process is terminated below)
+        inside = [ln for (ts, ln) in raw if t0 <= ts <= t1 + 0.03]
+        lines = inside if inside else [ln for (_, ln) in raw[-3:]]
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -101,7 +102,7 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
