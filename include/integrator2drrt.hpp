@@ -141,7 +141,9 @@ class TreeInt2D {
     c.S = edge_samples;
     c.precision = precision;
   }
-  int precision = KRRT_F64;  // KRRT_F32: the whole planner in binary32 (krrt.h); the reference is double throughout
+  // KRRT_F32: the whole planner in binary32 (krrt.h); the reference is double throughout.  (Environment KRRT_PRECISION=f32
+  // makes it the default: the reference's unmodified node can be run either way.)
+  int precision = krrt::default_precision();
   int capacity = 1 << 16;
   int edge_samples = 10;
 

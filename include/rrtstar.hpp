@@ -28,6 +28,12 @@
 
 namespace krrt {
 
+// KRRT_PRECISION=f32 in the environment: the component set plans in binary32 unless told otherwise (krrt.h: KRRT_F32)
+inline int default_precision() {
+  const char* e = std::getenv("KRRT_PRECISION");
+  return (e && (e[0] == 'f' || e[0] == 'F') && e[1] == '3') ? KRRT_F32 : KRRT_F64;
+}
+
 struct Error : std::runtime_error {
   int code;
   Error(int c, const std::string& what) : std::runtime_error("krrt[" + std::to_string(c) + "]: " + what), code(c) {}

@@ -195,7 +195,30 @@ static int trajectory_of_chain(krrt_ctx* ctx, const double* d_states, const doub
 
 int krrt_trajectory(krrt_ctx* ctx, int idx, double dt, double* rows, int cap_rows, int* n_rows) {
   if (!ctx || !n_rows) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  if (ctx->cfg.precision == KRRT_F32) {  // the chain root -> idx of the binary32 tree, re-solved by the float Connector kernels
+    REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
+    CK(cudaSetDevice(ctx->cfg.device));
+    int n32 = 0;
+    int rc32 = krrt_f32_api::tree_info(ctx->f32, &n32, nullptr, nullptr, nullptr, nullptr);
+    std::vector<double> st(4 * (size_t)(n32 + 1)), tm((size_t)n32 + 1);
+    int len = 0;
+    if (rc32 == KRRT_OK) rc32 = krrt_f32_api::tree_path(ctx->f32, idx, st.data(), tm.data(), n32 + 1, &len);
+    if (rc32 != KRRT_OK) {
+      ctx->err = krrt_f32_api::tree_error(ctx->f32);
+      return rc32;
+    }
+    if (len <= 0) {
+      *n_rows = 0;
+      return KRRT_OK;
+    }
+    if ((rc32 = ensure_scratch(ctx, 0, sizeof(double) * 4 * (size_t)len)) != KRRT_OK) return rc32;
+    if ((rc32 = ensure_scratch(ctx, 1, sizeof(double) * (size_t)len)) != KRRT_OK) return rc32;
+    CK(cudaMemcpyAsync(ctx->d_scratch[0], st.data(), sizeof(double) * 4 * (size_t)len, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->d_scratch[1], tm.data(), sizeof(double) * (size_t)len, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return trajectory_of_chain(ctx, (const double*)ctx->d_scratch[0], (const double*)ctx->d_scratch[1], len, dt, rows, cap_rows,
+                               n_rows);
+  }
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(dt > 0.0 && cap_rows >= 0, KRRT_ERR_INVALID, "dt must be > 0");
   CK(cudaSetDevice(ctx->cfg.device));
@@ -635,7 +658,32 @@ int krrt_edge_samples(krrt_ctx* ctx, const double* xi, const double* xf, const d
 
 int krrt_tree_edges(krrt_ctx* ctx, int S, double* rows, int cap_nodes) {
   if (!ctx || !rows) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  if (ctx->cfg.precision == KRRT_F32) {
+    // binary32 tree: the stored edge parent -> node is the optimal edge between the two states departing at the parent's
+    // arrival time, i.e. what the float Connector kernel gives for (states[parent], states[node], time[parent])
+    REQUIRE(S >= 1 && cap_nodes >= 0, KRRT_ERR_INVALID, "S < 1 / cap_nodes < 0");
+    int n32 = 0, gi32 = -1;
+    int rc32 = krrt_f32_api::tree_info(ctx->f32, &n32, nullptr, nullptr, nullptr, &gi32);
+    if (rc32 != KRRT_OK) {
+      ctx->err = krrt_f32_api::tree_error(ctx->f32);
+      return rc32;
+    }
+    const int n = std::min(n32 + (gi32 == n32 ? 1 : 0), cap_nodes);
+    if (n == 0) return KRRT_OK;
+    std::vector<double> st(4 * (size_t)n), tm((size_t)n), xi(4 * (size_t)n), t0((size_t)n);
+    std::vector<int32_t> par((size_t)n);
+    if ((rc32 = krrt_tree_read(ctx, 0, n, st.data(), par.data(), nullptr, tm.data())) != KRRT_OK) return rc32;
+    for (int i = 1; i < n; ++i) {
+      for (int d = 0; d < 4; ++d) xi[4 * (size_t)i + d] = st[4 * (size_t)par[i] + d];
+      t0[i] = tm[par[i]];
+    }
+    for (int k = 0; k < S; ++k) {
+      double* row = rows + 5 * (size_t)k;
+      row[0] = st[0]; row[1] = st[1]; row[2] = st[2]; row[3] = st[3]; row[4] = 0.0;
+    }
+    if (n == 1) return KRRT_OK;
+    return krrt_edge_samples(ctx, xi.data() + 4, st.data() + 4, t0.data() + 1, n - 1, S, rows + 5 * (size_t)S);
+  }
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(S >= 1 && cap_nodes >= 0, KRRT_ERR_INVALID, "S < 1 / cap_nodes < 0");
   CK(cudaSetDevice(ctx->cfg.device));

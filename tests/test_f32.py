@@ -262,13 +262,39 @@ def test_f32_tree_close_to_the_binary64_tree(gpu_required):
 
 
 @pytest.mark.gpu
+def test_f32_tree_edges_and_trajectory(gpu_required):
+    """tree.trajectories (robosoccer_visual.hpp:18) and the fine re-solve of the found path (…node.cpp:232-249) on a binary32 tree."""
+    from robosoccer_motion_planning_b200 import scenes
+    G, O = _pair32(1, 2002, p_direct=0.1)
+    rg = G.grow(scenes.GOAL, 1500)
+    ro = O.grow(scenes.GOAL, 1500)
+    assert rg == ro and rg[0]
+    st, par, ctc, tim = O.tree()
+    S = 10
+    E = G.tree_edges(S)
+    n = len(par) + (1 if rg[1] == len(par) else 0)
+    assert E.shape[0] == n
+    assert np.array_equal(E[0, :, :4], np.broadcast_to(st[0], (S, 4))) and not E[0, :, 4].any()
+    tau, _ = of.steer(st[par[1:]], st[1:])
+    for i in range(1, len(par), 37):
+        for k in (0, 3, S - 1):
+            h = np.float32(k) / np.float32(S - 1)
+            assert np.array_equal(E[i, k, :4], of.edge_state(st[par[i]], st[i], tau[i - 1], h)), (i, k)
+            assert E[i, k, 4] == float(np.float32(tim[par[i]]) + np.float32(tau[i - 1]) * h)
+    rows = G.trajectory(rg[1], dt=0.1)
+    path, ptime = O.path(ro[1])
+    want = np.concatenate([of.solve(a, b, 0.5, 0.1, t0) for a, b, t0 in zip(path[:-1], path[1:], ptime[:-1])])
+    assert rows.shape == want.shape and np.array_equal(rows, want)
+    G.close()
+
+
+@pytest.mark.gpu
 def test_f32_context_refuses_what_is_binary64_only(gpu_required):
     from robosoccer_motion_planning_b200 import capi, scenes
     G = capi.Planner(precision=capi.KRRT_F32)
     G.set_start(scenes.START)
     G.grow(scenes.GOAL, 50)
-    for call in (lambda: G.grow_logged(scenes.GOAL, 10), lambda: G.trajectory(1), lambda: G.near(scenes.GOAL, 1.0),
-                 lambda: G.tree_edges()):
+    for call in (lambda: G.grow_logged(scenes.GOAL, 10), lambda: G.near(scenes.GOAL, 1.0)):
         with pytest.raises(capi.KrrtError) as e:
             call()
         assert e.value.code == capi.KRRT_ERR_UNSUPPORTED

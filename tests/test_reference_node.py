@@ -33,10 +33,13 @@ def test_reference_node_compiles_unmodified_and_has_no_cpu_fallback():
     assert "no CPU fallback" in r.stderr          # krrt::Error(KRRT_ERR_NO_DEVICE) out of rrt.setStart: nothing plans on the host
 
 
-def _oracle_cycle(dynamic, target_size, direct, p):
-    """What …node.cpp:118-141,167-196,232-249 does in one cycle, on the oracle."""
+def _oracle_cycle(dynamic, target_size, direct, p, f32=False):
+    """What …node.cpp:118-141,167-196,232-249 does in one cycle, on the oracle (its float build for a binary32 run)."""
     import oracle_binding as ob
     from robosoccer_motion_planning_b200 import scenes
+    if f32:
+        import oracle_f32_binding as of
+        ob = type("F32", (), {"OraclePlanner": staticmethod(lambda **kw: of.OraclePlannerF32(**kw)), "solve": staticmethod(of.solve)})
     vel = np.array([(0.5, -0.25), (-0.5, 0.75), (0.25, 0.5), (-0.75, -0.5), (-1, 0.25), (0.5, 0.5), (-0.25, -0.75), (0.75, 0.25),
                     (-0.5, -0.25)])
     obs = scenes.static_obstacles()
@@ -65,8 +68,10 @@ def _oracle_cycle(dynamic, target_size, direct, p):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("environment,target_size,direct", [("static", 100, False), ("dynamic", 75, True), ("dynamic", 200, True)])
-def test_reference_node_publishes_the_oracles_path(gpu_required, tmp_path, environment, target_size, direct):
+@pytest.mark.parametrize("environment,target_size,direct,precision",
+                         [("static", 100, False, "f64"), ("dynamic", 75, True, "f64"), ("dynamic", 200, True, "f64"),
+                          ("dynamic", 75, True, "f32")])
+def test_reference_node_publishes_the_oracles_path(gpu_required, tmp_path, environment, target_size, direct, precision):
     exe = native_build.build_reference_node()
     if exe is None:
         pytest.skip("no reference node binary (built where /root/reference is mounted; it travels to the GPU box)")
@@ -74,11 +79,12 @@ def test_reference_node_publishes_the_oracles_path(gpu_required, tmp_path, envir
     vis = str(tmp_path / "vis.csv")
     env = {"KRRT_STUB_CYCLES": "1", "KRRT_STUB_GOAL": "7,0", "KRRT_STUB_PATH_CSV": base, "KRRT_RRTVISUAL_CSV": vis,
            "ROSPARAM_environment": environment, "ROSPARAM_target_size": str(target_size), "ROSPARAM_rrtvis_rate": "1e9",
-           "ROSPARAM_direct_sampling": "true" if direct else "false", "ROSPARAM_direct_sampling_prob": "0.1"}
+           "ROSPARAM_direct_sampling": "true" if direct else "false", "ROSPARAM_direct_sampling_prob": "0.1",
+           "KRRT_PRECISION": precision}
     r = _run(exe, env)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "1 cycle(s) done" in r.stdout
-    want, O = _oracle_cycle(environment == "dynamic", target_size, direct, 0.1)
+    want, O = _oracle_cycle(environment == "dynamic", target_size, direct, 0.1, f32=precision == "f32")
     assert ("solution" in r.stderr) and (("not found" not in r.stderr) == (want is not None)), r.stderr
     # the recorder saw the tree: one frame, a DELETEALL in front, the tree's edges
     frame = np.genfromtxt(vis, delimiter=",", skip_header=1, usecols=(0, 1, 2))
@@ -91,4 +97,4 @@ def test_reference_node_publishes_the_oracles_path(gpu_required, tmp_path, envir
     assert np.array_equal(pos[:, 2:4], want[:, 0:2]) and np.array_equal(vel[:, 2:4], want[:, 2:4])
     # stamps: rrt_t0 + time since the root (…node.cpp:319-322)
     assert np.allclose(pos[:, 1] - pos[0, 1], want[:, 4] - want[0, 4], rtol=0, atol=1e-6)
-    assert np.allclose(pos[-1, 2:4], [7.0, 0.0], rtol=0, atol=1e-9)
+    assert np.allclose(pos[-1, 2:4], [7.0, 0.0], rtol=0, atol=1e-9 if precision == "f64" else 1e-5)
