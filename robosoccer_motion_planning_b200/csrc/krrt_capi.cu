@@ -109,7 +109,7 @@ struct krrt_ctx {
 // (a KRRT_F32 context serves the planner proper, the batched planner and the stateless operators: krrt_f32.cu)
 #define F64_ONLY()                                                                                                    \
   REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
-          "not available on a KRRT_F32 context (krrt_grow_logged, krrt_near and the diagnostics are binary64 only)")
+          "not available on a KRRT_F32 context (krrt_near and the diagnostics are binary64 only)")
 
 // KRRT_F32 contexts: the call goes to the binary32 planner; its error text becomes the context's
 #define F32_FORWARD(expr)                                                \
@@ -504,7 +504,15 @@ int krrt_grow(krrt_ctx* ctx, const double* goal, int n_iter, const double* sampl
 int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double* samples, krrt_iter_record* records,
                      int* solved, int* goal_index) {
   if (!ctx || !records) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  if (ctx->cfg.precision == KRRT_F32) {
+    const int rc32 = krrt_f32_api::tree_grow_logged(ctx->f32, goal, n_iter, samples, records, solved, goal_index);
+    double ms32 = 0.0;
+    krrt_f32_api::tree_grow_done(ctx->f32, nullptr, nullptr, &ms32);
+    ctx->last_total_ms = ms32;
+    ctx->launches += 4;
+    if (rc32 != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
+    return rc32;
+  }
   REQUIRE(n_iter >= 1 && n_iter <= ITERLOG_MAX_ITERS, KRRT_ERR_UNSUPPORTED, "krrt_grow_logged: 1 <= n_iter <= 256");
   REQUIRE(ctx->started, KRRT_ERR_STATE, "krrt_grow_logged before krrt_set_start");
   REQUIRE(ctx->n_upper + n_iter <= ITERLOG_STRIDE, KRRT_ERR_UNSUPPORTED,

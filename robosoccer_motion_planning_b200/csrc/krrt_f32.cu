@@ -295,6 +295,9 @@ struct Tree {
   double* d_scr = nullptr;   // path read-out
   int* d_len = nullptr;
   size_t scr_cap = 0;
+  unsigned char* d_iterlog = nullptr;  // logged calls: the IterLog views + the device records (one allocation)
+  IterLog ilog = {nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  IterRec* d_iterrec = nullptr;
   int wave_min_n = 32;
   int64_t launches = 0, last_iters = 0;
   int last_full = 0;
@@ -440,6 +443,7 @@ static int create_body(Tree* t) {
   {
     const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));
     TCK(cudaFuncSetAttribute(k_grow, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+    TCK(cudaFuncSetAttribute(k_grow_logged, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
     int per_sm = 0, coop = 0;
     TCK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow, GROW_THREADS, dyn));
     TCK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c.device));
@@ -475,6 +479,7 @@ void tree_destroy(Tree* t) {
   if (t->arena) cudaFree(t->arena);
   if (t->d_user) cudaFree(t->d_user);
   if (t->d_scr) cudaFree(t->d_scr);
+  if (t->d_iterlog) cudaFree(t->d_iterlog);
   if (t->h_ctl) cudaFreeHost(t->h_ctl);
   if (t->ev0) cudaEventDestroy(t->ev0);
   if (t->ev1) cudaEventDestroy(t->ev1);
@@ -536,7 +541,27 @@ static int fetch(Tree* t, Ctl* h) {
   return KRRT_OK;
 }
 
+static int grow_body(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real* samples, int* solved, int* goal_index,
+                     krrt_iter_record* records);
+
 int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real* samples, int* solved, int* goal_index) {
+  return grow_body(t, goal, n_iter, samples, solved, goal_index, nullptr);
+}
+
+constexpr int F32_LOG_MAX_ITERS = 256, F32_LOG_STRIDE = 1024;
+
+int tree_grow_logged(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real* samples, krrt_iter_record* records,
+                     int* solved, int* goal_index) {
+  TREQ(records != nullptr, KRRT_ERR_INVALID, "null records");
+  TREQ(n_iter >= 1 && n_iter <= F32_LOG_MAX_ITERS, KRRT_ERR_UNSUPPORTED, "krrt_grow_logged: 1 <= n_iter <= 256");
+  TREQ(t->started, KRRT_ERR_STATE, "krrt_grow_logged before krrt_set_start");
+  TREQ(t->n_upper + n_iter <= F32_LOG_STRIDE, KRRT_ERR_UNSUPPORTED,
+       "krrt_grow_logged: the tree would outgrow the 1024 nodes a logged call can record; use krrt_grow");
+  return grow_body(t, goal, n_iter, samples, solved, goal_index, records);
+}
+
+static int grow_body(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real* samples, int* solved, int* goal_index,
+                     krrt_iter_record* records) {
   TREQ(t->started, KRRT_ERR_STATE, "krrt_grow before krrt_set_start");
   TREQ(n_iter >= 0, KRRT_ERR_INVALID, "n_iter < 0");
   TCK(cudaSetDevice(t->cfg.device));
@@ -566,6 +591,26 @@ int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real*
   gcfg.bar = t->d_bar;
   gcfg.gi = t->gi;
   gcfg.log = IterLog{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  const int n_before = t->n_upper;
+  if (records) {
+    if (!t->d_iterlog) {
+      const size_t rows = F32_LOG_MAX_ITERS + 1, it = F32_LOG_MAX_ITERS;
+      const size_t b_snap = rows * F32_LOG_STRIDE * sizeof(double), b_smp = it * 4 * sizeof(double), b_int = it * sizeof(int),
+                   b_rec = (it * sizeof(IterRec) + 15) / 16 * 16;
+      TCK(cudaMalloc((void**)&t->d_iterlog, 2 * b_snap + b_smp + b_rec + 2 * b_int));
+      unsigned char* q = t->d_iterlog;
+      t->ilog.snap_ctc = (double*)q; q += b_snap;
+      t->ilog.snap_tim = (double*)q; q += b_snap;
+      t->ilog.sample = (double*)q; q += b_smp;
+      t->d_iterrec = (IterRec*)q; q += b_rec;
+      t->ilog.n_after = (int*)q; q += b_int;
+      t->ilog.snap_of = (int*)q;
+      t->ilog.stride = F32_LOG_STRIDE;
+      t->ilog.rows = (int)rows;
+    }
+    gcfg.log = t->ilog;
+    gcfg.wave_enabled = 0;  // every iteration goes through the in-order commit, which keeps the records
+  }
   {
     auto envi = [](const char* k, int d) { const char* e = std::getenv(k); return e ? std::atoi(e) : d; };
     gcfg.pend_resolve = envi("KRRT_PEND", 1);
@@ -593,7 +638,11 @@ int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real*
     t->ctl_valid = false;
     k_begin_grow<<<1, 32, 0, st>>>(t->d_ctl, launch == 0, goal ? 1 : 0, g, n_iter, t->Bt, t->d_bar, wrap ? 1 : 0, t->T, gcfg.log);
     void* args[] = {(void*)&t->d_ctl, (void*)&t->P, (void*)&t->T, (void*)&t->Bt, (void*)&t->W, (void*)&gcfg};
-    TCK(cudaLaunchCooperativeKernel((const void*)k_grow, dim3(t->grow_grid), dim3(GROW_THREADS), args, (size_t)dyn, st));
+    if (records && t->n_upper + n_iter <= 512)  // (as in binary64: a small logged call is one CTA, plain launch)
+      k_grow_logged<<<1, GROW_THREADS, (size_t)dyn, st>>>(t->d_ctl, t->P, t->T, t->Bt, t->W, gcfg);
+    else
+      TCK(cudaLaunchCooperativeKernel(records ? (const void*)k_grow_logged : (const void*)k_grow, dim3(t->grow_grid),
+                                      dim3(GROW_THREADS), args, (size_t)dyn, st));
     if (t->P.goal_mode == KRRT_GOAL_TOLERANCE) {
       k_find_goal<<<1, 1024, 0, st>>>(t->d_ctl, t->T, t->P.goal_tol2);
     } else {
@@ -601,6 +650,10 @@ int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real*
       const int ctas = (int)std::max<long long>(1, std::min<long long>(std::min(GOAL_MAX_CTAS, 4 * t->sms),
                                                                        (n_max + GOAL_THREADS - 1) / GOAL_THREADS));
       k_goal_connect<<<ctas, GOAL_THREADS, 0, st>>>(t->d_ctl, t->P, t->T, t->goal_scr);
+    }
+    if (records) {
+      k_goal_log<<<n_iter, GLOG_THREADS, 0, st>>>(t->d_ctl, t->P, t->T, gcfg.log, n_iter, n_before, t->d_iterrec);
+      t->launches += 1;
     }
     TCK(cudaEventRecord(t->ev1, st));
     t->launches += 3;
@@ -616,6 +669,19 @@ int tree_grow(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_io_real*
   if (h.error) {
     t->err = h.error == KRRT_ERR_NEAR_OVERFLOW ? "near set exceeded near_cap; raise krrt_config.near_cap" : "device error";
     return h.error;
+  }
+  if (records) {  // the device records are float: widen into the C ABI's layout
+    std::vector<IterRec> hr((size_t)n_iter);
+    TCK(cudaMemcpyAsync(hr.data(), t->d_iterrec, sizeof(IterRec) * (size_t)n_iter, cudaMemcpyDeviceToHost, st));
+    TCK(cudaStreamSynchronize(st));
+    for (int i = 0; i < n_iter; ++i) {
+      records[i].n_nodes = hr[i].n_nodes;
+      records[i].solved = hr[i].solved;
+      records[i].goal_index = hr[i].goal_index;
+      records[i].inserted = hr[i].inserted;
+      for (int k = 0; k < 4; ++k) records[i].sample[k] = hr[i].sample[k];
+      records[i].goal_cost = hr[i].goal_cost;
+    }
   }
   if (solved) *solved = h.goal_index >= 0;
   if (goal_index) *goal_index = h.goal_index;

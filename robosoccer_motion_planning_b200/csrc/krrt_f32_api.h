@@ -63,6 +63,9 @@ int tree_set_params(Tree* t, const krrt_config* cfg);
 int tree_set_obstacles(Tree* t, const double* xyvxvy, int m, int dynamic);
 int tree_set_start(Tree* t, const double x0[4]);
 int tree_grow(Tree* t, const double* goal, int n_iter, const double* samples, int* solved, int* goal_index);
+// krrt_grow_logged: records != nullptr (1 <= n_iter <= 256, tree size after the call <= 1024)
+int tree_grow_logged(Tree* t, const double* goal, int n_iter, const double* samples, krrt_iter_record* records, int* solved,
+                     int* goal_index);
 int tree_grow_done(Tree* t, int64_t* iterations_done, int* full, double* ms);
 int tree_info(Tree* t, int* n, int64_t* iteration, double last_sample[4], krrt_stats* stats, int* goal_index);
 int tree_read(Tree* t, int first, int count, double* states, int32_t* parent, double* cost, double* time);

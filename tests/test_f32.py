@@ -262,6 +262,29 @@ def test_f32_tree_close_to_the_binary64_tree(gpu_required):
 
 
 @pytest.mark.gpu
+def test_f32_grow_logged_equals_single_calls(gpu_required):
+    """krrt_grow_logged on a binary32 tree: record i is what single call i returns and what the caller's loop reads after it."""
+    from robosoccer_motion_planning_b200 import scenes
+    G, O = _pair32(1, 2048, p_direct=0.1)
+    n_iter = 200
+    rows = np.full((n_iter, 4), np.nan)
+    rows[101] = scenes.GOAL
+    rows[199] = scenes.GOAL
+    rec, solved, gi = G.grow_logged(scenes.GOAL, n_iter, rows)
+    n_prev = 1
+    for i in range(n_iter):
+        so, go = O.grow(scenes.GOAL, 1, samples=rows[i:i + 1])
+        assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i])) == (so, go, O.size), i
+        assert bool(rec["inserted"][i]) == (O.size > n_prev) and np.array_equal(rec["sample"][i], O.last_sample()), i
+        if so:
+            assert rec["goal_cost"][i] == O.result(so, go)["cost"], i
+        n_prev = O.size
+    assert (solved, gi) == (so, go)
+    _same_tree32(G, O)
+    G.close()
+
+
+@pytest.mark.gpu
 def test_f32_tree_edges_and_trajectory(gpu_required):
     """tree.trajectories (robosoccer_visual.hpp:18) and the fine re-solve of the found path (…node.cpp:232-249) on a binary32 tree."""
     from robosoccer_motion_planning_b200 import scenes
@@ -294,7 +317,7 @@ def test_f32_context_refuses_what_is_binary64_only(gpu_required):
     G = capi.Planner(precision=capi.KRRT_F32)
     G.set_start(scenes.START)
     G.grow(scenes.GOAL, 50)
-    for call in (lambda: G.grow_logged(scenes.GOAL, 10), lambda: G.near(scenes.GOAL, 1.0)):
+    for call in (lambda: G.near(scenes.GOAL, 1.0),):
         with pytest.raises(capi.KrrtError) as e:
             call()
         assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
