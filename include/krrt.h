@@ -68,8 +68,9 @@ typedef struct krrt_config {
                          tests): the planner proper (krrt_set_start, krrt_grow, krrt_tree_*, krrt_path, krrt_result_of, ...),
                          krrt_plan_batch* and the stateless operators — the SAME kernels compiled in float, bit-exact with the
                          checker's float build; costs and times within 1e-4 of binary64 on the same edge.  Arrays at this
-                         interface stay binary64 (rounded on the way in, widened on the way out).  krrt_near and the
-                         diagnostics are binary64 only (KRRT_ERR_UNSUPPORTED on such a context) */
+                         interface stay binary64 (rounded on the way in, widened on the way out).  Every
+                         planning entry point serves both precisions; the development diagnostics below report the
+                         binary64 planner's phases only */
   int32_t capacity;   /* max tree nodes                                                      */
   int32_t S;          /* samples per edge for collision checks, both end points included     */
   double r;           /* input weight of J = int (1 + r|u|^2) dt; solver.set_weight(r) (…node.cpp:91-92) */

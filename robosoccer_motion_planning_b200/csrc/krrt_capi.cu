@@ -109,7 +109,7 @@ struct krrt_ctx {
 // (a KRRT_F32 context serves the planner proper, the batched planner and the stateless operators: krrt_f32.cu)
 #define F64_ONLY()                                                                                                    \
   REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
-          "not available on a KRRT_F32 context (krrt_near and the diagnostics are binary64 only)")
+          "not available on a KRRT_F32 context (the development diagnostics are binary64 only)")
 
 // KRRT_F32 contexts: the call goes to the binary32 planner; its error text becomes the context's
 #define F32_FORWARD(expr)                                                \

@@ -342,7 +342,7 @@ int krrt_edge_collide(krrt_ctx* ctx, const double* xi, const double* xf, const d
 int krrt_near(krrt_ctx* ctx, const double x[4], double radius2, int32_t* idx, int cap, int* count, int32_t* nearest,
               double* nearest_d2) {
   if (!ctx || !x) return KRRT_ERR_INVALID;
-  F64_ONLY();
+  F32_FORWARD(krrt_f32_api::tree_near(ctx->f32, x, radius2, idx, cap, count, nearest, nearest_d2));
   REQUIRE(ctx->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   REQUIRE(cap >= 0 && (cap == 0 || idx), KRRT_ERR_INVALID, "null buffer");
   CK(cudaSetDevice(ctx->cfg.device));

@@ -695,6 +695,32 @@ int tree_grow_done(Tree* t, int64_t* iterations_done, int* full, krrt_io_real* m
   return KRRT_OK;
 }
 
+int tree_near(Tree* t, const krrt_io_real x[4], krrt_io_real radius2, int32_t* idx, int cap, int* count, int32_t* nearest,
+              krrt_io_real* nearest_d2) {
+  TREQ(t->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
+  TREQ(cap >= 0 && (cap == 0 || idx), KRRT_ERR_INVALID, "null buffer");
+  TCK(cudaSetDevice(t->cfg.device));
+  Ctl h;
+  int rc = fetch(t, &h);
+  if (rc != KRRT_OK) return rc;
+  int* d_buf = nullptr;  // [count, nearest, d2 (float), pad] + the index list
+  TCK(cudaMalloc((void**)&d_buf, sizeof(int) * (4 + (size_t)std::max(cap, 1))));
+  const State4 s = {(double)x[0], (double)x[1], (double)x[2], (double)x[3]};
+  k_near_query<<<1, 1024, 0, t->st>>>(t->T, h.n, s, (double)radius2, d_buf + 4, cap, d_buf, d_buf + 1, (double*)(d_buf + 2));
+  t->launches++;
+  struct { int cnt, nearest; double nd2; int pad; } r;
+  cudaError_t e = cudaMemcpyAsync(&r, d_buf, sizeof(r), cudaMemcpyDeviceToHost, t->st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->st);
+  const int got = e == cudaSuccess ? std::min(r.cnt, cap) : 0;
+  if (e == cudaSuccess && got > 0) e = cudaMemcpy(idx, d_buf + 4, sizeof(int) * (size_t)got, cudaMemcpyDeviceToHost);
+  cudaFree(d_buf);
+  TCK(e);
+  if (count) *count = r.cnt;
+  if (nearest) *nearest = r.nearest;
+  if (nearest_d2) *nearest_d2 = r.nd2;
+  return KRRT_OK;
+}
+
 int tree_info(Tree* t, int* n, int64_t* iteration, krrt_io_real last_sample[4], krrt_stats* stats, int* goal_index) {
   TREQ(t->started, KRRT_ERR_STATE, "no tree: call krrt_set_start");
   TCK(cudaSetDevice(t->cfg.device));

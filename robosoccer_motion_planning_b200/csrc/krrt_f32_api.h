@@ -67,6 +67,9 @@ int tree_grow(Tree* t, const double* goal, int n_iter, const double* samples, in
 int tree_grow_logged(Tree* t, const double* goal, int n_iter, const double* samples, krrt_iter_record* records, int* solved,
                      int* goal_index);
 int tree_grow_done(Tree* t, int64_t* iterations_done, int* full, double* ms);
+// krrt_near (radius2 and the returned squared distance in the float metric, widened)
+int tree_near(Tree* t, const double x[4], double radius2, int32_t* idx, int cap, int* count, int32_t* nearest,
+              double* nearest_d2);
 int tree_info(Tree* t, int* n, int64_t* iteration, double last_sample[4], krrt_stats* stats, int* goal_index);
 int tree_read(Tree* t, int first, int count, double* states, int32_t* parent, double* cost, double* time);
 int tree_path(Tree* t, int idx, double* states, double* times, int cap, int* len);

@@ -40,64 +40,7 @@ __global__ void __launch_bounds__(128) k_edge_collide_batch(const double* __rest
   if (lane_id() == 0) hit[e] = h ? 1 : 0;
 }
 
-// radius + nearest query of one state against the tree; ascending indices (single CTA, ordered compaction)
-__global__ void __launch_bounds__(1024) k_near_query(TreeView T, int n, State4 x, double radius2, int* out_idx,
-                                                      int cap, int* out_count, int* out_nearest,
-                                                      double* out_nearest_d2) {
-  __shared__ int s_cnt[32];
-  __shared__ double s_d[32];
-  __shared__ int s_i[32];
-  __shared__ int s_total;
-  const int lane = lane_id(), warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_total = 0;
-  __syncthreads();
-  double bd = INFINITY;
-  int bi = -1, aux = 0;
-  for (int base = 0; base < n; base += 1024) {
-    int i = base + threadIdx.x;
-    bool valid = false;
-    if (i < n) {
-      double d = dist2(load_state(T, i), x);
-      if (bi < 0 || d < bd) {
-        bd = d;
-        bi = i;
-      }
-      valid = d <= radius2;
-    }
-    unsigned mk = __ballot_sync(FULL, valid);
-    if (lane == 0) s_cnt[warp] = __popc(mk);
-    __syncthreads();
-    int off = s_total;
-    for (int w = 0; w < warp; ++w) off += s_cnt[w];
-    if (valid) {
-      int k = off + __popc(mk & ((1u << lane) - 1));
-      if (k < cap) out_idx[k] = i;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      int tot = 0;
-      for (int w = 0; w < 32; ++w) tot += s_cnt[w];
-      s_total += tot;
-    }
-    __syncthreads();
-  }
-  warp_argmin(bd, bi, aux);
-  if (lane == 0) {
-    s_d[warp] = bd;
-    s_i[warp] = bi;
-  }
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    bd = s_d[threadIdx.x];
-    bi = s_i[threadIdx.x];
-    warp_argmin(bd, bi, aux);
-    if (threadIdx.x == 0) {
-      *out_count = s_total;
-      *out_nearest = bi;
-      *out_nearest_d2 = bd;
-    }
-  }
-}
+// (k_near_query, the radius + nearest query behind krrt_near, lives in krrt_kernels.cuh: both precisions use it)
 
 // root -> idx chain (tree.states(idx), …node.cpp:237): states (len x 4) and arrival times, root first
 __global__ void k_path_extract(TreeView T, int n, int idx, double* states, double* times, int cap, int* out_len) {

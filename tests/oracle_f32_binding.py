@@ -233,6 +233,19 @@ class OraclePlannerF32:
         lib().ko_get_stats(self.h, ctypes.byref(s))
         return {n: getattr(s, n) for n, _ in ob.KoStats._fields_}
 
+    def near(self, x, radius2, cap=4096):
+        x = _f32(x)
+        idx = np.empty(cap, dtype=np.int32)
+        nearest = ctypes.c_int32(-1)
+        nd2 = ctypes.c_float(0)
+        L = lib()
+        L.ko_near.argtypes = [ctypes.c_void_p, F, ctypes.c_float, I, ctypes.c_int, ctypes.POINTER(ctypes.c_int32),
+                              ctypes.POINTER(ctypes.c_float)]
+        L.ko_near.restype = ctypes.c_int
+        k = L.ko_near(self.h, _f(x), float(np.float32(radius2)), idx.ctypes.data_as(I), cap, ctypes.byref(nearest),
+                      ctypes.byref(nd2))
+        return idx[:min(k, cap)].copy(), nearest.value, float(nd2.value)
+
     def path(self, idx, cap=4096):
         st = np.empty((cap, 4), dtype=np.float32)
         tm = np.empty(cap, dtype=np.float32)

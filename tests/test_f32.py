@@ -312,15 +312,22 @@ def test_f32_tree_edges_and_trajectory(gpu_required):
 
 
 @pytest.mark.gpu
-def test_f32_context_refuses_what_is_binary64_only(gpu_required):
-    from robosoccer_motion_planning_b200 import capi, scenes
-    G = capi.Planner(precision=capi.KRRT_F32)
-    G.set_start(scenes.START)
-    G.grow(scenes.GOAL, 50)
-    for call in (lambda: G.near(scenes.GOAL, 1.0),):
-        with pytest.raises(capi.KrrtError) as e:
-            call()
-        assert e.value.code == capi.KRRT_ERR_UNSUPPORTED
+def test_f32_near_query(gpu_required):
+    """krrt_near on a binary32 tree: indices, nearest node and its squared distance are the float checker's."""
+    from robosoccer_motion_planning_b200 import scenes
+    G, O = _pair32(0, 8192)
+    for P in (G, O):
+        P.grow(None, 4000)
+    rng = np.random.default_rng(4)
+    for k in range(20):
+        x = rng.uniform(scenes.FIELD_LO, scenes.FIELD_HI, 4)
+        r2 = [0.0, 0.3, 1.0, 9.0, 400.0][k % 5]
+        gi, gn, gd = G.near(x, r2, cap=8192)
+        oi, on, od = O.near(x, r2, cap=8192)
+        assert np.array_equal(gi, oi) and gn == on and gd == od, k
+    s = O.tree()[0][123]
+    gi, gn, gd = G.near(s, 0.0)
+    assert list(gi) == [123] and gn == 123 and gd == 0.0
     G.close()
 
 
