@@ -69,6 +69,7 @@ struct krrt_ctx {
   Ctl* h_ctl = nullptr;       // pinned host copy of the control block ...
   bool ctl_valid = false;     // ... current until the next call that changes the tree (krrt_set_start, krrt_grow)
   int batch_v1 = 0;           // KRRT_BATCH_V1=1 in the environment: the shared-memory-list kernel only (A-B timing)
+  int b2_wave_fit = 1;        // KRRT_B2_WAVE_FIT=0: k_plan_batch2 with the most warps per CTA that fit even for a small batch (A-B timing)
   int rho2_batch_cap = -1, rho2_batch_alloc = 0;
   std::vector<double> h_rho2_batch;
   int* d_counter = nullptr;
@@ -325,6 +326,7 @@ static int create_impl(krrt_ctx* ctx) {
   CK(dev_alloc(ctx, &ctx->d_bar, (size_t)2));
   if (const char* e = std::getenv("KRRT_WAVE")) ctx->wave_enabled = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_BATCH_V1")) ctx->batch_v1 = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KRRT_B2_WAVE_FIT")) ctx->b2_wave_fit = std::atoi(e) != 0;
   if (const char* e = std::getenv("KRRT_WAVE_MIN_N")) ctx->wave_min_n = std::max(2, std::atoi(e));
   {
     const int dyn = (int)(grow_shared_bytes() + commit_smem_bytes(B.near_cap));

@@ -460,16 +460,24 @@ static int launch_plan_batch(krrt_ctx* ctx, const double* d_starts, const double
     J2.b = J;
     J2.redo_count = ctx->d_redo + 1;
     J2.redo_list = ctx->d_redo + 2;
-    const size_t smem2 = (size_t)w2 * pw2;
+    // a batch that fits the resident warps in one go is spread over ALL SMs (512 queries: 128 CTAs of 4 warps, not 32 CTAs of
+    // 16 — each warp gets four times the issue slots: 1.13 -> 0.94 ms, profiles/r2_wave_fit_s16.txt); a larger batch keeps the
+    // most warps that fit, because warps pull queries from a counter and more slots even out the unequal queries
+    int w_run = w2;
+    if (ctx->b2_wave_fit) {
+      const long long sms = ctx->prop.multiProcessorCount;
+      if ((long long)q <= sms * w2) w_run = (int)std::max<long long>(1, ((long long)q + sms - 1) / sms);
+    }
+    const size_t smem2 = (size_t)w_run * pw2;
     int grid2 = ctx->prop.multiProcessorCount;
-    grid2 = (int)std::max<long long>(1, std::min<long long>(grid2, ((long long)q + w2 - 1) / w2));
+    grid2 = (int)std::max<long long>(1, std::min<long long>(grid2, ((long long)q + w_run - 1) / w_run));
     if (f32) {
       A.redo_count = J2.redo_count;
       A.redo_list = J2.redo_list;
-      CK((cudaError_t)krrt_f32_api::launch_batch2(A, grid2, w2, smem2, st));
+      CK((cudaError_t)krrt_f32_api::launch_batch2(A, grid2, w_run, smem2, st));
     } else {
       CK(cudaFuncSetAttribute(k_plan_batch2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      k_plan_batch2<<<grid2, w2 * 32, smem2, st>>>(J2);
+      k_plan_batch2<<<grid2, w_run * 32, smem2, st>>>(J2);
     }
     ctx->launches++;
     CK(cudaGetLastError());
