@@ -113,7 +113,7 @@ void krrt_destroy(krrt_ctx* ctx);
  * settings: …node.cpp:84-92,225-226).  device / precision / capacity / batch / near_cap must equal the
  * create-time values (else KRRT_ERR_INVALID: create a new context).  The tree is left as it is.            */
 int krrt_set_params(krrt_ctx* ctx, const krrt_config* cfg);
-const char* krrt_last_error(const krrt_ctx* ctx); /* ctx may be NULL: last create error */
+const char* krrt_last_error(const krrt_ctx* ctx); /* ctx may be NULL: last krrt_create / krrt_plan_batch_static error of this thread */
 int krrt_device_count(void);
 
 int krrt_set_obstacles(krrt_ctx* ctx, const double* xyvxvy, int m, int dynamic);
@@ -198,6 +198,36 @@ int krrt_plan_batch_device_chunks(krrt_ctx* ctx, const double* d_starts, const d
                                   const double* d_obstacles, int q, int m, int dynamic, int n_iter,
                                   uint32_t query_base, krrt_result* d_out, int chunk_queries,
                                   uint32_t* d_chunk_done, void* cuda_stream);
+/* krrt_plan_batch_device for callers that are not allowed to allocate device memory.  (No counterpart in the reference:
+ * its planner is CPU code and never meets the question.)
+ *
+ * A krrt_ctx gets its device buffers from cudaMalloc — at krrt_create, and again whenever a batch is larger than any
+ * before it.  That rules the context-based calls out for (a) a planner inside a robot's fixed-rate control cycle, where a
+ * cudaMalloc / cudaFree (driver-wide lock, possibly a wait for the whole device) is a stall of unknown length, and (b) a
+ * process whose device memory is owned by another component's pool, where a raw cudaMalloc fails or takes memory the pool
+ * relies on.  This call needs no context and allocates nothing, on the host or on the device, on any successful path: the
+ * planner's scratch (radius table, work counters, statistics, redo list) is a 264 KB array compiled into libkrrt.so, which
+ * every GPU that loads the library holds until the process exits.  Hence the limits:
+ *     q <= KRRT_STATIC_MAX_QUERIES and n_iter <= KRRT_STATIC_MAX_ITER per call,
+ * beyond which the call returns KRRT_ERR_INVALID before it touches the GPU, and krrt_last_error(NULL) names both limits.
+ *
+ * cfg: the fields a batched plan reads (device, S, r, R, lo, hi, gamma, rho_max, p_direct, goal_tol, seed, goal_mode,
+ * capacity); precision must be KRRT_F64, device < 16.  All pointers are DEVICE memory of cfg->device from the caller's own
+ * allocator, laid out as for krrt_plan_batch_device; the records in d_out are the ones that call writes, byte for byte.
+ * The work is queued on cuda_stream (NULL = the default stream; there is no context stream) and the call returns without
+ * waiting: synchronise the stream before reading d_out.
+ *
+ * - The first call on each device also looks up where that device keeps the array and loads the kernels; make it during
+ *   start-up, outside the time-critical loop and before any stream capture begins.
+ * - There is ONE array per device and every call uses it.  Each call clears the counters it needs at zero and rewrites the
+ *   table it reads, so calls one after the other on a stream are independent; two calls whose GPU work overlaps (different
+ *   streams or threads without an event between them) race on it and return garbage.  Order them.
+ * - No krrt_batch_stats / krrt_launch_count: there is no context to ask (each call launches 2 kernels).                 */
+#define KRRT_STATIC_MAX_QUERIES 65536
+#define KRRT_STATIC_MAX_ITER 1024
+int krrt_plan_batch_static(const krrt_config* cfg, const double* d_starts, const double* d_goals,
+                           const double* d_obstacles, int q, int m, int dynamic, int n_iter, uint32_t query_base,
+                           krrt_result* d_out, void* cuda_stream);
 /* Yaw (heading) profiles for q independent queries: (w, dw) = current heading / rate, yaw = target heading, limits
  * v_max / a_max (Controller::setLimit), n sample rows over [0, final_time] as getAngleTrajectory(ctrl, offset, 0, t, n,
  * &inputs) returns them.  states: q x max(n,1) x 2 (w wrapped to [-pi, pi], dw), times / inputs: q x max(n,1),

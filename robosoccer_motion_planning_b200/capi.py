@@ -19,6 +19,7 @@ KRRT_MAX_WAYPOINTS = 32
 KRRT_OK, KRRT_ERR_INVALID, KRRT_ERR_CUDA, KRRT_ERR_NO_DEVICE, KRRT_ERR_NEAR_OVERFLOW, KRRT_ERR_STATE, \
     KRRT_ERR_UNSUPPORTED = range(7)
 KRRT_F64, KRRT_F32 = 0, 1   # krrt_config.precision
+KRRT_STATIC_MAX_QUERIES, KRRT_STATIC_MAX_ITER = 65536, 1024   # limits of krrt_plan_batch_static
 
 D = ctypes.POINTER(ctypes.c_double)
 I = ctypes.POINTER(ctypes.c_int32)
@@ -33,7 +34,7 @@ EXPORTS = (
     "krrt_timer_end", "krrt_set_params", "krrt_tree_edges", "krrt_edge_samples", "krrt_kernel_times", "krrt_wave_stats", "krrt_tail_commits", "krrt_debug_clocks",
     "krrt_yaw_profiles", "krrt_yaw_profiles_device", "krrt_ingest_vision", "krrt_ingest_vision_device",
     "krrt_solve_inputs", "krrt_scan_stats", "krrt_tree_read", "krrt_goal_index",
-    "krrt_plan_batch_device_chunks", "krrt_host_alloc", "krrt_host_free", "krrt_flush_l2", "krrt_synchronize",
+    "krrt_plan_batch_device_chunks", "krrt_plan_batch_static", "krrt_host_alloc", "krrt_host_free", "krrt_flush_l2", "krrt_synchronize",
 )
 
 
@@ -134,6 +135,9 @@ def lib():
     L.krrt_plan_batch_device_chunks.argtypes = [P, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                                 ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
                                                 ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    L.krrt_plan_batch_static.argtypes = [ctypes.POINTER(KrrtConfig), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                         ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint32,
+                                         ctypes.c_void_p, ctypes.c_void_p]
     L.krrt_host_alloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_uint64]
     L.krrt_host_free.argtypes = [ctypes.c_void_p]
     L.krrt_flush_l2.argtypes = [P]
@@ -211,6 +215,18 @@ def default_config(**kw):
         else:
             setattr(c, k, v)
     return c
+
+
+def plan_batch_static(cfg, d_starts, d_goals, d_obstacles, q, m, dynamic, n_iter, query_base, d_out, stream=0):
+    """krrt_plan_batch_static: the batched planner without a context and without a single allocation — for a caller
+    inside a fixed-rate control cycle, or one whose device memory belongs to another allocator's pool (include/krrt.h).
+    Device pointers as ints (tensor.data_ptr()); asynchronous on `stream` (0 = the default stream).  At most
+    KRRT_STATIC_MAX_QUERIES queries of KRRT_STATIC_MAX_ITER iterations per call; calls share one scratch array per
+    device, so do not let two of them overlap on the GPU.  Make the first call per device during start-up."""
+    rc = lib().krrt_plan_batch_static(ctypes.byref(cfg), d_starts, d_goals, d_obstacles, int(q), int(m), int(dynamic),
+                                      int(n_iter), int(query_base), d_out, stream or None)
+    if rc != KRRT_OK:
+        raise KrrtError(rc, lib().krrt_last_error(None).decode())
 
 
 class Planner:

@@ -823,3 +823,4 @@ int krrt_scan_stats(krrt_ctx* ctx, double* visited_pairs, int64_t* rebuilds, int
 }  // extern "C"
 
 #include "krrt_capi_ops.inl"
+#include "krrt_capi_static.inl"
