@@ -101,26 +101,61 @@ def unpermute(gathered, q_total, world, chunk):
     return out
 
 
-def exchange_id(rank, world, tag=None, timeout=120.0):
-    """Rank 0 makes the NCCL id and leaves it in a file every rank of the box can read (one node: /tmp)."""
+def _launcher():
+    """(pid, start time in s since the epoch) of the process that started this rank — torchrun's agent, mpirun, a test.
+    All ranks of one launch share it and two launches do not, which MASTER_PORT and TORCHELASTIC_RUN_ID cannot say
+    (torchrun's defaults are 29500 and 'none' every time).  Start time None where /proc cannot tell."""
+    ppid = os.getppid()
+    try:
+        with open(f"/proc/{ppid}/stat") as f:
+            ticks = int(f.read().rsplit(")", 1)[1].split()[19])       # field 22: starttime in clock ticks since boot
+        with open("/proc/stat") as f:
+            btime = next(int(line.split()[1]) for line in f if line.startswith("btime"))
+        return ppid, btime + ticks / os.sysconf("SC_CLK_TCK")
+    except (OSError, ValueError, StopIteration, IndexError):
+        return ppid, None
+
+
+def _id_path(tag=None):
+    ppid, born = _launcher()
+    tag = tag or os.environ.get("KRRT_MGPU_JOB") or "{}_{}_{}_{}".format(
+        os.environ.get("MASTER_PORT", "0"), os.environ.get("TORCHELASTIC_RUN_ID", "x"), ppid,
+        int(born) if born is not None else "x")
+    return os.path.join(os.environ.get("KRRT_ID_DIR", "/tmp"), f"krrt_mgpu_id_{tag}.bin"), born
+
+
+def exchange_id(rank, world, tag=None, timeout=120.0, make_id=None):
+    """Rank 0 makes the NCCL id and leaves it in a file every rank of the box can read (one node: /tmp).
+
+    The file belongs to ONE job: its name carries the launcher's pid and start time (or KRRT_MGPU_JOB, a nonce the
+    launcher exports), rank 0 removes whatever is there under that name before it asks NCCL for a new id, readers take
+    only a file written after their launcher was started, and release_id() removes it once the communicator is up."""
     if world == 1:
         return None
-    tag = tag or "{}_{}".format(os.environ.get("MASTER_PORT", "0"), os.environ.get("TORCHELASTIC_RUN_ID", "x"))
-    path = os.path.join(os.environ.get("KRRT_ID_DIR", "/tmp"), f"krrt_mgpu_id_{tag}.bin")
+    path, born = _id_path(tag)
     if rank == 0:
-        buf = ctypes.create_string_buffer(ID_BYTES)
-        rc = lib().krrt_mgpu_unique_id(buf)
-        if rc != KRRT_OK:
-            raise KrrtError(rc, "krrt_mgpu_unique_id failed")
+        try:
+            os.unlink(path)                                     # (a crashed earlier job's: never ours)
+        except OSError:
+            pass
+        if make_id is None:
+            buf = ctypes.create_string_buffer(ID_BYTES)
+            rc = lib().krrt_mgpu_unique_id(buf)
+            if rc != KRRT_OK:
+                raise KrrtError(rc, "krrt_mgpu_unique_id failed")
+            raw = buf.raw
+        else:
+            raw = make_id()
         tmp = path + f".{os.getpid()}"
         with open(tmp, "wb") as f:
-            f.write(buf.raw)
+            f.write(raw)
         os.replace(tmp, path)
-        return buf.raw
+        return raw
     t0 = time.time()
+    not_before = born - 2.0 if born is not None else t0 - 600.0  # (2 s: /proc start times are in clock ticks, mtimes are not)
     while True:
         try:
-            if time.time() - os.path.getmtime(path) < 600:      # (a stale file of an earlier job is ignored)
+            if os.path.getmtime(path) >= not_before:
                 with open(path, "rb") as f:
                     data = f.read()
                 if len(data) == ID_BYTES:
@@ -130,6 +165,15 @@ def exchange_id(rank, world, tag=None, timeout=120.0):
         if time.time() - t0 > timeout:
             raise KrrtError(-1, f"no NCCL id at {path} after {timeout} s")
         time.sleep(0.01)
+
+
+def release_id(rank, world, tag=None):
+    """After the communicator exists on rank 0 (ncclCommInitRank is collective: every rank has read the id by then)."""
+    if world > 1 and rank == 0:
+        try:
+            os.unlink(_id_path(tag)[0])
+        except OSError:
+            pass
 
 
 class Sweep:
@@ -161,6 +205,7 @@ class Sweep:
         ident = exchange_id(rank, world)
         h = ctypes.c_void_p()
         rc = lib().krrt_mgpu_create_rank(ctypes.byref(cfg), rank, world, ident, ctypes.byref(h))
+        release_id(rank, world)
         if rc != KRRT_OK:
             raise KrrtError(rc, lib().krrt_mgpu_last_error(None).decode())
         return cls(h, cfg)

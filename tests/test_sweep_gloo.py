@@ -112,3 +112,60 @@ def test_mgpu_library_exports_every_declared_symbol():
     assert "nccl" not in ldd and "torch" not in ldd
     ldd = subprocess.run(["ldd", sweep.MGPU_LIB_PATH], capture_output=True, text=True).stdout
     assert "libnccl" in ldd and "libkrrt.so" in ldd and "torch" not in ldd
+
+
+# ---- the NCCL id hand-over of Sweep.from_env (sweep.exchange_id / release_id): one file per JOB ----------------------
+def _id_reader(rank, path_dir, q):
+    os.environ["KRRT_ID_DIR"] = path_dir
+    os.environ["MASTER_PORT"] = "29500"                     # torchrun's defaults: the same for every launch
+    os.environ.pop("TORCHELASTIC_RUN_ID", None)
+    q.put(sweep.exchange_id(rank + 1, 2, timeout=20.0))
+
+
+def test_nccl_id_file_belongs_to_one_job(tmp_path, monkeypatch):
+    """a second launch with the same MASTER_PORT / run id must not pick up the first launch's id"""
+    import multiprocessing
+    import time
+    monkeypatch.setenv("KRRT_ID_DIR", str(tmp_path))
+    monkeypatch.setenv("MASTER_PORT", "29500")
+    monkeypatch.delenv("TORCHELASTIC_RUN_ID", raising=False)
+    monkeypatch.delenv("KRRT_MGPU_JOB", raising=False)
+    ctx = multiprocessing.get_context("spawn")
+    for job in range(2):                                     # two jobs in a row from the same launcher (this process)
+        ident = bytes([job + 1]) * sweep.ID_BYTES
+        q = ctx.Queue()
+        p = ctx.Process(target=_id_reader, args=(0, str(tmp_path), q))
+        p.start()                                            # the reader is up first and polls, as non-zero ranks do
+        time.sleep(0.5)
+        # rank 0 of the job lives in a child too, so that its launcher is this process as well
+        w = ctx.Process(target=_id_writer, args=(str(tmp_path), ident))
+        w.start()
+        got = q.get(timeout=60)
+        p.join()
+        w.join()
+        assert got == ident, f"job {job}: the reader took another job's id"
+        assert not [f for f in os.listdir(tmp_path) if f.startswith("krrt_mgpu_id_")], "rank 0 leaves no id file behind"
+    # a file from before this launcher existed (a crashed job that used the same name) is not accepted
+    path, born = sweep._id_path()
+    assert born is not None and str(os.getppid()) in os.path.basename(path)
+    with open(path, "wb") as f:
+        f.write(b"\xee" * sweep.ID_BYTES)
+    os.utime(path, (born - 3600, born - 3600))
+    with pytest.raises(capi.KrrtError):
+        sweep.exchange_id(1, 2, timeout=0.3)
+    os.utime(path, None)                                     # written during this launch: accepted
+    assert sweep.exchange_id(1, 2, timeout=5.0) == b"\xee" * sweep.ID_BYTES
+    # another launch (another nonce) never sees it
+    monkeypatch.setenv("KRRT_MGPU_JOB", "job-b")
+    with pytest.raises(capi.KrrtError):
+        sweep.exchange_id(1, 2, timeout=0.3)
+
+
+def _id_writer(path_dir, ident):
+    os.environ["KRRT_ID_DIR"] = path_dir
+    os.environ["MASTER_PORT"] = "29500"
+    os.environ.pop("TORCHELASTIC_RUN_ID", None)
+    import time
+    assert sweep.exchange_id(0, 2, make_id=lambda: ident) == ident
+    time.sleep(1.0)                                          # (krrt_mgpu_create_rank: the ranks meet in ncclCommInitRank)
+    sweep.release_id(0, 2)
