@@ -567,6 +567,7 @@ static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double
       const size_t b_snap = rows * ITERLOG_STRIDE * sizeof(double), b_smp = it * 4 * sizeof(double), b_int = it * sizeof(int),
                    b_rec = it * sizeof(IterRec);
       CK(cudaMalloc((void**)&ctx->d_iterlog, 2 * b_snap + b_smp + b_rec + 2 * b_int));
+      CK(cudaMemsetAsync(ctx->d_iterlog, 0, 2 * b_snap + b_smp + b_rec + 2 * b_int, st));  // no log entry is ever an uninitialised index
       unsigned char* q = ctx->d_iterlog;
       ctx->ilog.snap_ctc = (double*)q; q += b_snap;
       ctx->ilog.snap_tim = (double*)q; q += b_snap;

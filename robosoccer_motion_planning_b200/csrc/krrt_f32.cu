@@ -598,6 +598,7 @@ static int grow_body(Tree* t, const krrt_io_real* goal, int n_iter, const krrt_i
       const size_t b_snap = rows * F32_LOG_STRIDE * sizeof(double), b_smp = it * 4 * sizeof(double), b_int = it * sizeof(int),
                    b_rec = (it * sizeof(IterRec) + 15) / 16 * 16;
       TCK(cudaMalloc((void**)&t->d_iterlog, 2 * b_snap + b_smp + b_rec + 2 * b_int));
+      TCK(cudaMemsetAsync(t->d_iterlog, 0, 2 * b_snap + b_smp + b_rec + 2 * b_int, st));  // no log entry is ever an uninitialised index
       unsigned char* q = t->d_iterlog;
       t->ilog.snap_ctc = (double*)q; q += b_snap;
       t->ilog.snap_tim = (double*)q; q += b_snap;

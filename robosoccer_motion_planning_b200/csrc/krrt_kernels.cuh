@@ -323,9 +323,23 @@ __global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Param
   __shared__ int s_i[GLOG_THREADS / 32];
   const int t = threadIdx.x, it = blockIdx.x;
   if (it >= n_iter) return;
-  const int n = L.n_after[it];
-  const int row = L.snap_of[it];
-  const int n_prev = it > 0 ? L.n_after[it - 1] : n_before;
+  // the call ends at the iteration that finds the tree full, and the log ends with it: an iteration behind that one
+  // repeats its record (include/krrt.h) instead of reading log entries nobody wrote
+  const long long ran = ctl->iter - ctl->iter_begin;
+  const int done = (int)(ran < 0 ? 0 : (ran > n_iter ? n_iter : ran));
+  if (done == 0) {  // (a call that stopped with an error before its first iteration: the tree as it was)
+    if (t == 0) {
+      IterRec r;
+      r.n_nodes = n_before; r.solved = 0; r.goal_index = -1; r.inserted = 0; r.goal_cost = KR(0.0);
+      for (int k = 0; k < 4; ++k) r.sample[k] = KR(0.0);
+      out[it] = r;
+    }
+    return;
+  }
+  const int src = it < done ? it : done - 1;
+  const int n = L.n_after[src];
+  const int row = L.snap_of[src];
+  const int n_prev = it >= done ? n : (it > 0 ? L.n_after[it - 1] : n_before);
   const double* ctc = L.snap_ctc + (size_t)row * L.stride;
   const double* tim = L.snap_tim + (size_t)row * L.stride;
   for (int j = t; j < P.m; j += GLOG_THREADS) s_obs[j] = P.obs[j];
@@ -387,7 +401,7 @@ __global__ void __launch_bounds__(GLOG_THREADS) k_goal_log(const Ctl* ctl, Param
         r.goal_index = node_is_goal ? bi : n;
         r.goal_cost = bc;
       }
-      for (int k = 0; k < 4; ++k) r.sample[k] = L.sample[4 * (size_t)it + k];
+      for (int k = 0; k < 4; ++k) r.sample[k] = L.sample[4 * (size_t)src + k];
       out[it] = r;
     }
   }

@@ -285,6 +285,29 @@ def test_f32_grow_logged_equals_single_calls(gpu_required):
 
 
 @pytest.mark.gpu
+def test_f32_grow_logged_on_a_tree_that_fills_up(gpu_required):
+    """binary32: the iteration that finds the tree full ends the logged call with a record of its own; the iterations
+    behind it repeat that record (include/krrt.h) — no stale or unwritten log entry shows through"""
+    from robosoccer_motion_planning_b200 import scenes
+    G, O = _pair32(1, 40, p_direct=0.3)
+    rec, solved, gi = G.grow_logged(scenes.GOAL, 120)
+    n_prev = O.size
+    for i in range(120):
+        so, go = O.grow(scenes.GOAL, 1)
+        if O.size == 40 and n_prev == 40:
+            break
+        assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i])) == (so, go, O.size), i
+        n_prev = O.size
+    assert G.size == 40 and G.grow_done() == (i + 1, True) and 0 < i < 119
+    assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i]), int(rec["inserted"][i])) == (so, go, 40, 0)
+    for j in range(i + 1, 120):
+        for f in ("n_nodes", "solved", "goal_index", "inserted", "goal_cost"):
+            assert rec[f][j] == rec[f][i], (j, f)
+        assert np.array_equal(rec["sample"][j], rec["sample"][i]), j
+    G.close()
+
+
+@pytest.mark.gpu
 def test_f32_tree_edges_and_trajectory(gpu_required):
     """tree.trajectories (robosoccer_visual.hpp:18) and the fine re-solve of the found path (…node.cpp:232-249) on a binary32 tree."""
     from robosoccer_motion_planning_b200 import scenes

@@ -746,3 +746,18 @@ def test_grow_logged_edge_cases(gpu_required):
         assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i])) == (so, go, O.size), i
         n_prev = O.size
     assert G.size == 40 and G.grow_done()[1]
+    # iteration i is the one that found the tree full: it ends the call, and it is a record of its own (so, go: the full tree's)
+    assert 0 < i < 119 and G.grow_done()[0] == i + 1
+    assert (bool(rec["solved"][i]), int(rec["goal_index"][i]), int(rec["n_nodes"][i]), int(rec["inserted"][i])) == (so, go, 40, 0)
+    # the iterations behind it were never run: each repeats that record (include/krrt.h), none shows stale or unwritten log entries
+    for j in range(i + 1, 120):
+        for f in ("n_nodes", "solved", "goal_index", "inserted", "goal_cost"):
+            assert rec[f][j] == rec[f][i], (j, f)
+        assert np.array_equal(rec["sample"][j], rec["sample"][i]), j
+    # a second logged call on the full tree: its first iteration finds the tree full, the rest repeat it
+    rec2, solved2, gi2 = G.grow_logged(scenes.GOAL, 9)
+    so, go = O.grow(scenes.GOAL, 1)
+    assert G.grow_done()[0] == 1 and (bool(solved2), gi2) == (so, go)
+    for j in range(9):
+        assert (bool(rec2["solved"][j]), int(rec2["goal_index"][j]), int(rec2["n_nodes"][j]), int(rec2["inserted"][j])) == (so, go, 40, 0), j
+        assert np.array_equal(rec2["sample"][j], rec2["sample"][0])
