@@ -397,6 +397,7 @@ class SoccerEnv {
   void upload(krrt::Session& s) {
     static_assert(sizeof(std::array<double, 4>) == 4 * sizeof(double), "obstacle layout");
     if (s.obstacle_owner == this && s.obstacle_version == version_) return;
+    s.settings_change();  // (the iterations run ahead saw the discs that are resident now; a cycle under way stops running ahead)
     s.config().R = collision_radius;
     s.check(krrt_set_obstacles(s.ctx(), obs.empty() ? nullptr : obs[0].data(), (int)obs.size(), Dynamic ? 1 : 0));
     s.obstacle_owner = this;

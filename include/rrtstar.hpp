@@ -51,7 +51,9 @@ struct Error : std::runtime_error {
 // sample or none); on a mismatch, or when the tree is read while the device is ahead of the caller, the device tree is
 // rebuilt at the caller's iteration by replaying the cycle from its start (same samples -> the same tree, bit for bit).
 // What the caller sees is therefore exactly what one device call per iteration gives (tests/native/host_surface_check.cpp
-// runs the node's loop against the CPU checker call by call).  KRRT_RUN_AHEAD=0 in the environment switches it off.
+// runs the node's loop against the CPU checker call by call).  A replay uses the settings that are live, so a cycle whose
+// obstacles or parameters change after its first iteration stops running ahead (RunAhead::frozen) until the next setStart.
+// KRRT_RUN_AHEAD=0 in the environment switches it off.
 struct RunAhead {
   struct Forced { long at; double x[4]; };
   struct GoalSeg { long from; bool has; double g[4]; };
@@ -65,6 +67,11 @@ struct RunAhead {
   long last_len = 0;                  // iterations of the cycle before
   std::vector<long> last_goal_forced_at, goal_forced_at;  // where the caller forced the goal as the sample (before / now)
   long replays = 0, device_calls = 0;  // diagnostics
+  // The cycle's settings (discs, r, R, radius schedule, sampler) changed after its first iteration.  A replay rebuilds the
+  // cycle from its start with the settings that are live NOW, so it would redo the earlier iterations with settings they
+  // never saw.  For the rest of such a cycle nothing is run ahead — one iteration per device call, the device tree is
+  // always the caller's tree and nothing is ever replayed.  The next setStart lifts it.
+  bool frozen = false;
 
   const Forced* forced_at(long i) const {
     for (const Forced& f : forced)
@@ -116,7 +123,7 @@ class Session {
       live_ = cfg_;
       ++epoch_;
     } else if (std::memcmp(&cfg_, &live_, sizeof(cfg_)) != 0) {
-      sync_tree();  // iterations run ahead were run with the settings that are live now: settle the tree before they change
+      settings_change();  // iterations run ahead were run with the settings that are live now: settle the tree before they change
       check(krrt_set_params(ctx_, &cfg_));
       live_ = cfg_;
     }
@@ -134,7 +141,14 @@ class Session {
     ra_.goals.clear();
     ra_.goal_forced_at.clear();
     ra_.served = ra_.ahead = 0;
+    ra_.frozen = false;
     std::memcpy(ra_.start, x0, sizeof(ra_.start));
+  }
+  // about to change what the tree is grown with (krrt_set_params, krrt_set_obstacles): the device tree goes back to the
+  // caller's iteration while the old settings are still live, and a cycle that is already under way stops running ahead
+  void settings_change() {
+    sync_tree();
+    if (started && ra_.served > 0) ra_.frozen = true;
   }
   // the device tree at the caller's iteration: anything that reads the tree, or changes what it is grown with, calls this first
   void sync_tree() {
@@ -260,6 +274,7 @@ class RRTStar {
       long L = ra.last_len > i ? ra.last_len - i : (i < 1 ? 1 : (i < 64 ? i : 64));
       if (L > 256) L = 256;
       if (n_now + L > 1024) L = 1024 - n_now;
+      if (ra.frozen && L > 1) L = 1;  // (settings changed mid-cycle: no replay could be exact any more, so nothing is run ahead)
       std::vector<krrt_iter_record> recs;
       int solved = 0, gi = -1, rc = KRRT_ERR_UNSUPPORTED;
       if (L >= 1) {

@@ -215,7 +215,10 @@ int main(int argc, char** argv) {
     if (target_size >= 60) {
       auto& rr = Kinodynamic::Wrapper::get_rrtstar_int2d();
       krrt::RunAhead& ra = Kinodynamic::Wrapper::get_session().run_ahead();
-      auto run_cycle = [&](int iters, int read_at, int goal_change_at, int force_at) {
+      // (change_at: the obstacles move at that iteration of the cycle — env.setObstacles in the middle of the loop)
+      std::vector<ObState> moved = obstacles;
+      for (auto& o : moved) { o[0] += 0.6; o[1] -= 0.9; }
+      auto run_cycle = [&](int iters, int read_at, int goal_change_at, int force_at, int change_at = -1) {
         rr.setStart(start);
         rr.setIteration(0);
         env.setObstacles(obstacles);
@@ -228,6 +231,10 @@ int main(int argc, char** argv) {
           if (i == goal_change_at) {
             g(0) = 6.0;
             g(1) = 2.5;
+          }
+          if (i == change_at) {
+            env.setObstacles(moved);
+            ko_set_obstacles(oracle, moved[0].data(), 9, 0);
           }
           if (i == force_at) {
             Kinodynamic::TreeInt2D::State x;
@@ -274,7 +281,17 @@ int main(int argc, char** argv) {
       run_cycle((int)target_size, 7, 20, 31);
       run_cycle(N / 2, -1, -1, -1);
       run_cycle(N / 2, 3, -1, 5);
-      std::printf("run-ahead: %ld device calls, %ld replays over 5 cycles\n", ra.device_calls, ra.replays);
+      // obstacles that change in the middle of a cycle: the iterations before the change keep the tree they built with the old
+      // discs whatever happens later — a tree read-out, a forced sample nobody assumed, another goal (each used to replay the
+      // WHOLE cycle with the new discs)
+      run_cycle(N, 45, 50, 55, 30);  // (the CPU checker's tree after 45 iterations with the moved discs throughout differs: 26 nodes against 20)
+      if (ra.enabled) EXPECT(ra.frozen);
+      const long c1 = ra.device_calls, r1 = ra.replays;
+      run_cycle(N, -1, -1, -1);           // the next cycle runs ahead again
+      if (ra.enabled) EXPECT(!ra.frozen && ra.replays - r1 <= 2 && ra.device_calls - c1 <= 8);
+      run_cycle(N, 5, -1, -1, 1);
+      run_cycle(N, -1, -1, -1);
+      std::printf("run-ahead: %ld device calls, %ld replays over 9 cycles\n", ra.device_calls, ra.replays);
     }
     ko_destroy(oracle);
     std::printf("%s: %s, %zu nodes, goalIndex %d, %d check failure(s)\n", dynamic ? "dynamic" : "static",
