@@ -114,10 +114,12 @@ __device__ __noinline__ int warp_goal_connect(const Tree T, int n, const State4 
   return n;
 }
 
-// every lane's stores of the record are ordered before the counter (fence by each writing lane, then one atomic)
+// every lane's stores of the record are ordered before the counter (fence by each writing lane, then one atomic).
+// System scope: the consumer that waits on the counter ships the records with an NCCL gather, whose readers can be
+// copy engines and peer GPUs (symmetric windows), not only this device's SMs.  Once per query.
 __device__ __forceinline__ void batch_query_done(const BatchJob& J, int qi) {
   if (!J.chunk_done) return;
-  __threadfence();
+  __threadfence_system();
   __syncwarp();
   if ((threadIdx.x & 31) == 0) atomicAdd(&J.chunk_done[qi / J.chunk_queries], 1u);
 }

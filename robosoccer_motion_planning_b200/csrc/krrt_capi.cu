@@ -106,8 +106,9 @@ struct krrt_ctx {
       return (code);             \
     }                            \
   } while (0)
-// entry points that exist in binary64 only: the logged call, the tree-walking read-outs beyond states / path, the diagnostics
-// (a KRRT_F32 context serves the planner proper, the batched planner and the stateless operators: krrt_f32.cu)
+// entry points that exist in binary64 only: the development diagnostics (phase timers, sub-round statistics, scan statistics).
+// A KRRT_F32 context serves everything else — the planner proper incl. the logged call, the tree read-outs, the batched
+// planner and the stateless operators (krrt_f32.cu)
 #define F64_ONLY()                                                                                                    \
   REQUIRE(ctx->cfg.precision == KRRT_F64, KRRT_ERR_UNSUPPORTED,                                                       \
           "not available on a KRRT_F32 context (the development diagnostics are binary64 only)")
@@ -186,7 +187,10 @@ int krrt_device_count(void) {
 
 const char* krrt_last_error(const krrt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
-int64_t krrt_launch_count(const krrt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+// (a KRRT_F32 context's single-tree kernels are counted where they are launched: krrt_f32.cu's Tree)
+int64_t krrt_launch_count(const krrt_ctx* ctx) {
+  return ctx ? ctx->launches + (ctx->f32 ? krrt_f32_api::tree_launches(ctx->f32) : 0) : 0;
+}
 
 void krrt_destroy(krrt_ctx* ctx) {
   if (!ctx) return;
@@ -511,7 +515,6 @@ int krrt_grow_logged(krrt_ctx* ctx, const double* goal, int n_iter, const double
     double ms32 = 0.0;
     krrt_f32_api::tree_grow_done(ctx->f32, nullptr, nullptr, &ms32);
     ctx->last_total_ms = ms32;
-    ctx->launches += 4;
     if (rc32 != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
     return rc32;
   }
@@ -530,7 +533,6 @@ static int grow_impl(krrt_ctx* ctx, const double* goal, int n_iter, const double
     double ms32 = 0.0;
     krrt_f32_api::tree_grow_done(ctx->f32, nullptr, nullptr, &ms32);
     ctx->last_total_ms = ms32;
-    ctx->launches += 3;
     if (rc32 != KRRT_OK) ctx->err = krrt_f32_api::tree_error(ctx->f32);
     return rc32;
   }

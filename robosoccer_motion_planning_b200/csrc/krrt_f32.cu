@@ -5,8 +5,10 @@
 // and collision tests; results widen to the binary64 records of the C ABI.  Checked bit for bit against the CPU
 // checker's float build and within 1e-4 against the binary64 planner on costs and
 // arrival times of identical edges (tests/test_f32.py).
-// The single-tree planner (k_grow) exists in binary64 only: it is bound by the latency of its commit chain, not by
-// arithmetic, and krrt_grow on a KRRT_F32 context returns KRRT_ERR_UNSUPPORTED.
+// The single-tree planner too: k_grow and the kernels around it (krrt_grow.cuh, krrt_kernels.cuh) are compiled in float
+// from the same source further down, with a small runtime of their own (Tree: arena, stream, control block, logged
+// calls, read-outs); krrt_capi.cu forwards the entry points of a KRRT_F32 context here.  Only the development
+// diagnostics (phase timers, sub-round and scan statistics) stay binary64.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -299,6 +301,8 @@ struct Tree {
   IterLog ilog = {nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
   IterRec* d_iterrec = nullptr;
   int wave_min_n = 32;
+  int* d_near = nullptr;     // tree_near: [count, nearest, d2, pad] + the index list; grows, never shrinks
+  size_t near_cap = 0;       // ints
   int64_t launches = 0, last_iters = 0;
   int last_full = 0;
   float last_ms = 0.f;
@@ -479,6 +483,7 @@ void tree_destroy(Tree* t) {
   if (t->arena) cudaFree(t->arena);
   if (t->d_user) cudaFree(t->d_user);
   if (t->d_scr) cudaFree(t->d_scr);
+  if (t->d_near) cudaFree(t->d_near);
   if (t->d_iterlog) cudaFree(t->d_iterlog);
   if (t->h_ctl) cudaFreeHost(t->h_ctl);
   if (t->ev0) cudaEventDestroy(t->ev0);
@@ -704,8 +709,15 @@ int tree_near(Tree* t, const krrt_io_real x[4], krrt_io_real radius2, int32_t* i
   Ctl h;
   int rc = fetch(t, &h);
   if (rc != KRRT_OK) return rc;
-  int* d_buf = nullptr;  // [count, nearest, d2 (float), pad] + the index list
-  TCK(cudaMalloc((void**)&d_buf, sizeof(int) * (4 + (size_t)std::max(cap, 1))));
+  const size_t need = 4 + (size_t)std::max(cap, 1);  // [count, nearest, d2 (float), pad] + the index list
+  if (t->near_cap < need) {
+    if (t->d_near) TCK(cudaFree(t->d_near));
+    t->d_near = nullptr;
+    t->near_cap = 0;
+    TCK(cudaMalloc((void**)&t->d_near, sizeof(int) * need));
+    t->near_cap = need;
+  }
+  int* d_buf = t->d_near;
   const State4 s = {(double)x[0], (double)x[1], (double)x[2], (double)x[3]};
   k_near_query<<<1, 1024, 0, t->st>>>(t->T, h.n, s, (double)radius2, d_buf + 4, cap, d_buf, d_buf + 1, (double*)(d_buf + 2));
   t->launches++;
@@ -714,7 +726,6 @@ int tree_near(Tree* t, const krrt_io_real x[4], krrt_io_real radius2, int32_t* i
   if (e == cudaSuccess) e = cudaStreamSynchronize(t->st);
   const int got = e == cudaSuccess ? std::min(r.cnt, cap) : 0;
   if (e == cudaSuccess && got > 0) e = cudaMemcpy(idx, d_buf + 4, sizeof(int) * (size_t)got, cudaMemcpyDeviceToHost);
-  cudaFree(d_buf);
   TCK(e);
   if (count) *count = r.cnt;
   if (nearest) *nearest = r.nearest;

@@ -94,6 +94,24 @@ struct krrt_mgpu {
     }                             \
   } while (0)
 
+// One NCCL group over the local GPUs.  The group is closed on EVERY path: an error inside it is reported after
+// ncclGroupEnd, so no later NCCL call of this thread (krrt_mgpu_destroy's ncclCommDestroy included) runs inside a group
+// that was left open.  per_dev(Dev&) -> KRRT_OK or a status with mg->err set (MCK / NCK inside it return from the lambda).
+template <typename F>
+static int nccl_group(krrt_mgpu* mg, F&& per_dev) {
+  NCK(ncclGroupStart());
+  int rc = KRRT_OK;
+  for (Dev& d : mg->devs)
+    if ((rc = per_dev(d)) != KRRT_OK) break;
+  const ncclResult_t e = ncclGroupEnd();
+  if (rc != KRRT_OK) return rc;  // (mg->err is the first failure's)
+  if (e != ncclSuccess) {
+    mg->err = std::string("ncclGroupEnd: ") + ncclGetErrorString(e);
+    return KRRT_ERR_CUDA;
+  }
+  return KRRT_OK;
+}
+
 static const size_t ITEM = sizeof(krrt_result);
 
 extern "C" {
@@ -213,12 +231,12 @@ static int init_devices(krrt_mgpu* mg, const ncclUniqueId* id) {
 #if NCCL_VERSION_CODE >= 22800
     if (v >= 22800 && !std::getenv("KRRT_SWEEP_NO_CE")) conf.CTAPolicy = NCCL_CTA_POLICY_ZERO;
 #endif
-    NCK(ncclGroupStart());
-    for (Dev& d : mg->devs) {
+    const int grc = nccl_group(mg, [&](Dev& d) -> int {
       MCK(cudaSetDevice(d.device));
       NCK(ncclCommInitRankConfig(&d.comm, mg->world, *id, d.rank, &conf));
-    }
-    NCK(ncclGroupEnd());
+      return KRRT_OK;
+    });
+    if (grc != KRRT_OK) return grc;
   }
   return KRRT_OK;
 }
@@ -473,13 +491,13 @@ int krrt_sweep_run(krrt_mgpu* mg, int dynamic, int n_iter, uint32_t query_base, 
           }
         }
       }
-      NCK(ncclGroupStart());
-      for (Dev& d : mg->devs) {
+      const int grc = nccl_group(mg, [&](Dev& d) -> int {
         MCK(cudaSetDevice(d.device));
         NCK(ncclAllGather(d.d_out + (size_t)c0 * ITEM, d.d_all + (size_t)c0 * W * ITEM, (size_t)cc * ITEM, ncclChar, d.comm,
                           d.s_xfer));
-      }
-      NCK(ncclGroupEnd());
+        return KRRT_OK;
+      });
+      if (grc != KRRT_OK) return grc;
     }
     for (Dev& d : mg->devs) {
       MCK(cudaSetDevice(d.device));
@@ -556,12 +574,12 @@ static int reduce_small(krrt_mgpu* mg, double* x, int n, ncclRedOp_t op) {
     MCK(cudaSetDevice(d.device));
     MCK(cudaMemcpyAsync(d.d_red, x + (size_t)g * n, sizeof(double) * n, cudaMemcpyHostToDevice, d.s_plan));
   }
-  NCK(ncclGroupStart());
-  for (Dev& d : mg->devs) {
+  const int grc = nccl_group(mg, [&](Dev& d) -> int {
     MCK(cudaSetDevice(d.device));
     NCK(ncclAllReduce(d.d_red, d.d_red, n, ncclDouble, op, d.comm, d.s_plan));
-  }
-  NCK(ncclGroupEnd());
+    return KRRT_OK;
+  });
+  if (grc != KRRT_OK) return grc;
   Dev& d0 = mg->devs[0];
   MCK(cudaSetDevice(d0.device));
   MCK(cudaMemcpyAsync(x, d0.d_red, sizeof(double) * n, cudaMemcpyDeviceToHost, d0.s_plan));

@@ -339,15 +339,20 @@ def test_f32_near_query(gpu_required):
     """krrt_near on a binary32 tree: indices, nearest node and its squared distance are the float checker's."""
     from robosoccer_motion_planning_b200 import scenes
     G, O = _pair32(0, 8192)
+    l0 = G.launch_count
     for P in (G, O):
         P.grow(None, 4000)
+    # krrt_launch_count on a binary32 tree is the tree's own counter: k_begin_grow, k_grow and the goal kernel of this call
+    assert G.launch_count - l0 == 3
     rng = np.random.default_rng(4)
     for k in range(20):
         x = rng.uniform(scenes.FIELD_LO, scenes.FIELD_HI, 4)
         r2 = [0.0, 0.3, 1.0, 9.0, 400.0][k % 5]
-        gi, gn, gd = G.near(x, r2, cap=8192)
+        cap = 8192 if k % 2 == 0 else 64                  # (the query's device buffer is kept between calls and only grows)
+        gi, gn, gd = G.near(x, r2, cap=cap)
         oi, on, od = O.near(x, r2, cap=8192)
-        assert np.array_equal(gi, oi) and gn == on and gd == od, k
+        assert np.array_equal(gi, oi[:cap]) and gn == on and gd == od, k
+    assert G.launch_count - l0 == 3 + 20                  # one k_near_query per query
     s = O.tree()[0][123]
     gi, gn, gd = G.near(s, 0.0)
     assert list(gi) == [123] and gn == 123 and gd == 0.0
