@@ -176,8 +176,9 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "replicas": n, "note": "CPU oracle port; the reference's RRT* sources "
-                   "(submodule alifahrri/motion_planning@3b3183e) are absent, nothing of it builds"},
+        "config": bench_config(n),
+        "note": "CPU oracle port; the reference's RRT* sources (submodule alifahrri/motion_planning@3b3183e) are absent, "
+                "nothing of it builds",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{args.steps} full plans x {n} replica(s), {N_ITER} iterations each, kd-tree near search"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -186,6 +187,15 @@ def run_reference(args, rank, world):
         "solved": int(out["solved"].sum()),
     }
     emit(line)
+
+
+def bench_config(replicas):
+    """`config` of BOTH arms, key for key (the driver compares them): what is planned, how often, and how the timed steps
+    are kept honest."""
+    return {"workload": WORKLOAD, "replicas": int(replicas),
+            "l2": "GPU arm: flushed between timed steps (write of 2 x L2); CPU arm: not applicable",
+            "parallelism": "replicas only (single tree; every rank grows the same plan, same seed); "
+                           "batched queries shard by contiguous blocks"}
 
 
 # ---------------------------------------------------------------------------------------------------- our arm
@@ -380,14 +390,12 @@ def run_ours(args, rank, world, local_rank):
         sweep_line["records_sha256"] = hashlib.sha256(recs.tobytes()).hexdigest()
         sweep_line["solved_frac"] = float((recs["solved"] != 0).mean())
         import oracle_binding as ob
-        pick = np.arange(0, SWEEP_Q, SWEEP_Q // 512)          # 512 queries spread over every rank's block
+        # EVERY record against the CPU checker (all host cores; ~2 s for 65536 plans of 200 iterations) — outside any timed region
         cfgo = ob.default_config(p_direct=P_DIRECT)
-        okp = True
-        for i in pick:
-            ref1 = ob.plan_batch(cfgo, sw_s[i:i + 1], sw_g[i:i + 1], sw_o[i:i + 1], 1, BATCH_ITERS, query_base=int(i))
-            okp = okp and ref1.tobytes() == recs[i:i + 1].tobytes()
-        sweep_line["parity_vs_oracle"] = {"sample": "512 of the 65536 gathered records (every 128th query)",
-                                          "result": "bit-exact" if okp else "MISMATCH"}
+        ref_all = ob.plan_batch(cfgo, sw_s, sw_g, sw_o, 1, BATCH_ITERS, query_base=0, nthreads=os.cpu_count() or 1)
+        bad = int((ref_all.view(np.uint8).reshape(SWEEP_Q, -1) != recs.view(np.uint8).reshape(SWEEP_Q, -1)).any(axis=1).sum())
+        sweep_line["parity_vs_oracle"] = {"sample": f"all {SWEEP_Q} gathered records",
+                                          "result": "bit-exact" if bad == 0 else f"MISMATCH in {bad} records"}
     if world > 1:
         # the same sweep on ONE GPU, timed in the same run (rank 0; the others wait at the barrier): strong-scaling efficiency
         t1 = 0.0
@@ -430,9 +438,7 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "replicas": world, "window": int(G.cfg.batch),
-                   "l2": "flushed between timed steps (write of 2 x L2)", "parallelism": "replicas only (single tree; every rank grows the same plan, same seed); "
-                   "batched queries shard by contiguous blocks"},
+        "config": bench_config(world),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(launches),
@@ -512,7 +518,7 @@ def run_ours(args, rank, world, local_rank):
                          "peak": f32_peak, "unit": "TFLOP/s", "frac": f_tflops / f32_peak,
                          "peak_source": "measured (profiles/r1_fp_peak.json, FMA-chain microbenchmark)"}}
         # the C5 sweep (65536 queries, this GPU alone) in fp32: 28 rounds of the resident warps hide the tail that the 1.4 rounds of
-        # C4 expose, so this is what the float kernel sustains; a 256-record sample against the float checker
+        # C4 expose, so this is what the float kernel sustains; every record against the float checker
         S32.load(sw_s, sw_g, sw_o)
         S32.run(1, BATCH_ITERS)
         f5_ms = 0.0
@@ -520,16 +526,15 @@ def run_ours(args, rank, world, local_rank):
             flush_l2()
             f5_ms += S32.run(1, BATCH_ITERS)
         rec5 = S32.results()
-        pick5 = np.arange(0, SWEEP_Q, SWEEP_Q // 256)
-        ref5 = np.concatenate([of.plan_batch(of.default_config(p_direct=P_DIRECT), sw_s[i:i + 1], sw_g[i:i + 1], sw_o[i:i + 1], 1,
-                                             BATCH_ITERS, query_base=int(i), nthreads=1) for i in pick5])
+        ref5 = of.plan_batch(of.default_config(p_direct=P_DIRECT), sw_s, sw_g, sw_o, 1, BATCH_ITERS, query_base=0,
+                             nthreads=os.cpu_count() or 1)       # every record, all host cores, outside the timed region
+        bad5 = int((rec5.view(np.uint8).reshape(SWEEP_Q, -1) != ref5.view(np.uint8).reshape(SWEEP_Q, -1)).any(axis=1).sum())
         line["batched_f32"]["sweep_c5_one_gpu"] = {
             "workload": f"{SWEEP_Q} queries x {BATCH_ITERS} iterations on one GPU, KRRT_F32 context",
             "queries_per_sec": SWEEP_Q * 2 / (f5_ms * 1e-3), "ms_per_sweep": f5_ms / 2,
             "speedup_over_f64_one_gpu_sweep": ((s_ms / 3) / (f5_ms / 2)) if world == 1 else None,
-            "parity_vs_float_checker": {"sample": "256 of the 65536 records (every 256th query)",
-                                        "result": "bit-exact" if np.array_equal(rec5[pick5].view(np.uint8), ref5.view(np.uint8))
-                                        else "MISMATCH"}}
+            "parity_vs_float_checker": {"sample": f"all {SWEEP_Q} records",
+                                        "result": "bit-exact" if bad5 == 0 else f"MISMATCH in {bad5} records"}}
         S32.close()
         # ... and the headline plan on a KRRT_F32 context (k_grow compiled in float), against the float checker
         G32 = capi.Planner(device=local_rank, capacity=N_ITER + 2, p_direct=P_DIRECT, precision=capi.KRRT_F32)
