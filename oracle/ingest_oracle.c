@@ -1,4 +1,4 @@
-/* ingest_oracle.c — see ingest_oracle.h (TEST INFRASTRUCTURE ONLY; PARITY UNPINNED; CPU restatement of
+/* ingest_oracle.c — see ingest_oracle.h (TEST INFRASTRUCTURE ONLY; parity pinned by oracle/_ref/libingest_ref.so; CPU restatement of
  * robotsubscriber.cpp:29-77). */
 #include "ingest_oracle.h"
 

@@ -3,9 +3,11 @@
  * Follows RobotSubscriber::callback (robotsubscriber.cpp:44-77), ::rival_callback (robotsubscriber.cpp:29-42) and
  * ::getObstacles (robotsubscriber.h:50-55) of /root/reference/src/robosoccer_motion_planning; field types from
  * gazebo_visual/src/nubot_common/msgs/RobotInfo.msg:2,9-12 (int32 AgentID, float32 Point2d pos / vtrans, float32 heading).
- * PARITY UNPINNED: the reference source for this piece IS present (and is restated line by line here) but needs ROS to
- * compile and no reference test or fixture covers it; the restatement is checked against hand-computed known answers
- * in tests/test_ingest.py only. */
+ * PARITY PINNED: the reference source for this piece compiles here — robotsubscriber.cpp where it lies, against the ROS
+ * stand-ins of tests/native/ros_stub (oracle/Makefile target `ref` -> oracle/_ref/libingest_ref.so, wrapper
+ * oracle/ref_wrap/ingest_ref_wrap.cpp) — and this restatement equals it bit for bit on frames with missing and repeated
+ * own entries, no friends, no rivals (tests/test_ingest.py: test_restatement_equals_reference_subscriber); the CUDA kernel
+ * is held against the same library on the GPU box (test_gpu_ingest_equals_reference_subscriber). */
 #ifndef INGEST_ORACLE_H
 #define INGEST_ORACLE_H
 #include <stdint.h>

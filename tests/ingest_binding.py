@@ -1,4 +1,5 @@
-"""ctypes binding of the obstacle-ingest checker (oracle/ingest_oracle.c).  Test infrastructure only."""
+"""ctypes binding of the obstacle-ingest checker (oracle/ingest_oracle.c) and of oracle/_ref/libingest_ref.so — the
+REFERENCE's own robotsubscriber.cpp compiled where it lies (oracle/ref_wrap/ingest_ref_wrap.cpp).  Test infrastructure only."""
 import ctypes
 import os
 import subprocess
@@ -26,7 +27,36 @@ def _lib():
     return _fn
 
 
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libingest_ref.so")
+_ref_fn = None
+
+
+def have_ref():
+    """built in the build container (where /root/reference is mounted); the .so travels to the GPU box"""
+    if not os.path.exists(REF_SO) and os.path.isdir("/root/reference/src/robosoccer_motion_planning/src"):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s", "ref"])
+    return os.path.exists(REF_SO)
+
+
+def _ref():
+    global _ref_fn
+    if _ref_fn is None:
+        _ref_fn = ctypes.CDLL(REF_SO).ingest_ref_vision
+        _ref_fn.argtypes = [F, I, ctypes.c_int, F, ctypes.c_int, I, ctypes.c_int, D, D, I, D, I]
+        _ref_fn.restype = ctypes.c_int
+    return _ref_fn
+
+
+def reference_ingest(team, agent_id, rival, self_id):
+    """the reference's RobotSubscriber fed with the same frames (one fresh subscriber per frame)"""
+    return _ingest(_ref(), team, agent_id, rival, self_id)
+
+
 def oracle_ingest(team, agent_id, rival, self_id):
+    return _ingest(_lib(), team, agent_id, rival, self_id)
+
+
+def _ingest(fn, team, agent_id, rival, self_id):
     team = np.ascontiguousarray(team, dtype=np.float32)
     rival = np.ascontiguousarray(rival, dtype=np.float32)
     agent_id = np.ascontiguousarray(agent_id, dtype=np.int32)
@@ -36,9 +66,10 @@ def oracle_ingest(team, agent_id, rival, self_id):
     n_rival = rival.shape[1] if rival.ndim == 3 else 0
     out = {"self_state": np.zeros((f, 4)), "heading": np.zeros(f), "self_index": np.zeros(f, dtype=np.int32),
            "obstacles": np.zeros((f, n_team + n_rival, 4)), "n_obs": np.zeros(f, dtype=np.int32)}
-    _lib()(team.ctypes.data_as(F), agent_id.ctypes.data_as(I), n_team, rival.ctypes.data_as(F), n_rival,
+    rc = fn(team.ctypes.data_as(F), agent_id.ctypes.data_as(I), n_team, rival.ctypes.data_as(F), n_rival,
            self_id.ctypes.data_as(I), f, out["self_state"].ctypes.data_as(D), out["heading"].ctypes.data_as(D),
            out["self_index"].ctypes.data_as(I), out["obstacles"].ctypes.data_as(D), out["n_obs"].ctypes.data_as(I))
+    assert not rc, rc
     return out
 
 

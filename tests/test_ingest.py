@@ -97,3 +97,58 @@ def test_gpu_ingest_feeds_batched_planner(gpu_required):
                         np.ascontiguousarray(ref_in["obstacles"][:, :9]), 1, 60, nthreads=4)
     assert np.array_equal(out.view(np.uint8), ref.view(np.uint8))
     G.close()
+
+
+# ---- pinned against the REFERENCE's own code: robotsubscriber.cpp compiled where it lies (oracle/_ref/libingest_ref.so) ----
+REF_SHAPES = [(1, 5, 5), (1000, 5, 5), (257, 1, 0), (64, 0, 3), (512, 11, 11), (3, 2, 60)]
+
+
+def _need_ref():
+    if not ib.have_ref():
+        pytest.skip("oracle/_ref/libingest_ref.so is built where /root/reference is mounted (make -C oracle ref)")
+
+
+@pytest.mark.parametrize("f,n_team,n_rival", REF_SHAPES)
+def test_restatement_equals_reference_subscriber(f, n_team, n_rival):
+    """oracle/ingest_oracle.c against RobotSubscriber::callback / rival_callback / getObstacles themselves, bit for bit:
+    frames with the own entry missing, with a repeated AgentID, with no friends, with no rivals"""
+    _need_ref()
+    rng = np.random.default_rng(100 + f + n_team)
+    team, ids, rival, me = ib.random_frames(rng, f, n_team, n_rival, p_missing=0.1, p_dup=0.1)
+    ref = ib.reference_ingest(team, ids, rival, me)
+    got = ib.oracle_ingest(team, ids, rival, me)
+    for k in KEYS:
+        assert np.array_equal(got[k], ref[k]), k
+    if f >= 257 and n_team >= 5:
+        assert (ref["self_index"] < 0).any() and (ref["n_obs"] < n_team + n_rival - 1).any()   # the odd frames are in there
+
+
+def test_reference_subscriber_known_answers():
+    """the hand-computed answers of test_known_answers, asked of the reference's code"""
+    _need_ref()
+    team = np.array([[[150.0, -250.0, 30.0, -70.0, 0.5], [-845.5, 12.25, 1.0, 2.0, -1.25], [333.3, 0.1, -0.7, 299.9, 3.0]]],
+                    dtype=np.float32)
+    rival = np.array([[[700.0, 100.0, -50.0, 25.0], [0.3, -0.7, 33.3, -299.9]]], dtype=np.float32)
+    out = ib.reference_ingest(team, np.array([[2, 1, 3]], dtype=np.int32), rival, np.array([1], dtype=np.int32))
+    t64, r64 = team.astype(np.float64), rival.astype(np.float64)
+    assert out["self_index"][0] == 1 and out["n_obs"][0] == 4
+    assert np.array_equal(out["self_state"][0], t64[0, 1, :4] / 100.0) and out["heading"][0] == np.float64(np.float32(-1.25))
+    assert np.array_equal(out["obstacles"][0, :2], t64[0, [0, 2], :4] / 100.0)
+    assert np.array_equal(out["obstacles"][0, 2:4], -r64[0] * 1e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("f,n_team,n_rival", REF_SHAPES)
+def test_gpu_ingest_equals_reference_subscriber(gpu_required, f, n_team, n_rival):
+    """k_ingest_vision through the C ABI against the reference's subscriber (the library built in the build container
+    travels to the GPU box; nothing under /root/reference is read here)"""
+    from robosoccer_motion_planning_b200 import capi
+    assert ib.have_ref(), "oracle/_ref/libingest_ref.so did not travel: run __graft_entry__.build() where /root/reference is mounted"
+    rng = np.random.default_rng(100 + f + n_team)
+    team, ids, rival, me = ib.random_frames(rng, f, n_team, n_rival, p_missing=0.1, p_dup=0.1)
+    G = capi.Planner()
+    got = G.ingest_vision(team, ids, rival, me)
+    ref = ib.reference_ingest(team, ids, rival, me)
+    for k in KEYS:
+        assert np.array_equal(got[k], ref[k]), k
+    G.close()
